@@ -1,0 +1,143 @@
+/*
+ * torchpruner_b200 — C-ABI of the B200 (sm_100a) attribution-scoring / slicing hot path.
+ *
+ * Every entry point takes plain device pointers, sizes and a CUDA stream handle
+ * (a cudaStream_t passed as void*; NULL = the legacy default stream).  No torch
+ * types cross this boundary.  Unless stated otherwise an entry point
+ *   - allocates nothing and never synchronises the stream (work is enqueued),
+ *   - expects contiguous row-major fp32 tensors,
+ *   - returns TP_OK (0) or a negative TP_ERR_* code; tp_last_error() then holds a
+ *     thread-local human-readable message.
+ *
+ * "Reference" citations are file:line under the upstream TorchPruner tree
+ * (torchpruner/...), i.e. the eager-PyTorch op chain each kernel replaces.
+ */
+#ifndef TORCHPRUNER_B200_H
+#define TORCHPRUNER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* tp_stream_t; /* cudaStream_t */
+
+enum {
+  TP_OK = 0,
+  TP_ERR_INVALID = -1, /* bad argument (null pointer, negative size, misuse) */
+  TP_ERR_CUDA = -2,    /* a CUDA runtime call / launch failed */
+  TP_ERR_ARCH = -3,    /* device is not compute capability 10.x */
+  TP_ERR_LIMIT = -4    /* size beyond a documented limit */
+};
+
+/* Library version (major*10000 + minor*100 + patch). */
+int tp_version(void);
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* tp_last_error(void);
+
+/* TP_OK iff `device` (a CUDA ordinal) is an sm_100-class GPU this library was built for. */
+int tp_device_check(int device);
+
+/* Tuning / test hook.  key: "reduce_variant" (0 auto, 1 direct-load, 2 TMA-bulk tiles),
+ * "reduce_stages" (2..8), "reduce_tile_floats" (multiple of 256), "reduce_ctas_per_sm".
+ * Returns TP_ERR_INVALID for an unknown key. Not part of the reference surface. */
+int tp_set_tuning(const char* key, int64_t value);
+
+/* ---------------------------------------------------------------- K1
+ * Taylor: out[b,c] = | - sum_hw g[b,c,hw] * z[b,c,hw] |   (abs skipped when is_signed != 0)
+ * Replaces taylor.py:40-44 (grad_output[0] * activation, *-1, flatten(2).sum(-1), abs).
+ * The product is rounded to fp32 before summation, as the reference's elementwise mul is.
+ * z, g: [B,C,HW] fp32; out: [B,C] fp32.  HW == 1 covers Linear outputs ([B,C]).  */
+int tp_taylor_reduce(const float* z, const float* g, int64_t B, int64_t C, int64_t HW,
+                     int is_signed, float* out, tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K2
+ * APoZ: out[b,c] = #{hw : z[b,c,hw] > 0} as fp32 (exact integer, HW < 2^24).
+ * Replaces apoz.py:31-33 ((output > 0).float() summed over every trailing dim). */
+int tp_apoz_count(const float* z, int64_t B, int64_t C, int64_t HW, float* out,
+                  tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K3
+ * Sensitivity: out[b,c] = sum_hw |g[b,c,hw]|.  Replaces sensitivity.py:27-29. */
+int tp_abs_sum(const float* g, int64_t B, int64_t C, int64_t HW, float* out,
+               tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K4
+ * WeightNorm: out[o] = sum_k |w[o,k]|, k = Cin*kh*kw.  Replaces weight_norm.py:15-18
+ * (device->host copy of the weight, numpy abs, successive sum(-1)). */
+int tp_weight_abs_sum(const float* w, int64_t Cout, int64_t K, float* out, tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K5
+ * Stack of P prefix masks over a cached activation.  For p in [0,P):
+ *   out[p,b,c,:] = (inv_perm[c] <= k0 + p) ? +0.0f : z[b,c,:]
+ * where inv_perm[c] is the position of channel c in the permutation.  out viewed as
+ * [P*B, C, HW] is the batch handed to the downstream layers.  Replaces the clone at
+ * shapley_values.py:53 plus P successive index_fill_ calls (:56), incl. the 1-element
+ * host->device copy each of them makes.  z: [B,C,HW]; inv_perm: [C] int32 (device). */
+int tp_prefix_mask_stack(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
+                         int64_t B, int64_t C, int64_t HW, float* out, tp_stream_t stream);
+
+/* In-place x[:, idx[j], ...] = value for every j.  x: [B,C,inner]; idx: [n_idx] int64 on the
+ * device, each in [0,C).  Replaces index_fill_ at shapley_values.py:95-97 (value 0) and
+ * pruner.py:137-142 (value NaN).  `value_bits` is the fp32 bit pattern to store. */
+int tp_index_fill_dim1(float* x, int64_t B, int64_t C, int64_t inner, const int64_t* idx,
+                       int64_t n_idx, uint32_t value_bits, tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K6
+ * Per-sample loss differences of adjacent prefixes, accumulated into the fp64 score table.
+ *   L[p,b]   = kind==TP_LOSS_GIVEN ? src[p*B+b]
+ *            : cross_entropy(src[(p*B+b)*K .. +K], target[b])     (kind==TP_LOSS_CE)
+ *   prev     = p==0 ? prev_in[b] : L[p-1,b]
+ *   if p >= scatter_from:
+ *     sv[(row0+b)*ld_sv + perm[k0+p]] += (double)((L[p,b]-prev) / sv_samples)   (fp32 sub+div)
+ *   prev_out[b] = L[P-1,b]                 (prev_out must not alias prev_in)
+ *   if losses_out: losses_out[p*B+b] = L[p,b]
+ * Replaces shapley_values.py:57-61 (criterion(reduction="none"), sub, div, .cpu().numpy(),
+ * host += per evaluation) and the criterion call of attributions.py:86-87 for cross entropy.
+ * Within one call every (row, channel) cell is touched once, so no atomics are used and the
+ * accumulation order over permutations is the launch order, as in the reference.
+ * perm: [>= k0+P] int64 device; target: [B] int64 device (ignored for TP_LOSS_GIVEN). */
+enum { TP_LOSS_GIVEN = 0, TP_LOSS_CE = 1 };
+int tp_loss_delta_scatter(const float* src, const int64_t* target, int kind,
+                          const float* prev_in, float* prev_out, const int64_t* perm,
+                          int64_t k0, int64_t P, int64_t B, int64_t K, float sv_samples,
+                          double* sv, int64_t ld_sv, int64_t row0, int64_t scatter_from,
+                          float* losses_out, tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K7
+ * Fused index_select of many tensors in one launch.  Descriptor i copies
+ *   dst[o, j, :] = src[o, keep[keep_offset + j], :]   o < outer, j < n_keep
+ * with `inner_bytes` contiguous bytes per (o, j).  Replaces one index_select kernel plus one
+ * host->device index copy per tensor at pruner.py:105-112 and opt_pruner.py:16-19
+ * (weight, bias, grad, BatchNorm running stats, SGD momentum).  Copies are bit-exact.
+ * `descs` is a HOST array (it is passed to the kernel by value, <= TP_GATHER_MAX_DESCS per
+ * launch; longer tables are split into several launches); `keep` is a DEVICE int64 array. */
+typedef struct tp_gather_desc {
+  const void* src;
+  void* dst;
+  int64_t outer;        /* product of dims before the sliced axis            */
+  int64_t n_src;        /* length of the sliced axis in src                  */
+  int64_t n_keep;       /* length of the sliced axis in dst                  */
+  int64_t inner_bytes;  /* bytes per index along the axis (dims after * esz) */
+  int64_t keep_offset;  /* first element of this tensor's keep list in keep  */
+} tp_gather_desc;
+#define TP_GATHER_MAX_DESCS 32
+int tp_multi_gather(const tp_gather_desc* descs, int64_t n_desc, const int64_t* keep,
+                    int64_t keep_len, tp_stream_t stream);
+
+/* ---------------------------------------------------------------- K8
+ * NaN trick, detection side.  For x: [B,C,inner] lists (ascending) every c for which
+ * sum over b and inner of x[b,c,:] is NaN: a NaN is present, or both +inf and -inf are.
+ * Replaces pruner.py:153-167 (sum(-1)... sum(0), isnan, nonzero).  out_idx: [C] int64,
+ * out_count: [1] int64, flags_scratch: [C] int32 work area (contents undefined on return);
+ * all three on the device.  The caller reads out_count/out_idx back when it needs them. */
+int tp_nan_any_dim1(const float* x, int64_t B, int64_t C, int64_t inner,
+                    int32_t* flags_scratch, int64_t* out_idx, int64_t* out_count,
+                    tp_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TORCHPRUNER_B200_H */

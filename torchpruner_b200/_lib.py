@@ -1,0 +1,253 @@
+"""ctypes binding of the C-ABI in include/torchpruner_b200.h.
+
+Everything that reaches a GPU goes through this module: tensors are reduced to raw device
+pointers, sizes and the current CUDA stream handle before the call.  There is deliberately no
+CPU implementation behind these wrappers — if the shared library is missing, or a tensor does
+not live on a CUDA device, the call raises.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libtorchpruner_b200.so")
+
+TP_LOSS_GIVEN = 0
+TP_LOSS_CE = 1
+TP_GATHER_MAX_DESCS = 32
+
+_i64 = ctypes.c_int64
+_vp = ctypes.c_void_p
+
+
+class GatherDesc(ctypes.Structure):
+    """Mirror of `tp_gather_desc`."""
+
+    _fields_ = [
+        ("src", _vp),
+        ("dst", _vp),
+        ("outer", _i64),
+        ("n_src", _i64),
+        ("n_keep", _i64),
+        ("inner_bytes", _i64),
+        ("keep_offset", _i64),
+    ]
+
+
+_SIGNATURES = {
+    "tp_version": (ctypes.c_int, []),
+    "tp_last_error": (ctypes.c_char_p, []),
+    "tp_device_check": (ctypes.c_int, [ctypes.c_int]),
+    "tp_set_tuning": (ctypes.c_int, [ctypes.c_char_p, _i64]),
+    "tp_taylor_reduce": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, ctypes.c_int, _vp, _vp]),
+    "tp_apoz_count": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "tp_abs_sum": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
+    "tp_weight_abs_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
+    "tp_prefix_mask_stack": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
+    "tp_index_fill_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, ctypes.c_uint32, _vp]),
+    "tp_loss_delta_scatter": (
+        ctypes.c_int,
+        [_vp, _vp, ctypes.c_int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, ctypes.c_float, _vp,
+         _i64, _i64, _i64, _vp, _vp],
+    ),
+    "tp_multi_gather": (ctypes.c_int, [ctypes.POINTER(GatherDesc), _i64, _vp, _i64, _vp]),
+    "tp_nan_any_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+}
+
+_lib = None
+_checked_devices = set()
+
+
+class TorchPrunerB200Error(RuntimeError):
+    pass
+
+
+def load():
+    """Load (once) and return the ctypes handle. Raises if the library has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TorchPrunerB200Error(
+            f"{LIB_PATH} is missing: the CUDA library has not been built. Run "
+            "`python -m torchpruner_b200.csrc.build` (needs nvcc). There is no CPU fallback."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here means header and library disagree
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def _check(rc, what):
+    if rc != 0:
+        msg = load().tp_last_error().decode("utf-8", "replace")
+        raise TorchPrunerB200Error(f"{what} failed (code {rc}): {msg}")
+
+
+def _stream(t):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _cuda_f32(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TorchPrunerB200Error(
+            f"{name} must be a CUDA tensor: torchpruner_b200 has no CPU path (got "
+            f"{getattr(t, 'device', type(t))})"
+        )
+    if t.dtype != torch.float32:
+        raise TorchPrunerB200Error(f"{name} must be float32, got {t.dtype}")
+    if t.device.index not in _checked_devices:
+        _check(load().tp_device_check(t.device.index), "tp_device_check")
+        _checked_devices.add(t.device.index)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _bchw(t):
+    """(B, C, HW) of a [B, C, *spatial] tensor; HW = 1 for 2-D tensors."""
+    if t.dim() < 2:
+        raise TorchPrunerB200Error(f"expected a tensor with >= 2 dims, got shape {tuple(t.shape)}")
+    B, C = t.shape[0], t.shape[1]
+    hw = 1
+    for s in t.shape[2:]:
+        hw *= s
+    return B, C, hw
+
+
+def set_tuning(key, value):
+    _check(load().tp_set_tuning(key.encode(), int(value)), "tp_set_tuning")
+
+
+# ---------------------------------------------------------------- K1-K4 row reductions
+def taylor_reduce(z, g, signed=False, out=None):
+    z = _cuda_f32(z, "z")
+    g = _cuda_f32(g, "g")
+    if z.shape != g.shape:
+        raise TorchPrunerB200Error(f"activation {tuple(z.shape)} and gradient {tuple(g.shape)} differ")
+    B, C, hw = _bchw(z)
+    if out is None:
+        out = torch.empty((B, C), dtype=torch.float32, device=z.device)
+    with torch.cuda.device(z.device):
+        _check(load().tp_taylor_reduce(z.data_ptr(), g.data_ptr(), B, C, hw, int(bool(signed)),
+                                       out.data_ptr(), _stream(z)), "tp_taylor_reduce")
+    return out
+
+
+def apoz_count(z, out=None):
+    z = _cuda_f32(z, "z")
+    B, C, hw = _bchw(z)
+    if out is None:
+        out = torch.empty((B, C), dtype=torch.float32, device=z.device)
+    with torch.cuda.device(z.device):
+        _check(load().tp_apoz_count(z.data_ptr(), B, C, hw, out.data_ptr(), _stream(z)),
+               "tp_apoz_count")
+    return out
+
+
+def abs_sum(g, out=None):
+    g = _cuda_f32(g, "g")
+    B, C, hw = _bchw(g)
+    if out is None:
+        out = torch.empty((B, C), dtype=torch.float32, device=g.device)
+    with torch.cuda.device(g.device):
+        _check(load().tp_abs_sum(g.data_ptr(), B, C, hw, out.data_ptr(), _stream(g)), "tp_abs_sum")
+    return out
+
+
+def weight_abs_sum(w):
+    w = _cuda_f32(w, "weight")
+    cout = w.shape[0]
+    k = w.numel() // cout if cout else 0
+    out = torch.empty((cout,), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check(load().tp_weight_abs_sum(w.data_ptr(), cout, k, out.data_ptr(), _stream(w)),
+               "tp_weight_abs_sum")
+    return out
+
+
+# ---------------------------------------------------------------- K5 masks
+def prefix_mask_stack(z, inv_perm, k0, P, out=None):
+    """out[p] = z with every channel c such that inv_perm[c] <= k0+p zeroed; shape [P*B, C, ...]."""
+    z = _cuda_f32(z, "z")
+    B, C, hw = _bchw(z)
+    if inv_perm.dtype != torch.int32 or not inv_perm.is_cuda or inv_perm.numel() != C:
+        raise TorchPrunerB200Error("inv_perm must be a CUDA int32 tensor with one entry per channel")
+    if out is None:
+        out = torch.empty((P * B,) + tuple(z.shape[1:]), dtype=torch.float32, device=z.device)
+    elif out.numel() < P * z.numel() or not out.is_contiguous():
+        raise TorchPrunerB200Error("prefix_mask_stack: `out` is too small or not contiguous")
+    with torch.cuda.device(z.device):
+        _check(load().tp_prefix_mask_stack(z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C,
+                                           hw, out.data_ptr(), _stream(z)), "tp_prefix_mask_stack")
+    return out
+
+
+def index_fill_dim1_(x, idx, value_bits):
+    """In-place x[:, idx] = value (given as fp32 bit pattern). idx: CUDA int64 tensor in [0, C)."""
+    if not x.is_contiguous():
+        raise TorchPrunerB200Error("index_fill_dim1_: tensor must be contiguous to be filled in place")
+    x = _cuda_f32(x, "x")
+    if idx.dtype != torch.int64 or not idx.is_cuda:
+        raise TorchPrunerB200Error("index_fill_dim1_: idx must be a CUDA int64 tensor")
+    B, C, inner = _bchw(x)
+    with torch.cuda.device(x.device):
+        _check(load().tp_index_fill_dim1(x.data_ptr(), B, C, inner, idx.data_ptr(), idx.numel(),
+                                         int(value_bits), _stream(x)), "tp_index_fill_dim1")
+    return x
+
+
+# ---------------------------------------------------------------- K6 loss deltas
+def loss_delta_scatter(src, target, kind, prev_in, prev_out, perm, k0, P, B, K, sv_samples, sv,
+                       row0, scatter_from=0, losses_out=None):
+    src = _cuda_f32(src, "src")
+    if sv.dtype != torch.float64 or not sv.is_cuda or not sv.is_contiguous() or sv.dim() != 2:
+        raise TorchPrunerB200Error("sv must be a contiguous CUDA float64 [d, C] tensor")
+    if perm.dtype != torch.int64 or not perm.is_cuda:
+        raise TorchPrunerB200Error("perm must be a CUDA int64 tensor")
+    if row0 + B > sv.shape[0]:
+        raise TorchPrunerB200Error(
+            f"score table has {sv.shape[0]} rows but rows [{row0}, {row0 + B}) were addressed")
+    tptr = 0
+    if kind == TP_LOSS_CE:
+        if target.dtype != torch.int64 or not target.is_cuda or target.numel() != B:
+            raise TorchPrunerB200Error("cross-entropy targets must be a CUDA int64 [B] tensor")
+        tptr = target.data_ptr()
+    with torch.cuda.device(src.device):
+        _check(load().tp_loss_delta_scatter(
+            src.data_ptr(), tptr, int(kind), prev_in.data_ptr(), prev_out.data_ptr(),
+            perm.data_ptr(), int(k0), int(P), int(B), int(K), float(sv_samples), sv.data_ptr(),
+            sv.shape[1], int(row0), int(scatter_from),
+            losses_out.data_ptr() if losses_out is not None else 0, _stream(src)),
+            "tp_loss_delta_scatter")
+
+
+# ---------------------------------------------------------------- K7 gather
+def multi_gather(descs, keep, device):
+    """descs: list of GatherDesc (host); keep: CUDA int64 tensor holding every keep list."""
+    n = len(descs)
+    if n == 0:
+        return
+    arr = (GatherDesc * n)(*descs)
+    with torch.cuda.device(device):
+        _check(load().tp_multi_gather(arr, n, keep.data_ptr(), keep.numel(),
+                                      torch.cuda.current_stream(device).cuda_stream),
+               "tp_multi_gather")
+
+
+# ---------------------------------------------------------------- K8 NaN detection
+def nan_any_dim1(x, flags, out_idx, out_count):
+    x = _cuda_f32(x, "x")
+    B, C, inner = _bchw(x)
+    if flags.numel() < C or out_idx.numel() < C:
+        raise TorchPrunerB200Error("nan_any_dim1: work buffers smaller than the channel count")
+    with torch.cuda.device(x.device):
+        _check(load().tp_nan_any_dim1(x.data_ptr(), B, C, inner, flags.data_ptr(),
+                                      out_idx.data_ptr(), out_count.data_ptr(), _stream(x)),
+               "tp_nan_any_dim1")

@@ -1,0 +1,141 @@
+"""Common machinery of the attribution metrics (reference: attributions/attributions.py).
+
+The public surface (constructor, ``run``, ``find_evaluation_module``, ``run_all_forward``,
+``run_all_forward_and_backward``, ``run_forward_partial``, ``aggregate_over_samples``, the cuDNN
+determinism toggles) is the reference's.  What differs is underneath: per-batch results stay on
+the GPU until the data pass is over (one device->host copy per ``run`` instead of one per batch
+or per evaluation), and the per-channel arithmetic is done by the sm_100a kernels behind
+``torchpruner_b200._lib``.
+"""
+from abc import ABC, abstractmethod
+
+import numpy as np
+import torch
+import torch.nn as nn
+from torch.nn.modules.conv import _ConvNd
+
+from ..utils import find_best_module_for_attributions
+from ..utils.graph import ACTIVATIONS  # noqa: F401  (re-exported like the reference does)
+
+SUPPORTED_OUT_PRUNING_MODULES = [nn.Linear, _ConvNd]
+
+
+class _RowCollector:
+    """Keeps the [B, C] result of every batch on the device; one concatenation and one
+    device->host copy at the end (the reference does ``.cpu().numpy()`` + ``np.concatenate``
+    per batch: taylor.py:45-48, apoz.py:34-38, sensitivity.py:30-33)."""
+
+    def __init__(self):
+        self.blocks = []
+        self.fired = 0
+
+    def add(self, rows):
+        if self.blocks and rows.shape[1:] != self.blocks[0].shape[1:]:
+            raise RuntimeError(
+                "the evaluation module produced outputs with different channel counts "
+                f"({tuple(self.blocks[0].shape[1:])} then {tuple(rows.shape[1:])}) during one "
+                "data pass; it is probably shared between several layers (e.g. a single ReLU "
+                "reused inside a ResNet block), for which per-channel attributions are undefined")
+        self.blocks.append(rows)
+
+    def numpy(self, what):
+        if not self.blocks:
+            raise AttributeError(
+                f"no {what} was recorded: the evaluation module never ran (or, for gradient "
+                "based metrics, its output does not require grad)")
+        table = self.blocks[0] if len(self.blocks) == 1 else torch.cat(self.blocks, 0)
+        return table.cpu().numpy()
+
+
+class _AttributionMetric(ABC):
+    def __init__(self, model, data_generator, criterion, device, reduction="mean"):
+        assert reduction in ["mean", "none", "sum"] or callable(reduction), \
+            'Reduction must be a string in ["mean", "none", "sum"] or a function'
+        self.model = model
+        self.data_gen = data_generator
+        self.criterion = criterion
+        self.device = device
+        self.reduction = reduction
+        self.deterministic = False
+        self.benchmark = False
+
+    @abstractmethod
+    def run(self, module, **kwargs):
+        """Type-check ``module`` and resolve the module to evaluate at (attributions.py:28-32)."""
+        assert isinstance(module, tuple(SUPPORTED_OUT_PRUNING_MODULES)), \
+            f"Attributions can be computed only for the following modules {SUPPORTED_OUT_PRUNING_MODULES}"
+        return self.find_evaluation_module(module, **kwargs)
+
+    def find_evaluation_module(self, module, find_best_evaluation_module=False):
+        if find_best_evaluation_module is True:
+            return find_best_module_for_attributions(self.model, module)
+        return module
+
+    # ------------------------------------------------------------------ data passes
+    def _batches(self):
+        for x, y in self.data_gen:
+            yield x.to(self.device), y.to(self.device)
+
+    def run_all_forward(self):
+        """Forward pass over the whole loader; per-example losses, concatenated
+        (attributions.py:40-56).  Returns None for an empty loader, like the reference."""
+        self.set_deterministic()
+        pieces = []
+        with torch.no_grad():
+            for x, y in self._batches():
+                pieces.append(self.criterion(self.model(x), y, reduction="none"))
+            self.restore_deterministic()
+            if not pieces:
+                return None
+            return pieces[0] if len(pieces) == 1 else torch.cat(pieces, 0)
+
+    def _run_all_forward_no_loss(self):
+        """Forward-only data pass for metrics that read activations and ignore the loss."""
+        self.set_deterministic()
+        with torch.no_grad():
+            for x, _ in self._batches():
+                self.model(x)
+        self.restore_deterministic()
+
+    def run_all_forward_and_backward(self):
+        """Forward + backward of the mean loss per batch (attributions.py:58-68).  Parameter
+        gradients accumulate across batches and runs exactly as in the reference."""
+        self.set_deterministic()
+        for x, y in self._batches():
+            loss = self.criterion(self.model(x), y)
+            loss.backward()
+        self.restore_deterministic()
+
+    def run_forward_partial(self, x=None, y_true=None, to_module=None, from_module=None):
+        """Partial forward through ``model.forward_partial``; per-example loss when targets are
+        given and the pass runs to the end (attributions.py:70-89)."""
+        self.set_deterministic()
+        loss = None
+        y = self.model.forward_partial(x, to_module=to_module, from_module=from_module)
+        if y_true is not None and to_module is None:
+            loss = self.criterion(y, y_true, reduction="none")
+        self.restore_deterministic()
+        return y, loss
+
+    # ------------------------------------------------------------------ host aggregation
+    def aggregate_over_samples(self, attributions):
+        """Host-side numpy aggregation over the example axis (attributions.py:91-106); kept on
+        the host so that callable reductions see the full [N, C] matrix and means are
+        bit-identical to the reference's ``np.mean``."""
+        if self.reduction == "mean":
+            return np.mean(attributions, 0)
+        if self.reduction == "sum":
+            return np.sum(attributions, 0)
+        if self.reduction == "none":
+            return attributions
+        return self.reduction(attributions)
+
+    def set_deterministic(self):
+        self.deterministic = torch.backends.cudnn.deterministic
+        self.benchmark = torch.backends.cudnn.benchmark
+        torch.backends.cudnn.deterministic = True
+        torch.backends.cudnn.benchmark = False
+
+    def restore_deterministic(self):
+        torch.backends.cudnn.deterministic = self.deterministic
+        torch.backends.cudnn.benchmark = self.benchmark

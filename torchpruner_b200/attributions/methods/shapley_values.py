@@ -1,0 +1,269 @@
+import logging
+import os
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+from torch.nn.modules.batchnorm import _BatchNorm
+from torch.nn.modules.dropout import _DropoutNd
+
+from .. import attributions as _base
+from ... import _lib
+
+_ZERO_BITS = 0x00000000
+
+
+def shard_spans(sv_samples, n_channels, world_size, rank):
+    """Work items are the ``sv_samples * n_channels`` (permutation j, prefix position k) pairs in
+    j-major order.  Rank ``rank`` owns one contiguous span of them; the result lists, per
+    permutation touched, the half-open prefix range ``(j, k_begin, k_end)`` it evaluates.
+    25 permutations do not divide over 8 GPUs, so the split is over (j, k) pairs, not over j.
+    """
+    total = sv_samples * n_channels
+    lo = rank * total // world_size
+    hi = (rank + 1) * total // world_size
+    spans = []
+    if hi <= lo or n_channels == 0:
+        return spans
+    for j in range(lo // n_channels, (hi - 1) // n_channels + 1):
+        k_begin = max(lo, j * n_channels) - j * n_channels
+        k_end = min(hi, (j + 1) * n_channels) - j * n_channels
+        spans.append((j, k_begin, k_end))
+    return spans
+
+
+def allreduce_scores(sv, group=None):
+    """Sum the per-rank partial score tables in place (one collective per ``run``)."""
+    import torch.distributed as dist
+
+    dist.all_reduce(sv, op=dist.ReduceOp.SUM, group=group)
+    return sv
+
+
+class ShapleyAttributionMetric(_base._AttributionMetric):
+    """Monte-Carlo permutation-sampling Shapley values (reference:
+    attributions/methods/shapley_values.py).
+
+    Same estimator, same permutations (drawn from the global numpy RNG in the same call order),
+    same sign convention (positive = removing the unit raises the loss), same fp32 loss
+    arithmetic and fp64 accumulation order.  What changes is the schedule.  The reference
+    evaluates one prefix mask at a time and synchronises with the host after each one
+    (shapley_values.py:55-61); here, per batch and permutation,
+
+      1. ``tp_prefix_mask_stack`` writes P cumulatively masked copies of the cached activation
+         in one launch,
+      2. the layers after the evaluation module run once on the stacked [P*B, ...] batch
+         (the user's ``forward_partial`` — per-example maths is independent of its batch
+         neighbours as long as BatchNorm/Dropout are in eval mode; otherwise each mask gets its
+         own forward, in the reference's order),
+      3. ``tp_loss_delta_scatter`` forms the adjacent-prefix loss differences and adds them to
+         the fp64 score table that lives on the GPU,
+
+    and nothing is copied to the host until the whole table is done.
+
+    Optional sharding over the GPUs of one node: set ``TORCHPRUNER_B200_SHARD=1`` (or assign
+    ``metric.process_group``) with ``torch.distributed`` initialised and every rank holding the
+    same model, data and numpy seed.  (j, k) work items are split into contiguous spans, each
+    rank evaluates one extra "halo" prefix so that loss differences stay local, and a single
+    all-reduce (NCCL over NVLink) of the score table ends the run.
+    """
+
+    def __init__(self, *args, sv_samples=5, **kwargs):
+        super().__init__(*args, **kwargs)
+        self.samples = sv_samples
+        self.mask_indices = []
+        self.process_group = None
+        self.shard = os.environ.get("TORCHPRUNER_B200_SHARD", "0") == "1"
+        self.max_stack_bytes = int(os.environ.get("TORCHPRUNER_B200_STACK_MB", "1024")) << 20
+        self.max_stack = int(os.environ.get("TORCHPRUNER_B200_MAX_STACK", "512"))
+        self.last_run_info = {}
+
+    def run(self, module, sv_samples=None, **kwargs):
+        module = super().run(module, **kwargs)
+        sv_samples = sv_samples if sv_samples is not None else self.samples
+        if hasattr(self.model, "forward_partial"):
+            return self.run_module_with_partial(module, sv_samples)
+        logging.warning("Consider adding a 'forward_partial' method to your model to speed-up "
+                        "Shapley values computation")
+        return self.run_module(module, sv_samples)
+
+    # ------------------------------------------------------------------ helpers
+    def _dist(self):
+        """(group, world_size, rank) when sharding is requested and possible, else (None, 1, 0)."""
+        if not (self.shard or self.process_group is not None):
+            return None, 1, 0
+        import torch.distributed as dist
+
+        if not (dist.is_available() and dist.is_initialized()):
+            return None, 1, 0
+        group = self.process_group
+        return group, dist.get_world_size(group), dist.get_rank(group)
+
+    def _stack_safe(self):
+        """Evaluating several masks as one batch is only the same computation if no layer mixes
+        examples of a batch or draws per-call randomness: BatchNorm/Dropout must be in eval."""
+        return not any(m.training and isinstance(m, (_BatchNorm, _DropoutNd))
+                       for m in self.model.modules())
+
+    @staticmethod
+    def _per_example(loss, batch):
+        if loss.numel() != batch:
+            raise ValueError(
+                f"criterion(..., reduction='none') returned {tuple(loss.shape)} for a batch of "
+                f"{batch}; one loss per example is required")
+        return loss.reshape(batch).float().contiguous()
+
+    def _fused_ce_ok(self, logits, y, loss):
+        """The fused cross-entropy path is taken only when it reproduces the user's criterion on
+        this batch's unmasked logits."""
+        if not (logits.dim() == 2 and y.dim() == 1 and y.dtype == torch.int64
+                and logits.dtype == torch.float32 and y.numel() == logits.shape[0]):
+            return False
+        if self.criterion is F.cross_entropy:
+            return True
+        B, K = logits.shape
+        probe = torch.empty(B, dtype=torch.float32, device=logits.device)
+        scratch_prev = torch.zeros(B, dtype=torch.float32, device=logits.device)
+        dummy_sv = torch.zeros((B, 1), dtype=torch.float64, device=logits.device)
+        dummy_perm = torch.zeros(1, dtype=torch.int64, device=logits.device)
+        _lib.loss_delta_scatter(logits.contiguous(), y, _lib.TP_LOSS_CE, scratch_prev,
+                                torch.empty_like(scratch_prev), dummy_perm, 0, 1, B, K, 1.0,
+                                dummy_sv, 0, scatter_from=1, losses_out=probe)
+        return bool(torch.allclose(probe, loss, rtol=2e-6, atol=2e-6))
+
+    # ------------------------------------------------------------------ fast path
+    def run_module_with_partial(self, module, sv_samples):
+        """Shapley sampling for models that provide ``forward_partial``
+        (shapley_values.py:28-64)."""
+        d = len(self.data_gen.dataset)
+        group, world, rank = self._dist()
+        sv = None
+        perm_dev = inv_dev = None
+        spans = None
+        row = 0
+        n_evals = 0
+        stack_safe = self._stack_safe()
+
+        with torch.no_grad():
+            for x, y in self._batches():
+                original_z, _ = self.run_forward_partial(x, to_module=module)
+                logits0, original_loss = self.run_forward_partial(original_z, y_true=y,
+                                                                  from_module=module)
+                z = original_z.detach().float().contiguous()
+                B, n = z.shape[0], z.shape[1]
+                if perm_dev is None:
+                    # Same permutations for all batches; same RNG calls as the reference (:47).
+                    permutations = [np.random.permutation(n) for _ in range(sv_samples)]
+                    perm_host = np.stack(permutations).astype(np.int64) if sv_samples else \
+                        np.zeros((0, n), np.int64)
+                    inv_host = np.empty_like(perm_host, dtype=np.int32)
+                    for j in range(sv_samples):
+                        inv_host[j, perm_host[j]] = np.arange(n, dtype=np.int32)
+                    perm_dev = torch.from_numpy(perm_host).to(z.device)
+                    inv_dev = torch.from_numpy(inv_host).to(z.device)
+                    spans = shard_spans(sv_samples, n, world, rank)
+                if sv is None:
+                    sv = torch.zeros((d, n), dtype=torch.float64, device=z.device)
+
+                loss0 = self._per_example(original_loss, B)
+                fused_ce = self._fused_ce_ok(logits0, y, loss0)
+                bytes_per_copy = max(1, z.numel() * 4)
+                P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // bytes_per_copy)))
+                stack = torch.empty((P_max * B,) + tuple(z.shape[1:]), dtype=torch.float32,
+                                    device=z.device)
+                prev_a = torch.empty(B, dtype=torch.float32, device=z.device)
+                prev_b = torch.empty_like(prev_a)
+                y_stack = None
+
+                def evaluate(j, k0, P, prev_in, prev_out, scatter_from):
+                    nonlocal y_stack
+                    masked = _lib.prefix_mask_stack(z, inv_dev[j], k0, P, out=stack)[:P * B]
+                    if stack_safe:
+                        out = self.model.forward_partial(masked, to_module=None, from_module=module)
+                    else:
+                        out = torch.cat([
+                            self.model.forward_partial(masked[p * B:(p + 1) * B], to_module=None,
+                                                       from_module=module) for p in range(P)], 0)
+                    if fused_ce:
+                        _lib.loss_delta_scatter(out.float().contiguous(), y, _lib.TP_LOSS_CE,
+                                                prev_in, prev_out, perm_dev[j], k0, P, B,
+                                                out.shape[1], sv_samples, sv, row, scatter_from)
+                    else:
+                        if y_stack is None or y_stack.shape[0] != P * B:
+                            y_stack = y.repeat((P,) + (1,) * (y.dim() - 1))
+                        losses = self.criterion(out, y_stack, reduction="none")
+                        _lib.loss_delta_scatter(self._per_example(losses, P * B), None,
+                                                _lib.TP_LOSS_GIVEN, prev_in, prev_out, perm_dev[j],
+                                                k0, P, B, 1, sv_samples, sv, row, scatter_from)
+
+                self.set_deterministic()
+                for (j, k_begin, k_end) in spans:
+                    prev_in, prev_out = prev_a, prev_b
+                    if k_begin == 0:
+                        prev_in.copy_(loss0)
+                    else:  # halo: loss with the first k_begin channels of permutation j removed
+                        evaluate(j, k_begin - 1, 1, prev_out, prev_in, scatter_from=1)
+                        n_evals += 1
+                    for k0 in range(k_begin, k_end, P_max):
+                        P = min(P_max, k_end - k0)
+                        evaluate(j, k0, P, prev_in, prev_out, scatter_from=0)
+                        prev_in, prev_out = prev_out, prev_in
+                        n_evals += P
+                self.restore_deterministic()
+                row += B
+
+            if sv is None:  # empty loader: the reference would hand None to numpy
+                return self.aggregate_over_samples(None)
+            if world > 1:
+                allreduce_scores(sv, group)
+            self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
+                                  "stacked": stack_safe}
+            return self.aggregate_over_samples(sv.cpu().numpy())
+
+    # ------------------------------------------------------------------ slow path
+    def run_module(self, module, samples):
+        """Shapley sampling without ``forward_partial`` (shapley_values.py:66-90): every marginal
+        evaluation is a forward pass of the whole model over the whole loader with the growing
+        set of masked channels zero-filled by a forward hook.  The fill is ``tp_index_fill_dim1``
+        and the score update ``tp_loss_delta_scatter``; no per-evaluation host sync."""
+        with torch.no_grad():
+            self.mask_indices = []
+            mask_dev = {"idx": None}
+
+            def forward_hook(mod, _inputs, output):
+                mod._tp_prune_dim = output.shape[1]
+                if mask_dev["idx"] is not None and mask_dev["idx"].numel() > 0:
+                    if output.is_contiguous():
+                        _lib.index_fill_dim1_(output, mask_dev["idx"], _ZERO_BITS)
+                    else:
+                        filled = _lib.index_fill_dim1_(output.contiguous(), mask_dev["idx"],
+                                                       _ZERO_BITS)
+                        output.copy_(filled)
+                return output
+
+            handle = module.register_forward_hook(forward_hook)
+            try:
+                original_loss = self.run_all_forward()
+                n = module._tp_prune_dim
+                N = original_loss.shape[0]
+                dev = original_loss.device
+                sv = torch.zeros((N, n), dtype=torch.float64, device=dev)
+                prev_a = torch.empty(N, dtype=torch.float32, device=dev)
+                prev_b = torch.empty_like(prev_a)
+                for _ in range(samples):
+                    self.mask_indices = []
+                    prev_in, prev_out = prev_a, prev_b
+                    prev_in.copy_(self._per_example(original_loss, N))
+                    perm = np.random.permutation(n)  # drawn per sample, as in the reference (:83)
+                    perm_dev = torch.from_numpy(perm.astype(np.int64)).to(dev)
+                    for k, i in enumerate(perm):
+                        self.mask_indices.append(i)
+                        mask_dev["idx"] = perm_dev[:k + 1]
+                        new_loss = self._per_example(self.run_all_forward(), N)
+                        _lib.loss_delta_scatter(new_loss, None, _lib.TP_LOSS_GIVEN, prev_in,
+                                                prev_out, perm_dev, k, 1, N, 1, samples, sv, 0)
+                        prev_in, prev_out = prev_out, prev_in
+                    mask_dev["idx"] = None
+            finally:
+                handle.remove()
+            return self.aggregate_over_samples(sv.cpu().numpy())

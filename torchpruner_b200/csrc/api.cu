@@ -1,0 +1,81 @@
+// Library-level entry points: version, error string, device check, tuning knobs.
+#include "common.cuh"
+
+#include <string.h>
+
+namespace tp {
+
+static thread_local char g_err[512] = {0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int sm_count() {
+  // One entry per device ordinal; filled lazily.  cudaDeviceGetAttribute is cheap but this is
+  // on the launch path of microsecond kernels.
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+Tuning& tuning() {
+  static Tuning t;
+  return t;
+}
+
+}  // namespace tp
+
+extern "C" {
+
+int tp_version(void) { return 100; /* 0.1.0 */ }
+
+const char* tp_last_error(void) { return tp::g_err; }
+
+int tp_device_check(int device) {
+  int major = 0, minor = 0;
+  TP_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  TP_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+  TP_REQUIRE(major == 10, TP_ERR_ARCH,
+             "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, major,
+             minor);
+  return TP_OK;
+}
+
+int tp_set_tuning(const char* key, int64_t value) {
+  TP_REQUIRE(key != nullptr, TP_ERR_INVALID, "tp_set_tuning: key is NULL");
+  tp::Tuning& t = tp::tuning();
+  if (!strcmp(key, "reduce_variant")) {
+    TP_REQUIRE(value >= 0 && value <= 2, TP_ERR_INVALID, "reduce_variant must be 0, 1 or 2");
+    t.reduce_variant = (int)value;
+  } else if (!strcmp(key, "reduce_stages")) {
+    TP_REQUIRE(value >= 2 && value <= 8, TP_ERR_INVALID, "reduce_stages must be in [2,8]");
+    t.reduce_stages = (int)value;
+  } else if (!strcmp(key, "reduce_tile_floats")) {
+    TP_REQUIRE(value >= 256 && value <= 16384 && value % 256 == 0, TP_ERR_INVALID,
+               "reduce_tile_floats must be a multiple of 256 in [256,16384]");
+    t.reduce_tile_floats = (int)value;
+  } else if (!strcmp(key, "reduce_ctas_per_sm")) {
+    TP_REQUIRE(value >= 1 && value <= 8, TP_ERR_INVALID, "reduce_ctas_per_sm must be in [1,8]");
+    t.reduce_ctas_per_sm = (int)value;
+  } else if (!strcmp(key, "reduce_tma_min_elems")) {
+    TP_REQUIRE(value >= 0, TP_ERR_INVALID, "reduce_tma_min_elems must be >= 0");
+    t.reduce_tma_min_elems = (int)(value > (1ll << 30) ? (1ll << 30) : value);
+  } else {
+    tp::set_error("tp_set_tuning: unknown key '%s'", key);
+    return TP_ERR_INVALID;
+  }
+  return TP_OK;
+}
+
+}  // extern "C"

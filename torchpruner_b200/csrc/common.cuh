@@ -1,0 +1,119 @@
+// Shared helpers for the torchpruner_b200 CUDA library (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/torchpruner_b200.h"
+
+namespace tp {
+
+// ---- error plumbing -----------------------------------------------------------------
+void set_error(const char* fmt, ...);
+
+#define TP_REQUIRE(cond, code, ...)       \
+  do {                                    \
+    if (!(cond)) {                        \
+      ::tp::set_error(__VA_ARGS__);       \
+      return (code);                      \
+    }                                     \
+  } while (0)
+
+#define TP_CUDA(expr)                                                               \
+  do {                                                                              \
+    cudaError_t _e = (expr);                                                        \
+    if (_e != cudaSuccess) {                                                        \
+      ::tp::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),       \
+                      __FILE__, __LINE__);                                          \
+      return TP_ERR_CUDA;                                                           \
+    }                                                                               \
+  } while (0)
+
+#define TP_LAUNCH_CHECK(name)                                                       \
+  do {                                                                              \
+    cudaError_t _e = cudaGetLastError();                                            \
+    if (_e != cudaSuccess) {                                                        \
+      ::tp::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));     \
+      return TP_ERR_CUDA;                                                           \
+    }                                                                               \
+  } while (0)
+
+// Cached per-process device facts (SM count of the current device).
+int sm_count();
+
+// ---- tuning knobs (tp_set_tuning) ---------------------------------------------------
+struct Tuning {
+  int reduce_variant = 0;        // 0 auto, 1 direct loads, 2 TMA bulk tiles
+  int reduce_stages = 4;         // smem ring depth of the TMA variant
+  int reduce_tile_floats = 4096; // floats per stream per stage
+  int reduce_ctas_per_sm = 2;    // persistent CTAs per SM (TMA variant)
+  int reduce_tma_min_elems = 1 << 20;
+};
+Tuning& tuning();
+
+// ---- device helpers -----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+
+// Make mbarrier initialisation visible to the async (TMA) proxy.
+__device__ __forceinline__ void fence_mbar_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP).
+// dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes,
+                                         uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// Streaming 128-bit load that does not allocate in L1 (data is read exactly once).
+__device__ __forceinline__ float4 ldg_stream4(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ldg_stream1(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+}  // namespace tp

@@ -1,0 +1,500 @@
+// K1-K4: single-pass per-row reductions over a flat [R, L] fp32 view of an NCHW tensor
+// (R = B*C rows, L = H*W contiguous elements per row), one fp32 result per row.
+//
+//   Taylor      out[r] = | - sum_l g[r,l]*z[r,l] |      reference taylor.py:40-44
+//   APoZ        out[r] = #{l : z[r,l] > 0}              reference apoz.py:31-33
+//   Sensitivity out[r] = sum_l |g[r,l]|                 reference sensitivity.py:27-29
+//   WeightNorm  out[o] = sum_k |w[o,k]|                 reference weight_norm.py:15-18
+//
+// All four are HBM-bound streaming reads (algorithmic bytes: 8*R*L+4*R for Taylor, 4*R*L+4*R
+// for the others).  Two implementations share the per-element op and the reduction tree:
+//
+//  * reduce_rows_tma  — persistent CTAs (a multiple of the SM count).  Each CTA walks tiles of
+//    whole rows (or 16 KB chunks of one long row); tiles are brought into a shared-memory ring
+//    by 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx) issued `stages-1` tiles
+//    ahead, so the bytes in flight per SM do not depend on register count or occupancy.  Rows
+//    whose length is not a multiple of 4 floats (ResNet 7x7 = 49) still move as 16-byte-aligned
+//    tiles because a tile always starts on a multiple of 4 rows.
+//  * reduce_rows_ldg  — direct 128-bit (or scalar, for unaligned views) streaming loads with
+//    `LPR` lanes cooperating on a row; used for small problems, unaligned pointers and the
+//    ragged tail the TMA kernel cannot express.
+//
+// Summation is fp32 in a fixed order (per-lane strided partials, then a shuffle tree), so the
+// result is deterministic run to run; it differs from ATen's order only by fp32 rounding.
+#include "common.cuh"
+
+#include <type_traits>
+
+namespace tp {
+
+enum RowOp { OP_TAYLOR = 0, OP_APOZ = 1, OP_ABSSUM = 2 };
+
+template <int OP>
+struct RowOpTraits {
+  using acc_t = float;
+  static constexpr int kStreams = (OP == OP_TAYLOR) ? 2 : 1;
+  __device__ __forceinline__ static void add(acc_t& acc, float a, float b) {
+    if (OP == OP_TAYLOR) {
+      // -(g*z) with the product rounded to fp32 first (no FMA contraction), as torch's mul is.
+      acc = __fsub_rn(acc, __fmul_rn(a, b));
+    } else {
+      acc = __fadd_rn(acc, fabsf(a));
+    }
+  }
+  __device__ __forceinline__ static float finalize(acc_t acc, int is_signed) {
+    if (OP == OP_TAYLOR) return is_signed ? acc : fabsf(acc);
+    return acc;
+  }
+};
+
+template <>
+struct RowOpTraits<OP_APOZ> {
+  using acc_t = int;
+  static constexpr int kStreams = 1;
+  __device__ __forceinline__ static void add(acc_t& acc, float a, float) { acc += (a > 0.0f); }
+  __device__ __forceinline__ static float finalize(acc_t acc, int) { return (float)acc; }
+};
+
+template <typename T>
+__device__ __forceinline__ T group_reduce(T v, int lpr) {
+  // Sum over aligned groups of `lpr` lanes (lpr a power of two <= 32).  Every lane takes part.
+  for (int off = lpr >> 1; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+
+template <int OP>
+__device__ __forceinline__ void add4(typename RowOpTraits<OP>::acc_t& acc, const float4& a,
+                                     const float4& b) {
+  RowOpTraits<OP>::add(acc, a.x, b.x);
+  RowOpTraits<OP>::add(acc, a.y, b.y);
+  RowOpTraits<OP>::add(acc, a.z, b.z);
+  RowOpTraits<OP>::add(acc, a.w, b.w);
+}
+
+// =====================================================================================
+// Direct-load kernel.
+//   LONG == false: a row has n <= LPR units (unit = float4 if VEC else float): one unit per
+//                  lane, 32/LPR rows per warp pass, 4 passes in flight per warp.
+//   LONG == true : LPR == 32, one warp per row, units strided over lanes, 4 loads in flight.
+// =====================================================================================
+template <int OP, int LPR, bool VEC, bool LONG>
+__global__ void __launch_bounds__(256)
+reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
+                float* __restrict__ out, int64_t R, int64_t L, int is_signed) {
+  using T = RowOpTraits<OP>;
+  using acc_t = typename T::acc_t;
+  constexpr bool kTwo = (T::kStreams == 2);
+  constexpr int RPW = 32 / LPR;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPR;
+  const int slot = lane / LPR;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = (gridDim.x * (int64_t)blockDim.x) >> 5;
+  const int64_t n = VEC ? (L >> 2) : L;
+
+  if (!LONG) {
+    constexpr int U = 4;
+    for (int64_t base = warp * (RPW * U); base < R; base += nwarps * (RPW * U)) {
+      acc_t acc[U];
+      if (VEC) {
+        float4 va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t row = base + u * RPW + slot;
+          va[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          vb[u] = va[u];
+          if (row < R && sub < n) {
+            va[u] = ldg_stream4(reinterpret_cast<const float4*>(a) + row * n + sub);
+            if (kTwo) vb[u] = ldg_stream4(reinterpret_cast<const float4*>(b) + row * n + sub);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u] = 0;
+          add4<OP>(acc[u], va[u], vb[u]);
+        }
+      } else {
+        float va[U], vb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t row = base + u * RPW + slot;
+          va[u] = 0.f;
+          vb[u] = 0.f;
+          if (row < R && sub < n) {
+            va[u] = ldg_stream1(a + row * n + sub);
+            if (kTwo) vb[u] = ldg_stream1(b + row * n + sub);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          acc[u] = 0;
+          T::add(acc[u], va[u], vb[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const acc_t s = group_reduce(acc[u], LPR);
+        const int64_t row = base + u * RPW + slot;
+        if (sub == 0 && row < R) out[row] = T::finalize(s, is_signed);
+      }
+    }
+  } else {
+    constexpr int U = 4;
+    for (int64_t row = warp; row < R; row += nwarps) {
+      acc_t acc = 0;
+      if (VEC) {
+        const float4* pa = reinterpret_cast<const float4*>(a) + row * n;
+        const float4* pb = reinterpret_cast<const float4*>(b) + row * n;
+        for (int64_t i = lane; i < n; i += 32 * U) {
+          float4 va[U], vb[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t j = i + 32 * u;
+            va[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            vb[u] = va[u];
+            if (j < n) {
+              va[u] = ldg_stream4(pa + j);
+              if (kTwo) vb[u] = ldg_stream4(pb + j);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) add4<OP>(acc, va[u], vb[u]);
+        }
+      } else {
+        const float* pa = a + row * n;
+        const float* pb = b + row * n;
+        for (int64_t i = lane; i < n; i += 32 * U) {
+          float va[U], vb[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t j = i + 32 * u;
+            va[u] = 0.f;
+            vb[u] = 0.f;
+            if (j < n) {
+              va[u] = ldg_stream1(pa + j);
+              if (kTwo) vb[u] = ldg_stream1(pb + j);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) T::add(acc, va[u], vb[u]);
+        }
+      }
+      const acc_t s = group_reduce(acc, 32);
+      if (lane == 0) out[row] = T::finalize(s, is_signed);
+    }
+  }
+}
+
+// =====================================================================================
+// TMA-bulk tiled kernel (persistent).  Shared memory: [stages][streams][tile_floats] floats,
+// then `stages` mbarriers, then 8 floats/ints of block-reduction scratch.
+//   chunk_mode == 0: tile = `tile_rows` whole rows (host guarantees tile_rows*L % 4 == 0 and
+//                    the last, shorter tile is also a multiple of 16 bytes).
+//   chunk_mode == 1: L > tile_floats and L % 4 == 0; a CTA owns whole rows and streams each
+//                    one through the ring in chunks of tile_floats.
+// =====================================================================================
+constexpr int kTmaThreads = 256;
+
+template <int OP, bool VEC>
+__global__ void __launch_bounds__(kTmaThreads)
+reduce_rows_tma(const float* __restrict__ a, const float* __restrict__ b,
+                float* __restrict__ out, int64_t R, int64_t L, int is_signed, int tile_rows,
+                int chunk_mode, int stages, int tile_floats, int lpr) {
+  using T = RowOpTraits<OP>;
+  using acc_t = typename T::acc_t;
+  constexpr int kStreams = T::kStreams;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* ring = reinterpret_cast<float*>(smem_raw);
+  uint64_t* bars =
+      reinterpret_cast<uint64_t*>(smem_raw + (size_t)stages * kStreams * tile_floats * 4);
+  acc_t* red = reinterpret_cast<acc_t*>(bars + stages);
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int wid = tid >> 5;
+  const int64_t G = gridDim.x;
+  const int64_t c = blockIdx.x;
+
+  // Work owned by this CTA.
+  int64_t n_chunks = 1;  // chunks per row (chunk mode)
+  int64_t my_count;
+  if (chunk_mode) {
+    n_chunks = (L + tile_floats - 1) / tile_floats;
+    const int64_t my_rows = (R > c) ? (R - c + G - 1) / G : 0;
+    my_count = my_rows * n_chunks;
+  } else {
+    const int64_t n_tiles = (R + tile_rows - 1) / tile_rows;
+    my_count = (n_tiles > c) ? (n_tiles - c + G - 1) / G : 0;
+  }
+
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&bars[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  auto tile_extent = [&](int64_t i, int64_t& first_elem, int64_t& n_floats) {
+    if (chunk_mode) {
+      const int64_t row = c + (i / n_chunks) * G;
+      const int64_t ch = i % n_chunks;
+      first_elem = row * L + ch * tile_floats;
+      const int64_t left = L - ch * tile_floats;
+      n_floats = left < tile_floats ? left : tile_floats;
+    } else {
+      const int64_t t = c + i * G;
+      const int64_t r0 = t * tile_rows;
+      const int64_t rows = (R - r0) < tile_rows ? (R - r0) : tile_rows;
+      first_elem = r0 * L;
+      n_floats = rows * L;
+    }
+  };
+
+  auto issue = [&](int64_t i) {  // called by thread 0 only
+    const int s = (int)(i % stages);
+    int64_t first, nf;
+    tile_extent(i, first, nf);
+    const uint32_t bytes = (uint32_t)(nf * 4);
+    mbar_arrive_expect_tx(&bars[s], bytes * kStreams);
+    float* dst = ring + (size_t)s * kStreams * tile_floats;
+    bulk_g2s(dst, a + first, bytes, &bars[s]);
+    if (kStreams == 2) bulk_g2s(dst + tile_floats, b + first, bytes, &bars[s]);
+  };
+
+  if (tid == 0) {
+    const int64_t pre = my_count < (stages - 1) ? my_count : (stages - 1);
+    for (int64_t i = 0; i < pre; ++i) issue(i);
+  }
+
+  acc_t row_acc = 0;  // chunk mode: partial of the row in flight
+
+  for (int64_t i = 0; i < my_count; ++i) {
+    // Stage (i-1)%stages was drained by every thread before the barrier that ended the
+    // previous iteration, so it can be refilled now.
+    if (tid == 0 && i + stages - 1 < my_count) issue(i + stages - 1);
+    const int s = (int)(i % stages);
+    mbar_wait(&bars[s], (uint32_t)((i / stages) & 1));
+
+    const float* sa = ring + (size_t)s * kStreams * tile_floats;
+    const float* sb = sa + tile_floats;
+    int64_t first, nf;
+    tile_extent(i, first, nf);
+
+    if (chunk_mode) {
+      const int nv = (int)(nf >> 2);
+      const float4* sa4 = reinterpret_cast<const float4*>(sa);
+      const float4* sb4 = reinterpret_cast<const float4*>(sb);
+      for (int v = tid; v < nv; v += kTmaThreads) {
+        const float4 va = sa4[v];
+        const float4 vb = (kStreams == 2) ? sb4[v] : va;
+        add4<OP>(row_acc, va, vb);
+      }
+      if ((i % n_chunks) == n_chunks - 1) {
+        const acc_t w = group_reduce(row_acc, 32);
+        if (lane == 0) red[wid] = w;
+        __syncthreads();
+        if (tid == 0) {
+          acc_t tot = 0;
+          for (int k = 0; k < kTmaThreads / 32; ++k) tot += red[k];
+          out[c + (i / n_chunks) * G] = T::finalize(tot, is_signed);
+        }
+        row_acc = 0;
+      }
+    } else {
+      const int64_t r0 = (c + i * G) * tile_rows;
+      const int rows = (int)(nf / L);
+      const int rpw = 32 / lpr;
+      const int sub = lane % lpr;
+      const int slot = lane / lpr;
+      const int n = VEC ? (int)(L >> 2) : (int)L;
+      for (int rb = wid * rpw; rb < rows; rb += (kTmaThreads / 32) * rpw) {
+        const int r = rb + slot;
+        acc_t acc = 0;
+        if (r < rows) {
+          if (VEC) {
+            const float4* pa = reinterpret_cast<const float4*>(sa) + (size_t)r * n;
+            const float4* pb = reinterpret_cast<const float4*>(sb) + (size_t)r * n;
+            for (int j = sub; j < n; j += lpr) {
+              const float4 va = pa[j];
+              const float4 vb = (kStreams == 2) ? pb[j] : va;
+              add4<OP>(acc, va, vb);
+            }
+          } else {
+            const float* pa = sa + (size_t)r * n;
+            const float* pb = sb + (size_t)r * n;
+            for (int j = sub; j < n; j += lpr) {
+              const float va = pa[j];
+              const float vb = (kStreams == 2) ? pb[j] : va;
+              T::add(acc, va, vb);
+            }
+          }
+        }
+        acc = group_reduce(acc, lpr);
+        if (sub == 0 && r < rows) out[r0 + r] = T::finalize(acc, is_signed);
+      }
+    }
+    __syncthreads();  // stage s fully consumed (and `red` free again)
+  }
+}
+
+// ---- host-side dispatch ---------------------------------------------------------------
+
+static inline int pow2_ceil(int64_t v) {
+  int p = 1;
+  while (p < v && p < 32) p <<= 1;
+  return p;
+}
+
+static inline int64_t gcd64(int64_t x, int64_t y) {
+  while (y) {
+    int64_t t = x % y;
+    x = y;
+    y = t;
+  }
+  return x;
+}
+
+template <int OP, int LPR, bool VEC, bool LONG>
+static int launch_ldg_inst(const float* a, const float* b, float* out, int64_t R, int64_t L,
+                           int is_signed, cudaStream_t st) {
+  constexpr int RPW = 32 / LPR;
+  const int64_t rows_per_warp = LONG ? 1 : RPW * 4;
+  const int64_t warps = (R + rows_per_warp - 1) / rows_per_warp;
+  int64_t blocks = (warps + 7) / 8;
+  const int64_t cap = (int64_t)sm_count() * 8 * 4;  // 8 resident 256-thread CTAs x 4 waves
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  reduce_rows_ldg<OP, LPR, VEC, LONG><<<(unsigned)blocks, 256, 0, st>>>(a, b, out, R, L, is_signed);
+  TP_LAUNCH_CHECK("reduce_rows_ldg");
+  return TP_OK;
+}
+
+template <int OP, bool VEC>
+static int launch_ldg_vec(const float* a, const float* b, float* out, int64_t R, int64_t L,
+                          int is_signed, cudaStream_t st) {
+  const int64_t n = VEC ? (L >> 2) : L;
+  if (n > 32) return launch_ldg_inst<OP, 32, VEC, true>(a, b, out, R, L, is_signed, st);
+  switch (pow2_ceil(n)) {
+    case 1: return launch_ldg_inst<OP, 1, VEC, false>(a, b, out, R, L, is_signed, st);
+    case 2: return launch_ldg_inst<OP, 2, VEC, false>(a, b, out, R, L, is_signed, st);
+    case 4: return launch_ldg_inst<OP, 4, VEC, false>(a, b, out, R, L, is_signed, st);
+    case 8: return launch_ldg_inst<OP, 8, VEC, false>(a, b, out, R, L, is_signed, st);
+    case 16: return launch_ldg_inst<OP, 16, VEC, false>(a, b, out, R, L, is_signed, st);
+    default: return launch_ldg_inst<OP, 32, VEC, false>(a, b, out, R, L, is_signed, st);
+  }
+}
+
+template <int OP>
+static int launch_ldg(const float* a, const float* b, float* out, int64_t R, int64_t L,
+                      int is_signed, cudaStream_t st) {
+  const bool two = RowOpTraits<OP>::kStreams == 2;
+  const bool aligned =
+      ((uintptr_t)a % 16 == 0) && (!two || (uintptr_t)b % 16 == 0) && (L % 4 == 0);
+  if (aligned) return launch_ldg_vec<OP, true>(a, b, out, R, L, is_signed, st);
+  return launch_ldg_vec<OP, false>(a, b, out, R, L, is_signed, st);
+}
+
+template <int OP, bool VEC>
+static int launch_tma_inst(const float* a, const float* b, float* out, int64_t R, int64_t L,
+                           int is_signed, int tile_rows, int chunk_mode, int tile_floats,
+                           cudaStream_t st) {
+  const Tuning& t = tuning();
+  constexpr int kStreams = RowOpTraits<OP>::kStreams;
+  const int ctas = t.reduce_ctas_per_sm;
+  const size_t per_stage = (size_t)kStreams * tile_floats * 4;
+  const size_t budget = (size_t)(220 * 1024) / ctas - 256;
+  int stages = t.reduce_stages;
+  if ((size_t)stages * per_stage > budget) stages = (int)(budget / per_stage);
+  TP_REQUIRE(stages >= 2, TP_ERR_INVALID,
+             "reduce tuning leaves room for < 2 stages (tile_floats=%d, ctas_per_sm=%d)",
+             tile_floats, ctas);
+  const size_t smem = (size_t)stages * per_stage + (size_t)stages * 8 + 64;
+  const int64_t units = chunk_mode ? R : (R + tile_rows - 1) / tile_rows;
+  int64_t grid = (int64_t)sm_count() * ctas;
+  if (grid > units) grid = units;
+  auto kern = reduce_rows_tma<OP, VEC>;
+  TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int n = VEC ? (int)(L >> 2) : (int)L;
+  const int lpr = pow2_ceil(n);
+  kern<<<(unsigned)grid, kTmaThreads, smem, st>>>(a, b, out, R, L, is_signed, tile_rows, chunk_mode,
+                                                  stages, tile_floats, lpr);
+  TP_LAUNCH_CHECK("reduce_rows_tma");
+  return TP_OK;
+}
+
+template <int OP>
+static int launch_reduce(const float* a, const float* b, float* out, int64_t R, int64_t L,
+                         int is_signed, tp_stream_t stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool two = RowOpTraits<OP>::kStreams == 2;
+  TP_REQUIRE(R >= 0 && L >= 0, TP_ERR_INVALID, "negative size (rows=%lld, len=%lld)",
+             (long long)R, (long long)L);
+  if (R == 0) return TP_OK;
+  TP_REQUIRE(out != nullptr, TP_ERR_INVALID, "out is NULL");
+  if (L == 0) {  // empty sum
+    TP_CUDA(cudaMemsetAsync(out, 0, (size_t)R * 4, st));
+    return TP_OK;
+  }
+  TP_REQUIRE(a != nullptr && (!two || b != nullptr), TP_ERR_INVALID, "input pointer is NULL");
+  TP_REQUIRE(L < (1ll << 31) && R < (1ll << 40), TP_ERR_LIMIT, "shape too large");
+
+  const Tuning& t = tuning();
+  const bool ptr_aligned = ((uintptr_t)a % 16 == 0) && (!two || (uintptr_t)b % 16 == 0);
+  bool use_tma = ptr_aligned && (t.reduce_variant == 2 ||
+                                 (t.reduce_variant == 0 && R * L >= t.reduce_tma_min_elems));
+  if (use_tma) {
+    const int tile_floats = t.reduce_tile_floats;
+    if (L <= tile_floats) {
+      const int64_t ar = 4 / gcd64(L, 4);  // tiles must start on a 16-byte boundary
+      const int64_t tr = (tile_floats / L) / ar * ar;
+      if (tr >= 1) {
+        const int64_t n_full = R / tr, rem = R % tr;
+        const int64_t rows_tma = n_full * tr + (((rem * L) % 4 == 0) ? rem : 0);
+        if (rows_tma > 0) {
+          int rc = (L % 4 == 0)
+                       ? launch_tma_inst<OP, true>(a, b, out, rows_tma, L, is_signed, (int)tr, 0,
+                                                   tile_floats, st)
+                       : launch_tma_inst<OP, false>(a, b, out, rows_tma, L, is_signed, (int)tr, 0,
+                                                    tile_floats, st);
+          if (rc != TP_OK) return rc;
+        }
+        if (rows_tma < R)
+          return launch_ldg<OP>(a + rows_tma * L, two ? b + rows_tma * L : b, out + rows_tma,
+                                R - rows_tma, L, is_signed, st);
+        return TP_OK;
+      }
+    } else if (L % 4 == 0) {
+      return launch_tma_inst<OP, true>(a, b, out, R, L, is_signed, 1, 1, tile_floats, st);
+    }
+  }
+  return launch_ldg<OP>(a, b, out, R, L, is_signed, st);
+}
+
+}  // namespace tp
+
+extern "C" {
+
+int tp_taylor_reduce(const float* z, const float* g, int64_t B, int64_t C, int64_t HW,
+                     int is_signed, float* out, tp_stream_t stream) {
+  TP_REQUIRE(B >= 0 && C >= 0 && HW >= 0, TP_ERR_INVALID, "tp_taylor_reduce: negative dimension");
+  // a = g, b = z: the op computes -(a*b); multiplication commutes exactly.
+  return tp::launch_reduce<tp::OP_TAYLOR>(g, z, out, B * C, HW, is_signed, stream);
+}
+
+int tp_apoz_count(const float* z, int64_t B, int64_t C, int64_t HW, float* out,
+                  tp_stream_t stream) {
+  TP_REQUIRE(B >= 0 && C >= 0 && HW >= 0, TP_ERR_INVALID, "tp_apoz_count: negative dimension");
+  TP_REQUIRE(HW < (1 << 24), TP_ERR_LIMIT, "tp_apoz_count: HW must be < 2^24 for exact fp32");
+  return tp::launch_reduce<tp::OP_APOZ>(z, nullptr, out, B * C, HW, 0, stream);
+}
+
+int tp_abs_sum(const float* g, int64_t B, int64_t C, int64_t HW, float* out, tp_stream_t stream) {
+  TP_REQUIRE(B >= 0 && C >= 0 && HW >= 0, TP_ERR_INVALID, "tp_abs_sum: negative dimension");
+  return tp::launch_reduce<tp::OP_ABSSUM>(g, nullptr, out, B * C, HW, 0, stream);
+}
+
+int tp_weight_abs_sum(const float* w, int64_t Cout, int64_t K, float* out, tp_stream_t stream) {
+  TP_REQUIRE(Cout >= 0 && K >= 0, TP_ERR_INVALID, "tp_weight_abs_sum: negative dimension");
+  return tp::launch_reduce<tp::OP_ABSSUM>(w, nullptr, out, Cout, K, 0, stream);
+}
+
+}  // extern "C"
