@@ -1,0 +1,443 @@
+#!/usr/bin/env python
+"""Benchmark of the attribution-scoring hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (config 3 of BASELINE.json, the one the headline metric is quoted on): VGG16-BN for
+CIFAR-10 shaped inputs, one batch of 256 synthetic examples, layer-wise Monte-Carlo Shapley
+scoring of all 13 conv layers (evaluated after BN+ReLU, find_best_evaluation_module=True).
+
+One STEP = every GPU evaluates one full permutation (C prefix masks) for each of the 13 layers
+= 4224 channel-evals per GPU, through the product's own sharding path (sv_samples = N
+permutations split over N ranks) including the all-reduce of each layer's score table.  25 such
+steps are the sv_samples=25 job of the config on one GPU.  Scaling is therefore weak.
+
+Printed keys follow the driver's contract; see DESIGN.md "Measurement" for the definitions of
+`roofline`, `cpu_baseline`, `e2e` and `reductions`.
+"""
+import argparse
+import contextlib
+import io
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from torchpruner_b200 import workloads  # noqa: E402
+
+BATCH = 256
+METRIC = "shapley_channel_evals_per_s"
+UNIT = "channel-evals/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def workload_description(n_gpus):
+    return {
+        "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
+                    "BN+ReLU, one permutation per GPU per step = 4224 channel-evals/GPU/step "
+                    "(25 steps = the sv_samples=25 job); fp32 downstream layers, TF32 off",
+        "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224,
+        "sv_samples_per_step": n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
+        "l2": "working set per step (stacked masked activations, up to 1 GiB per chunk) far "
+              "exceeds the 126 MB L2; reduction kernels are timed with an L2 flush between "
+              "iterations",
+    }
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "200", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, cell in zip(self.NAMES, r[3:7]):
+                if cell.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- model / data
+def build_model(device):
+    model, shape = workloads.build("vgg16_cifar", seed=1)
+    model.to(device)
+    return model, shape
+
+
+def host_batch(shape, pin):
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((BATCH,) + tuple(shape), generator=g)
+    y = torch.randint(0, 10, (BATCH,), generator=g)
+    if pin:
+        x, y = x.pin_memory(), y.pin_memory()
+    return x, y
+
+
+class OneBatch:
+    """Minimal loader: an iterable of (x, y) with the `.dataset` length the Shapley metric
+    reads (reference shapley_values.py:34)."""
+
+    def __init__(self, x, y):
+        self.x, self.y = x, y
+        self.dataset = range(x.shape[0])
+
+    def __iter__(self):
+        yield self.x, self.y
+
+
+def quiet():
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+# --------------------------------------------------------------------------- product arm
+def flush_l2(buf):
+    buf.add_(1.0)
+
+
+def time_reductions(device, hbm_peak):
+    """Taylor / APoZ / Sensitivity kernels on the activation shapes of config 2 (VGG16, bs 256)
+    and the largest config-4 shape, in isolation: CUDA events around each launch, L2 flushed
+    between launches by writing a 512 MB buffer."""
+    from torchpruner_b200 import _lib
+
+    shapes = [(256, 64, 32, 32), (256, 64, 32, 32), (256, 128, 16, 16), (256, 128, 16, 16),
+              (256, 256, 8, 8), (256, 256, 8, 8), (256, 256, 8, 8), (256, 512, 4, 4),
+              (256, 512, 4, 4), (256, 512, 4, 4), (256, 512, 2, 2), (256, 512, 2, 2),
+              (256, 512, 2, 2)]
+    big = (256, 64, 112, 112)  # ResNet-50 stem output, 822 MB
+    flush = torch.empty(128 << 20, dtype=torch.float32, device=device)
+    stream = torch.cuda.current_stream(device)
+    out = {}
+
+    def run(fn, tensors, nbytes, iters):
+        ms = []
+        for _ in range(3):
+            fn(*tensors)
+        for _ in range(iters):
+            flush_l2(flush)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            fn(*tensors)
+            b.record(stream)
+            b.synchronize()
+            ms.append(a.elapsed_time(b))
+        t = statistics.median(ms)
+        return t, nbytes / t / 1e6
+
+    uniq = sorted(set(shapes), reverse=True)
+    per_shape = {}
+    for shp in uniq + [big]:
+        z = torch.relu(torch.randn(shp, device=device))
+        g = torch.randn(shp, device=device)
+        n, rows = z.numel(), shp[0] * shp[1]
+        res = {}
+        res["taylor"] = run(lambda a, b: _lib.taylor_reduce(a, b), (z, g), 8 * n + 4 * rows, 10)
+        res["apoz"] = run(lambda a: _lib.apoz_count(a), (z,), 4 * n + 4 * rows, 10)
+        res["sensitivity"] = run(lambda a: _lib.abs_sum(a), (g,), 4 * n + 4 * rows, 10)
+        per_shape[shp] = res
+        del z, g
+    for op in ("taylor", "apoz", "sensitivity"):
+        tot_ms = sum(per_shape[s][op][0] for s in shapes)
+        mult = 8 if op == "taylor" else 4
+        tot_bytes = sum(mult * np.prod(s) + 4 * s[0] * s[1] for s in shapes)
+        out[op] = {
+            "c2_sweep_gbs": float(tot_bytes / tot_ms / 1e6),
+            "c2_sweep_frac": float(tot_bytes / tot_ms / 1e6 / hbm_peak),
+            "c2_sweep_us": tot_ms * 1e3,
+            "c2_largest_layer_gbs": per_shape[(256, 64, 32, 32)][op][1],
+            "c2_largest_layer_frac": per_shape[(256, 64, 32, 32)][op][1] / hbm_peak,
+            "c4_largest_gbs": per_shape[big][op][1],
+            "c4_largest_frac": per_shape[big][op][1] / hbm_peak,
+            "per_shape_gbs": {"x".join(map(str, s)): round(per_shape[s][op][1], 1) for s in uniq},
+        }
+    del flush
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_product(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from torchpruner_b200 import _lib
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    device = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(device)
+    torch.backends.cudnn.allow_tf32 = False        # fp32-accurate downstream layers
+    torch.backends.cuda.matmul.allow_tf32 = False
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    hbm_peak, peak_src = peaks()
+
+    model, shape = build_model(device)
+    convs = model.conv_layers()
+    hx, hy = host_batch(shape, pin=True)
+    dx, dy = hx.to(device), hy.to(device)
+    evals_per_rank_step = sum(c.out_channels for c in convs)
+
+    def make_metric(loader):
+        m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, device,
+                                     sv_samples=world, reduction="none")
+        m.shard = world > 1
+        return m
+
+    def device_step(step):
+        np.random.seed(1000 + step)  # identical permutations on every rank
+        m = make_metric(OneBatch(dx, dy))
+        for conv in convs:
+            module = m.find_evaluation_module(conv, find_best_evaluation_module=True)
+            m._scores_on_device(module, world)
+
+    def e2e_step(step):
+        np.random.seed(1000 + step)
+        m = make_metric(OneBatch(hx, hy))
+        h2d = d2h = 0
+        for conv in convs:
+            sv = m.run(conv, find_best_evaluation_module=True)
+            h2d += hx.numel() * 4 + hy.numel() * 8
+            d2h += sv.nbytes
+        return h2d, d2h
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    with quiet():
+        for s in range(args.warmup):
+            device_step(s)
+        barrier()
+        prof = _lib.profile_begin(timed=True)
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local_rank) as clocks:
+            start.record(torch.cuda.current_stream(device))
+            for s in range(args.steps):
+                device_step(args.warmup + s)
+            stop.record(torch.cuda.current_stream(device))
+            barrier()
+        _lib.profile_end()
+        total_ms = start.elapsed_time(stop)
+        kernel_summary = prof.summary()
+
+        # end to end through the public API with host (pinned) inputs and host results
+        e2e_steps = max(1, min(args.steps, 3))
+        e2e_step(-1)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(e2e_steps):
+            h2d, d2h = e2e_step(args.warmup + s)
+        barrier()
+        e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, e2e_s = float(t[0]), float(t[1])
+    ms_per_step = total_ms / args.steps
+    value = world * evals_per_rank_step / (ms_per_step / 1e3)
+    e2e_value = world * evals_per_rank_step * e2e_steps / e2e_s
+
+    result = None
+    if rank == 0:
+        own_ms = {k: v["ms"] for k, v in kernel_summary.items()}
+        dominant = max(own_ms, key=own_ms.get)
+        dom = kernel_summary[dominant]
+        achieved = dom["bytes"] / dom["ms"] / 1e6 if dom["ms"] > 0 else 0.0
+        roofline = {
+            "kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+            "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+            "peak_source": peak_src, "launches": dom["launches"],
+            "avg_launch_ms": dom["ms"] / max(1, dom["launches"]),
+            "share_of_step": dom["ms"] / total_ms,
+            "note": "dominant hand-written kernel of the step; the rest of the step is the "
+                    "user model's downstream layers in fp32 cuDNN/cuBLAS (library code)",
+        }
+        own = {k: {"launches": v["launches"], "ms_per_step": v["ms"] / args.steps,
+                   "gbs": (v["bytes"] / v["ms"] / 1e6) if v["ms"] > 0 else None}
+               for k, v in kernel_summary.items()}
+        with quiet():
+            reductions = time_reductions(device, hbm_peak) if world == 1 else None
+        cpu = cpu_sample(steps=1, warmup=0) if world == 1 else None
+        result = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_description(world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                    "api": "ShapleyAttributionMetric.run(conv, find_best_evaluation_module=True) "
+                           "x13, pinned host batch in, numpy [256,C] float64 out"},
+            "gpu_launches": int(sum(v["launches"] for v in kernel_summary.values())),
+            "own_kernels": own,
+            "roofline": roofline,
+            "reductions": reductions,
+            "cpu_baseline": cpu,
+            "clocks": clocks.summary(),
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return result
+
+
+# --------------------------------------------------------------------------- CPU arm
+_CPU_STATE = {}
+
+
+def cpu_sample(steps, warmup, evals_per_layer=2):
+    """The reference's algorithm for the path (oracle port: the loop body of
+    shapley_values.py:55-61 on torch CPU ops) on this host's cores, on a bounded sample:
+    `evals_per_layer` prefix evaluations of one permutation for each of the 13 layers at bs 256.
+    Per-evaluation cost does not depend on the mask, so the whole-job rate is extrapolated as
+    sum_l n_l / sum_l (n_l * t_l) with n_l = 25*C_l evaluations."""
+    from oracle import tp_oracle as oracle
+
+    threads = torch.get_num_threads()
+    if "model" not in _CPU_STATE:
+        model, shape = workloads.build("vgg16_cifar", seed=1)
+        _CPU_STATE["model"] = model
+        _CPU_STATE["batch"] = host_batch(shape, pin=False)
+    model = _CPU_STATE["model"]
+    x, y = _CPU_STATE["batch"]
+    convs = model.conv_layers()
+    from torchpruner_b200.utils import find_best_module_for_attributions
+
+    with quiet():
+        modules = [find_best_module_for_attributions(model, c) for c in convs]
+    if "cached" not in _CPU_STATE:  # once per batch in the reference too (shapley_values.py:42-43)
+        with torch.no_grad():
+            cached = []
+            for module in modules:
+                z0 = model.forward_partial(x, to_module=module)
+                loss0 = workloads.cross_entropy(model.forward_partial(z0, from_module=module), y,
+                                                reduction="none")
+                cached.append((z0, loss0))
+        _CPU_STATE["cached"] = cached
+    rates = []
+    t_begin = time.perf_counter()
+    for it in range(warmup + steps):
+        t_layers = []
+        for conv, module, (z0, loss0) in zip(convs, modules, _CPU_STATE["cached"]):
+            perm = np.random.RandomState(it).permutation(conv.out_channels)
+            sv = np.zeros((BATCH, conv.out_channels))
+            t0 = time.perf_counter()
+            oracle.shapley_prefix_steps(model, z0, loss0, y, workloads.cross_entropy, module, perm,
+                                        evals_per_layer, sv, 25)
+            t_layers.append((time.perf_counter() - t0) / evals_per_layer)
+        if it >= warmup:
+            n = [25 * c.out_channels for c in convs]
+            rates.append(sum(n) / sum(ni * ti for ni, ti in zip(n, t_layers)))
+    wall = time.perf_counter() - t_begin
+    value = statistics.median(rates)
+    return {
+        "value": value, "unit": UNIT, "cores": threads, "host_cpus": os.cpu_count(), "kind": "port",
+        "sample": f"{evals_per_layer} prefix evaluations of one permutation per layer x 13 layers "
+                  f"at bs 256 per step ({steps} timed step(s), {wall:.1f} s of CPU work); "
+                  "whole-job rate extrapolated by per-layer evaluation counts (25*C_l); the "
+                  "once-per-batch forward to the evaluation module is outside the timed loop",
+        "seconds_per_step": wall / max(1, warmup + steps),
+    }
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    torch.backends.cudnn.allow_tf32 = False
+    cpu = cpu_sample(steps=args.steps, warmup=args.warmup)
+    value = cpu["value"]
+    return {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": cpu["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_description(world), "cpu_baseline": cpu,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        log(f"bench.py: --gpus {args.gpus} needs torchrun (one process per GPU); running 1 GPU")
+    if args.impl == "reference":
+        result = run_reference(args, rank, world)
+    else:
+        if args.warmup < 3:
+            log("bench.py: timing rules ask for >= 3 warm-up steps")
+        result = run_product(args, rank, world, local_rank)
+    if rank == 0 and result is not None:
+        sys.stdout.write(json.dumps(result) + "\n")
+        sys.stdout.flush()
+
+
+if __name__ == "__main__":
+    main()

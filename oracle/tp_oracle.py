@@ -175,6 +175,25 @@ def shapley_eval_losses(model, x, y, criterion, module, perm, k_positions):
     return out
 
 
+def shapley_prefix_steps(model, z0, loss0, y, criterion, module, perm, n_steps, sv, sv_samples,
+                          row0=0):
+    """The body of the reference's hot loop (shapley_values.py:52-61) for the first `n_steps`
+    prefix positions of one permutation: clone, then per step index_fill_ one more channel, run
+    the layers after `module`, per-example loss, delta, host-side `sv +=`.  This is what the CPU
+    baseline times (the cached activation z0 and loss0 are computed once per batch outside)."""
+    with torch.no_grad():
+        loss = loss0.detach().clone()
+        z = z0.clone().detach()
+        B = z.shape[0]
+        for i in perm[:n_steps]:
+            z.index_fill_(1, torch.tensor(np.array([i])).long(), 0.0)
+            new_loss = criterion(model.forward_partial(z, from_module=module), y, reduction="none")
+            delta = new_loss - loss
+            sv[row0:row0 + B, i] += (delta / sv_samples).squeeze().detach().cpu().numpy()
+            loss = new_loss
+    return sv
+
+
 def shapley_without_partial(model, batches, criterion, samples, module):
     """shapley_values.py:66-99, restated (whole-model forward per evaluation, masking hook)."""
     mask = []

@@ -1,0 +1,404 @@
+"""End-to-end parity of the drop-in Python API on a GPU: the reference's own unit tests restated
+against torchpruner_b200 (same fixtures, same expected values), golden vectors produced by the
+unmodified reference on the BASELINE configs, and the CPU oracle run side by side."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.utils.data import DataLoader, TensorDataset
+
+from oracle import tp_oracle as oracle
+from tests import cases
+from torchpruner_b200 import workloads
+from torchpruner_b200.attributions import (APoZAttributionMetric, RandomAttributionMetric,
+                                           SensitivityAttributionMetric, ShapleyAttributionMetric,
+                                           TaylorAttributionMetric, WeightNormAttributionMetric)
+from torchpruner_b200.pruner import Pruner
+from torchpruner_b200.utils import get_vgg_pruning_graph
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+DEV = torch.device("cuda:0")
+
+
+@pytest.fixture(autouse=True)
+def fp32_math():
+    """The reference's oracle is fp32 on the CPU; keep cuDNN/cuBLAS out of TF32."""
+    saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+def gold(name):
+    return np.load(os.path.join(GOLDEN, name))
+
+
+def norm_err(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    assert got.shape == want.shape
+    return np.abs(got - want).max() / max(np.abs(want).max(), 1e-30)
+
+
+def max_model_loader(version):
+    x, y, model = cases.max_model(version, device=DEV)
+    return DataLoader(TensorDataset(x, y), batch_size=1, shuffle=False), model
+
+
+# ------------------------------------------------------------------ reference unit tests, restated
+@pytest.mark.parametrize("cls,kw,version,expected", [
+    (WeightNormAttributionMetric, {}, 1, [1, 2, 2, 2]),
+    (APoZAttributionMetric, {}, 1, [0.5, 0.5, 1, 1]),
+    (SensitivityAttributionMetric, {}, 1, [0, 0, 0, 0]),
+    (TaylorAttributionMetric, {}, 1, [0, 0, 0, 0]),
+    (SensitivityAttributionMetric, {}, 2, [0.2, 0.1, 0.2, 0.04]),
+    (TaylorAttributionMetric, {}, 2, [0.1, 0.1, 0.5, 0.1]),
+    (TaylorAttributionMetric, {"signed": True}, 2, [0.1, 0.1, 0.5, -0.1]),
+])
+def test_known_answers(cls, kw, version, expected):
+    """torchpruner/tests/test_attributions.py:84-175."""
+    loader, model = max_model_loader(version)
+    attr = cls(model, loader, F.mse_loss, DEV, **kw).run(list(model.children())[0])
+    assert list(attr.shape) == [4] and attr.dtype == np.float32
+    np.testing.assert_array_almost_equal(attr, expected)
+    key = {WeightNormAttributionMetric: "weight_norm", APoZAttributionMetric: "apoz",
+           SensitivityAttributionMetric: "sensitivity", TaylorAttributionMetric: "taylor"}[cls]
+    if kw.get("signed"):
+        key = "taylor_signed"
+    for best in (False, True):
+        got = cls(model, loader, F.mse_loss, DEV, **kw).run(list(model.children())[0],
+                                                           find_best_evaluation_module=best)
+        np.testing.assert_allclose(got, gold("max_model.npz")[f"v{version}/best{int(best)}/{key}"],
+                                   rtol=1e-6, atol=1e-7)
+
+
+def test_sv_known_answer_and_random():
+    """test_attributions.py:74-82 and :128-137 (Shapley pinned to one decimal, unseeded there)."""
+    loader, model = max_model_loader(1)
+    np.random.seed(0)
+    a = ShapleyAttributionMetric(model, loader, F.mse_loss, DEV, sv_samples=300)
+    attr = a.run(list(model.children())[0])
+    assert list(attr.shape) == [4] and attr.dtype == np.float64
+    np.testing.assert_array_almost_equal(attr, [0.37, 0.37, 1.7, 0.], decimal=1)
+    r = RandomAttributionMetric(model, loader, F.mse_loss, DEV).run(list(model.children())[0])
+    assert list(r.shape) == [4]
+
+
+@pytest.mark.parametrize("version", [1, 2])
+@pytest.mark.parametrize("best", [False, True])
+def test_shapley_slow_path_matches_reference_run(version, best):
+    """Same seed, same permutations, same per-example table as the reference's run_module()."""
+    loader, model = max_model_loader(version)
+    np.random.seed(7)
+    a = ShapleyAttributionMetric(model, loader, F.mse_loss, DEV, sv_samples=20, reduction="none")
+    got = a.run(list(model.children())[0], find_best_evaluation_module=best)
+    want = gold("max_model.npz")[f"v{version}/best{int(best)}/shapley_slow"]
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got, want, rtol=0, atol=2e-7)
+
+
+def test_all_metrics_run_with_best_module():
+    """test_attributions.py:203-229."""
+    loader, model = max_model_loader(1)
+    layer = list(model.children())[0]
+    for A in (TaylorAttributionMetric, SensitivityAttributionMetric, APoZAttributionMetric,
+              WeightNormAttributionMetric):
+        a = A(model, loader, F.mse_loss, DEV)
+        np.testing.assert_array_almost_equal(a.run(layer, find_best_evaluation_module=False),
+                                             a.run(layer, find_best_evaluation_module=True))
+    for A in (RandomAttributionMetric, ShapleyAttributionMetric):
+        assert list(A(model, loader, F.mse_loss, DEV).run(layer, find_best_evaluation_module=True).shape) == [4]
+
+
+def test_reductions_and_row_order():
+    model, shape = workloads.build("small_cnn")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=96, batch_size=40)  # ragged last batch (16)
+    layer = model.features[3]
+    table = APoZAttributionMetric(model, loader, workloads.cross_entropy, DEV, reduction="none").run(layer)
+    assert table.shape == (96, 64)
+    for red, fn in (("mean", lambda t: t.mean(0)), ("sum", lambda t: t.sum(0)),
+                    (lambda t: t.max(0), lambda t: t.max(0))):
+        got = APoZAttributionMetric(model, loader, workloads.cross_entropy, DEV, reduction=red).run(layer)
+        np.testing.assert_array_equal(got, fn(table))
+    # rows follow the loader order: recompute batch 2 alone on the CPU oracle
+    x, _ = list(loader)[2]
+    with torch.no_grad():
+        z = model.forward_partial(x.to(DEV), to_module=layer)
+    np.testing.assert_array_equal(table[80:], oracle.apoz_rows(z.cpu()))
+
+
+# ------------------------------------------------------------------ config 1: small CNN vs reference
+def test_small_cnn_matches_reference():
+    g = gold("small_cnn.npz")
+    model, shape = workloads.build("small_cnn")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=128, batch_size=64)
+    mk = lambda cls, **kw: cls(model, loader, workloads.cross_entropy, DEV, **kw)
+    report = {}
+    for name, layer in (("conv1", model.features[0]), ("conv2", model.features[3])):
+        for best in (False, True):
+            tag = f"{name}/best{int(best)}"
+            t = mk(TaylorAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=best)
+            model.zero_grad()
+            s = mk(SensitivityAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=best)
+            model.zero_grad()
+            a = mk(APoZAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=best)
+            report[tag] = (norm_err(t, g[f"{tag}/taylor"]), norm_err(s, g[f"{tag}/sensitivity"]),
+                           float((a != g[f"{tag}/apoz"]).mean()))
+            # Tier B: the forward/backward itself runs on different hardware (cuDNN vs oneDNN),
+            # so activations differ by fp32 rounding before our kernels see them.
+            assert report[tag][0] <= 1e-4 and report[tag][1] <= 1e-4, report
+            # a rounding difference can flip `z > 0` at the threshold for a handful of pixels
+            assert np.abs(a - g[f"{tag}/apoz"]).max() <= 2 and report[tag][2] <= 1e-3, report
+        np.testing.assert_allclose(mk(WeightNormAttributionMetric).run(layer), g[f"{name}/weight_norm"], rtol=1e-5)
+        np.random.seed(11)
+        sv = mk(ShapleyAttributionMetric, sv_samples=5, reduction="none").run(layer, find_best_evaluation_module=True)
+        assert sv.dtype == np.float64 and sv.shape == g[f"{name}/shapley"].shape
+        # scores are sums of loss differences: compare on the loss scale (|loss| ~ 2.3)
+        assert np.abs(sv - g[f"{name}/shapley"]).max() <= 5e-6, np.abs(sv - g[f"{name}/shapley"]).max()
+        assert norm_err(sv.mean(0), g[f"{name}/shapley"].mean(0)) <= 2e-3
+    np.testing.assert_allclose(mk(WeightNormAttributionMetric).run(model.classifier[0]),
+                               g["fc1/weight_norm"], rtol=1e-5)
+
+
+# ------------------------------------------------------------------ configs 2/3: VGG16 vs reference
+def test_vgg16_scores_match_reference():
+    g = gold("vgg16.npz")
+    model, shape = workloads.build("vgg16_cifar")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=256, batch_size=256)
+    names = {m: n for n, m in model.named_modules()}
+    mk = lambda cls, **kw: cls(model, loader, workloads.cross_entropy, DEV, **kw)
+    worst = {"taylor": 0.0, "sensitivity": 0.0, "apoz": 0.0}
+    for layer in model.conv_layers():
+        tag = names[layer]
+        t = mk(TaylorAttributionMetric).run(layer, find_best_evaluation_module=True)
+        model.zero_grad()
+        s = mk(SensitivityAttributionMetric).run(layer, find_best_evaluation_module=True)
+        model.zero_grad()
+        a = mk(APoZAttributionMetric).run(layer, find_best_evaluation_module=True)
+        worst["taylor"] = max(worst["taylor"], norm_err(t, g[f"{tag}/taylor"]))
+        worst["sensitivity"] = max(worst["sensitivity"], norm_err(s, g[f"{tag}/sensitivity"]))
+        worst["apoz"] = max(worst["apoz"], norm_err(a, g[f"{tag}/apoz"]))
+        np.testing.assert_allclose(mk(WeightNormAttributionMetric).run(layer), g[f"{tag}/weight_norm"], rtol=1e-5)
+    print("VGG16 tier-B worst normalised errors vs reference-CPU:", worst)
+    # 13 conv+BN layers of fp32 forward/backward on different hardware sit between the input and
+    # these scores; the kernels themselves are held to 1e-5 in test_gpu_kernels.py.
+    assert worst["taylor"] <= 2e-3 and worst["sensitivity"] <= 2e-3 and worst["apoz"] <= 2e-3, worst
+
+
+@pytest.mark.parametrize("tag", ["features.0", "features.24", "features.40"])
+def test_vgg16_shapley_matches_reference(tag):
+    g = gold("vgg16.npz")
+    model, shape = workloads.build("vgg16_cifar")
+    model.to(DEV)
+    small = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+    layer = dict(model.named_modules())[tag]
+    np.random.seed(3)
+    m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, DEV, sv_samples=1, reduction="none")
+    sv = m.run(layer, find_best_evaluation_module=True)
+    want = g[f"{tag}/shapley16"]
+    assert sv.shape == want.shape
+    # per-evaluation losses agree to ~1e-6 relative; scores are differences of |loss| ~ 2.3
+    assert np.abs(sv - want).max() <= 3e-5, np.abs(sv - want).max()
+    assert m.last_run_info["stacked"] is True
+
+
+def test_shapley_schedules_agree():
+    """Stacked evaluation, one-mask-at-a-time evaluation (train-mode fallback), any stack size and
+    any rank split produce the same table up to fp32 rounding of the batched layers."""
+    model, shape = workloads.build("small_cnn")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=24, batch_size=12, seed=4)
+    layer = model.features[3]
+
+    def run(**attrs):
+        np.random.seed(9)
+        m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=3, reduction="none")
+        for k, v in attrs.items():
+            setattr(m, k, v)
+        return m.run(layer, find_best_evaluation_module=True), m
+
+    base, m = run()
+    assert m.last_run_info["evaluations"] == 2 * 3 * 64
+    for attrs in ({"max_stack": 1}, {"max_stack": 7}, {"max_stack_bytes": 1}):
+        other, _ = run(**attrs)
+        assert np.abs(other - base).max() <= 2e-6
+
+    # generic-criterion path (not recognised as cross entropy) against the fused one
+    def odd_loss(output, target, reduction="mean"):
+        return F.cross_entropy(output, target, reduction=reduction) * 1.5
+    np.random.seed(9)
+    scaled = ShapleyAttributionMetric(model, loader, odd_loss, DEV, sv_samples=3, reduction="none").run(
+        layer, find_best_evaluation_module=True)
+    assert np.abs(scaled / 1.5 - base).max() <= 2e-6
+
+    # emulate a 3-rank job on one GPU: each "rank" computes its spans, tables are summed
+    from torchpruner_b200.attributions.methods import shapley_values as sh
+    total = np.zeros_like(base)
+    evals = 0
+    for rank in range(3):
+        np.random.seed(9)
+        mm = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=3, reduction="none")
+        mm._dist = lambda rank=rank: (None, 3, rank)
+        saved = sh.allreduce_scores
+        sh.allreduce_scores = lambda sv, group=None: sv
+        try:
+            total += mm.run(layer, find_best_evaluation_module=True)
+        finally:
+            sh.allreduce_scores = saved
+        evals += mm.last_run_info["evaluations"]
+    assert np.abs(total - base).max() <= 2e-6
+    assert evals == 2 * (3 * 64 + 2)  # one halo evaluation for each of the two interior cuts
+
+
+def test_shapley_train_mode_falls_back_to_sequential():
+    net, shape = workloads.build("vgg16_cifar")
+    net.to(DEV)
+    net.classifier[0].train()  # a Dropout in train mode: stacking masks is no longer legal
+    loader = workloads.synthetic_batches(shape, n=4, batch_size=4)
+    m = ShapleyAttributionMetric(net, loader, workloads.cross_entropy, DEV, sv_samples=1)
+    np.random.seed(0)
+    out = m.run(net.features[40], find_best_evaluation_module=True)
+    assert out.shape == (512,) and m.last_run_info["stacked"] is False
+
+
+# ------------------------------------------------------------------ pruner: reference tests restated
+def simple_model():
+    x, y = torch.ones((10, 3)), torch.randint(0, 10, (10, 1))
+    return (x.to(DEV), y.to(DEV)), nn.Sequential(nn.Linear(3, 2), nn.ReLU(), nn.Linear(2, 1)).to(DEV)
+
+
+def test_prune_parameter_and_module():
+    """torchpruner/tests/test_pruner.py:38-70, plus the values (the reference checks shapes only)."""
+    (x, y), model = simple_model()
+    p = Pruner(model, input_size=(3,), device=DEV)
+    module = list(model.children())[0]
+    w0, b0 = module.weight.detach().clone(), module.bias.detach().clone()
+    weight_id = id(module.weight)
+    p.prune_parameter(module, "weight", [0], axis=0)
+    p.prune_parameter(module, "bias", [0], axis=0)
+    assert list(module.weight.shape) == [1, 3] and list(module.bias.shape) == [1]
+    assert id(module.weight) == weight_id
+    assert torch.equal(module.weight.data, w0[1:]) and torch.equal(module.bias.data, b0[1:])
+    p.prune_parameter(module, "weight", [0], axis=1)
+    assert list(module.weight.shape) == [1, 2] and torch.equal(module.weight.data, w0[1:, 1:])
+    assert module.weight.is_contiguous()
+
+    (x, y), model = simple_model()
+    p = Pruner(model, input_size=(3,), device=DEV)
+    module = list(model.children())[0]
+    p.prune_module(module, [0], direction="out")
+    assert list(module.weight.shape) == [1, 3]
+    p.prune_module(module, [0], direction="in")
+    assert list(module.weight.shape) == [1, 2]
+    # index flavours the reference accepts: unsorted, duplicated, negative, ndarray, tensor
+    lin = nn.Linear(4, 6).to(DEV)
+    w = lin.weight.detach().clone()
+    Pruner(lin, (4,), DEV).prune_parameter(lin, "weight", np.array([5, 2, 2]), axis=0)
+    assert torch.equal(lin.weight.data, w[[0, 1, 3, 4]])
+    Pruner(lin, (4,), DEV).prune_parameter(lin, "weight", torch.tensor([-1]), axis=1)
+    assert torch.equal(lin.weight.data, w[[0, 1, 3, 4]][:, :3])
+
+
+def test_nan_trick_index_discovery():
+    """test_pruner.py:72-121."""
+    def probe(model, input_size, poisoned, listeners):
+        p = Pruner(model, input_size=input_size, device=DEV)
+        kids = list(model.children())
+        kids[0].register_forward_hook(p._nanify_hook(poisoned))
+        for i in listeners:
+            kids[i].register_forward_hook(p._detect_nan_hook())
+        p._run_forward()
+        return [list(getattr(kids[i], "_nan_indices")) for i in listeners], kids
+
+    got, _ = probe(nn.Sequential(nn.Linear(3, 2), nn.ReLU(), nn.Linear(2, 1)).to(DEV), (3,), [0], [2])
+    assert got == [[0]]
+    got, _ = probe(nn.Sequential(nn.Conv2d(1, 3, 2), nn.ReLU(), nn.Flatten(), nn.Linear(12, 1)).to(DEV),
+                   (1, 3, 3), [0], [3])
+    assert got == [[0, 1, 2, 3]]
+    got, _ = probe(nn.Sequential(nn.Conv2d(1, 3, 2), nn.ReLU(), nn.MaxPool2d(2), nn.Flatten(),
+                                 nn.Linear(3, 1)).to(DEV), (1, 3, 3), [0], [4])
+    assert got == [[0]]
+    got, kids = probe(nn.Sequential(nn.Linear(3, 2), nn.BatchNorm1d(2), nn.Linear(2, 1)).to(DEV), (3,), [0], [1, 2])
+    assert got == [[0], [0]] and kids[1]._activation_len == 2.0
+    with pytest.raises(RuntimeError):  # the reference rejects non-int64 index arrays here too
+        probe(nn.Sequential(nn.Linear(3, 2), nn.Linear(2, 1)).to(DEV), (3,), np.array([0], np.int32), [1])
+
+
+def test_prune_model_cascades():
+    """test_pruner.py:124-176."""
+    (x, y), model = simple_model()
+    Pruner(model, (3,), DEV).prune_model(model[0], [0], cascading_modules=[model[2]])
+    assert list(model[0].weight.shape) == [1, 3] and list(model[2].weight.shape) == [1, 1]
+    assert list(model(x).shape) == list(y.shape)
+
+    model = nn.Sequential(nn.Linear(3, 2), nn.BatchNorm1d(2), nn.Linear(2, 1)).to(DEV)
+    Pruner(model, (3,), DEV).prune_model(model[0], [0], [model[1], model[2]])
+    assert list(model[0].weight.shape) == [1, 3] and list(model[2].weight.shape) == [1, 1]
+    for name in ("weight", "bias", "running_var", "running_mean"):
+        assert list(getattr(model[1], name).shape) == [1]
+    assert list(model(x).shape) == list(y.shape)
+
+    model = nn.Sequential(nn.Linear(3, 5), nn.Dropout(0.5), nn.Linear(5, 1)).to(DEV)
+    Pruner(model, (3,), DEV).prune_model(model[0], [0], [model[1], model[2]])
+    assert model[1].p == 0.5 * 4 / 5
+    assert not hasattr(model[2], "_nan_indices")
+
+
+@pytest.mark.parametrize("momentum", [0.0, 0.01])
+def test_training_step_after_pruning(momentum):
+    """test_pruner.py:180-228 (the momentum case raises KeyError in the reference on torch>=1.6)."""
+    (x, y), _ = simple_model()
+    model = nn.Sequential(nn.Linear(3, 2), nn.BatchNorm1d(2), nn.Linear(2, 1)).to(DEV)
+    opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=momentum)
+    p = Pruner(model, (3,), DEV, optimizer=opt if momentum else None)
+
+    def step():
+        model(x).mean().backward()
+        opt.step()
+
+    step()
+    p.prune_model(model[0], [0], [model[1], model[2]])
+    step()
+    if momentum:
+        assert list(opt.state[model[0].weight]["momentum_buffer"].shape) == [1, 3]
+        assert list(model[0].weight.grad.shape) == [1, 3]
+
+
+# ------------------------------------------------------------------ config 5 / 1: bit-exact cascade
+@pytest.mark.parametrize("cfg", ["small_cnn", "vgg16_cifar"])
+def test_cascading_prune_is_bit_exact(cfg, capsys):
+    with open(os.path.join(GOLDEN, "prune.txt")) as f:
+        want = [line[len(cfg) + 1:].rstrip("\n") for line in f if line.startswith(cfg + " ")]
+    model, shape, opt = cases.prune_setup(cfg, device=DEV)
+    cpu_model, _, cpu_opt = cases.prune_setup(cfg, device="cpu")
+    pruner = Pruner(model, shape, DEV, optimizer=opt)
+    check = oracle.OraclePruner(cpu_model, shape, optimizer=cpu_opt)
+    graph = get_vgg_pruning_graph(model) if cfg == "vgg16_cifar" else model.get_pruning_graph()
+    cpu_graph = get_vgg_pruning_graph(cpu_model) if cfg == "vgg16_cifar" else cpu_model.get_pruning_graph()
+    # Unit choices and the probe batches both come from the global numpy RNG, interleaved exactly
+    # as in the golden run: identical digests therefore also prove identical RNG consumption.
+    np.random.seed(21)
+    for module, cascade in graph:
+        pruner.prune_model(module, cases.prune_choice(module.weight.shape[0]), cascading_modules=cascade)
+    rng_after_product = np.random.get_state()[1][:8].copy()
+    np.random.seed(21)
+    for module, cascade in cpu_graph:
+        check.prune_model(module, cases.prune_choice(module.weight.shape[0]), cascade)
+    assert (np.random.get_state()[1][:8] == rng_after_product).all(), "numpy RNG consumed differently"
+    got = cases.model_digest(model, opt)
+    assert got == cases.model_digest(cpu_model, cpu_opt), "differs from the CPU oracle"
+    assert got == want, "differs from the digests of the unmodified reference"
+    printed = capsys.readouterr().out
+    assert "Pruning" in printed and "(out)" in printed and "(in)" in printed
+    # the pruned model still trains
+    x = torch.randn((4,) + tuple(shape), device=DEV)
+    model.train()
+    model(x).sum().backward()
+    opt.step()

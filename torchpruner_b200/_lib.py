@@ -96,6 +96,67 @@ def _stream(t):
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
+class LaunchProfile:
+    """Optional per-kernel accounting used by bench.py: while active, every C-ABI call is
+    bracketed by CUDA events on the stream it is launched on and its algorithmic bytes are
+    recorded.  Inactive (the default) it costs one attribute test per call."""
+
+    def __init__(self):
+        self.records = {}   # name -> [launches, bytes, [(start_event, stop_event), ...]]
+        self.timed = True
+
+    def summary(self):
+        """{name: {"launches", "bytes", "ms"}}; synchronises the device."""
+        torch.cuda.synchronize()
+        out = {}
+        for name, (n, nbytes, pairs) in self.records.items():
+            ms = sum(a.elapsed_time(b) for a, b in pairs)
+            out[name] = {"launches": n, "bytes": nbytes, "ms": ms}
+        return out
+
+
+_profile = None
+
+
+def profile_begin(timed=True):
+    global _profile
+    _profile = LaunchProfile()
+    _profile.timed = timed
+    return _profile
+
+
+def profile_end():
+    global _profile
+    p, _profile = _profile, None
+    return p
+
+
+class _launch:
+    """with _launch(name, algorithmic_bytes, tensor, kernels): <C-ABI call>"""
+
+    __slots__ = ("name", "nbytes", "t", "kernels", "ev")
+
+    def __init__(self, name, nbytes, t, kernels=1):
+        self.name, self.nbytes, self.t, self.kernels = name, nbytes, t, kernels
+
+    def __enter__(self):
+        self.ev = None
+        if _profile is not None and _profile.timed:
+            self.ev = torch.cuda.Event(enable_timing=True)
+            self.ev.record(torch.cuda.current_stream(self.t.device))
+
+    def __exit__(self, et, ev, tb):
+        if _profile is not None and et is None:
+            rec = _profile.records.setdefault(self.name, [0, 0, []])
+            rec[0] += self.kernels
+            rec[1] += int(self.nbytes)
+            if self.ev is not None:
+                stop = torch.cuda.Event(enable_timing=True)
+                stop.record(torch.cuda.current_stream(self.t.device))
+                rec[2].append((self.ev, stop))
+        return False
+
+
 def _cuda_f32(t, name):
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise TorchPrunerB200Error(
@@ -134,7 +195,7 @@ def taylor_reduce(z, g, signed=False, out=None):
     B, C, hw = _bchw(z)
     if out is None:
         out = torch.empty((B, C), dtype=torch.float32, device=z.device)
-    with torch.cuda.device(z.device):
+    with torch.cuda.device(z.device), _launch("taylor_reduce", 8 * z.numel() + 4 * B * C, z, 1):
         _check(load().tp_taylor_reduce(z.data_ptr(), g.data_ptr(), B, C, hw, int(bool(signed)),
                                        out.data_ptr(), _stream(z)), "tp_taylor_reduce")
     return out
@@ -145,7 +206,7 @@ def apoz_count(z, out=None):
     B, C, hw = _bchw(z)
     if out is None:
         out = torch.empty((B, C), dtype=torch.float32, device=z.device)
-    with torch.cuda.device(z.device):
+    with torch.cuda.device(z.device), _launch("apoz_count", 4 * z.numel() + 4 * B * C, z, 1):
         _check(load().tp_apoz_count(z.data_ptr(), B, C, hw, out.data_ptr(), _stream(z)),
                "tp_apoz_count")
     return out
@@ -156,7 +217,7 @@ def abs_sum(g, out=None):
     B, C, hw = _bchw(g)
     if out is None:
         out = torch.empty((B, C), dtype=torch.float32, device=g.device)
-    with torch.cuda.device(g.device):
+    with torch.cuda.device(g.device), _launch("abs_sum", 4 * g.numel() + 4 * B * C, g, 1):
         _check(load().tp_abs_sum(g.data_ptr(), B, C, hw, out.data_ptr(), _stream(g)), "tp_abs_sum")
     return out
 
@@ -166,7 +227,7 @@ def weight_abs_sum(w):
     cout = w.shape[0]
     k = w.numel() // cout if cout else 0
     out = torch.empty((cout,), dtype=torch.float32, device=w.device)
-    with torch.cuda.device(w.device):
+    with torch.cuda.device(w.device), _launch("weight_abs_sum", 4 * w.numel() + 4 * cout, w, 1):
         _check(load().tp_weight_abs_sum(w.data_ptr(), cout, k, out.data_ptr(), _stream(w)),
                "tp_weight_abs_sum")
     return out
@@ -183,7 +244,7 @@ def prefix_mask_stack(z, inv_perm, k0, P, out=None):
         out = torch.empty((P * B,) + tuple(z.shape[1:]), dtype=torch.float32, device=z.device)
     elif out.numel() < P * z.numel() or not out.is_contiguous():
         raise TorchPrunerB200Error("prefix_mask_stack: `out` is too small or not contiguous")
-    with torch.cuda.device(z.device):
+    with torch.cuda.device(z.device), _launch("prefix_mask_stack", 4 * z.numel() * (int(P) + 1), z, 1):
         _check(load().tp_prefix_mask_stack(z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C,
                                            hw, out.data_ptr(), _stream(z)), "tp_prefix_mask_stack")
     return out
@@ -197,7 +258,7 @@ def index_fill_dim1_(x, idx, value_bits):
     if idx.dtype != torch.int64 or not idx.is_cuda:
         raise TorchPrunerB200Error("index_fill_dim1_: idx must be a CUDA int64 tensor")
     B, C, inner = _bchw(x)
-    with torch.cuda.device(x.device):
+    with torch.cuda.device(x.device), _launch("index_fill_dim1", 4 * B * idx.numel() * inner, x, 1):
         _check(load().tp_index_fill_dim1(x.data_ptr(), B, C, inner, idx.data_ptr(), idx.numel(),
                                          int(value_bits), _stream(x)), "tp_index_fill_dim1")
     return x
@@ -219,7 +280,7 @@ def loss_delta_scatter(src, target, kind, prev_in, prev_out, perm, k0, P, B, K, 
         if target.dtype != torch.int64 or not target.is_cuda or target.numel() != B:
             raise TorchPrunerB200Error("cross-entropy targets must be a CUDA int64 [B] tensor")
         tptr = target.data_ptr()
-    with torch.cuda.device(src.device):
+    with torch.cuda.device(src.device), _launch("loss_delta_scatter", 4 * src.numel() + 24 * int(P) * int(B), src, 1):
         _check(load().tp_loss_delta_scatter(
             src.data_ptr(), tptr, int(kind), prev_in.data_ptr(), prev_out.data_ptr(),
             perm.data_ptr(), int(k0), int(P), int(B), int(K), float(sv_samples), sv.data_ptr(),
@@ -235,7 +296,9 @@ def multi_gather(descs, keep, device):
     if n == 0:
         return
     arr = (GatherDesc * n)(*descs)
-    with torch.cuda.device(device):
+    nbytes = 2 * sum(d.outer * d.n_keep * d.inner_bytes for d in descs) + 8 * keep.numel()
+    launches = (n + TP_GATHER_MAX_DESCS - 1) // TP_GATHER_MAX_DESCS
+    with torch.cuda.device(device), _launch("multi_gather", nbytes, keep, launches):
         _check(load().tp_multi_gather(arr, n, keep.data_ptr(), keep.numel(),
                                       torch.cuda.current_stream(device).cuda_stream),
                "tp_multi_gather")
@@ -247,7 +310,7 @@ def nan_any_dim1(x, flags, out_idx, out_count):
     B, C, inner = _bchw(x)
     if flags.numel() < C or out_idx.numel() < C:
         raise TorchPrunerB200Error("nan_any_dim1: work buffers smaller than the channel count")
-    with torch.cuda.device(x.device):
+    with torch.cuda.device(x.device), _launch("nan_any_dim1", 4 * x.numel(), x, 2):
         _check(load().tp_nan_any_dim1(x.data_ptr(), B, C, inner, flags.data_ptr(),
                                       out_idx.data_ptr(), out_count.data_ptr(), _stream(x)),
                "tp_nan_any_dim1")

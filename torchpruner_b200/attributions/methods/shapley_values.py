@@ -135,6 +135,13 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
     def run_module_with_partial(self, module, sv_samples):
         """Shapley sampling for models that provide ``forward_partial``
         (shapley_values.py:28-64)."""
+        sv = self._scores_on_device(module, sv_samples)
+        if sv is None:  # empty loader: the reference would hand None to numpy as well
+            return self.aggregate_over_samples(None)
+        return self.aggregate_over_samples(sv.cpu().numpy())
+
+    def _scores_on_device(self, module, sv_samples):
+        """The [d, C] float64 score table, left on the GPU (all-reduced when sharded)."""
         d = len(self.data_gen.dataset)
         group, world, rank = self._dist()
         sv = None
@@ -212,13 +219,13 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 self.restore_deterministic()
                 row += B
 
-            if sv is None:  # empty loader: the reference would hand None to numpy
-                return self.aggregate_over_samples(None)
+            if sv is None:
+                return None
             if world > 1:
                 allreduce_scores(sv, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe}
-            return self.aggregate_over_samples(sv.cpu().numpy())
+            return sv
 
     # ------------------------------------------------------------------ slow path
     def run_module(self, module, samples):
