@@ -281,13 +281,16 @@ def run_product(args, rank, world, local_rank):
 
         # end to end through the public API with host (pinned) inputs and host results
         e2e_steps = max(1, min(args.steps, 3))
-        e2e_step(-1)
-        barrier()
-        t0 = time.perf_counter()
-        for s in range(e2e_steps):
-            h2d, d2h = e2e_step(args.warmup + s)
-        barrier()
-        e2e_s = time.perf_counter() - t0
+        h2d = d2h = 0
+        e2e_s = float("nan")
+        if not args.core_only:
+            e2e_step(-1)
+            barrier()
+            t0 = time.perf_counter()
+            for s in range(e2e_steps):
+                h2d, d2h = e2e_step(args.warmup + s)
+            barrier()
+            e2e_s = time.perf_counter() - t0
 
     t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device=device)
     if world > 1:
@@ -316,8 +319,8 @@ def run_product(args, rank, world, local_rank):
                    "gbs": (v["bytes"] / v["ms"] / 1e6) if v["ms"] > 0 else None}
                for k, v in kernel_summary.items()}
         with quiet():
-            reductions = time_reductions(device, hbm_peak) if world == 1 else None
-        cpu = cpu_sample(steps=1, warmup=0) if world == 1 else None
+            reductions = time_reductions(device, hbm_peak) if (world == 1 and not args.core_only) else None
+        cpu = cpu_sample(steps=1, warmup=0) if (world == 1 and not args.core_only) else None
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -422,6 +425,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    ap.add_argument("--core-only", action="store_true",
+                    help="timed Shapley steps only (no e2e / reductions / CPU legs); for ncu runs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -238,14 +238,14 @@ def test_shapley_schedules_agree():
         layer, find_best_evaluation_module=True)
     assert np.abs(scaled / 1.5 - base).max() <= 2e-6
 
-    # emulate a 3-rank job on one GPU: each "rank" computes its spans, tables are summed
+    # emulate a 4-rank job on one GPU: each "rank" computes its spans, tables are summed
     from torchpruner_b200.attributions.methods import shapley_values as sh
     total = np.zeros_like(base)
     evals = 0
-    for rank in range(3):
+    for rank in range(4):
         np.random.seed(9)
         mm = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=3, reduction="none")
-        mm._dist = lambda rank=rank: (None, 3, rank)
+        mm._dist = lambda rank=rank: (None, 4, rank)
         saved = sh.allreduce_scores
         sh.allreduce_scores = lambda sv, group=None: sv
         try:
@@ -254,7 +254,8 @@ def test_shapley_schedules_agree():
             sh.allreduce_scores = saved
         evals += mm.last_run_info["evaluations"]
     assert np.abs(total - base).max() <= 2e-6
-    assert evals == 2 * (3 * 64 + 2)  # one halo evaluation for each of the two interior cuts
+    # 192 items / 4 ranks: cuts at 48, 96, 144 fall inside permutations -> 3 halo evaluations
+    assert evals == 2 * (3 * 64 + 3)
 
 
 def test_shapley_train_mode_falls_back_to_sequential():

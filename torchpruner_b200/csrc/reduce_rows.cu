@@ -399,8 +399,10 @@ static int launch_tma_inst(const float* a, const float* b, float* out, int64_t R
                            cudaStream_t st) {
   const Tuning& t = tuning();
   constexpr int kStreams = RowOpTraits<OP>::kStreams;
-  const int ctas = t.reduce_ctas_per_sm;
+  int ctas = t.reduce_ctas_per_sm;
   const size_t per_stage = (size_t)kStreams * tile_floats * 4;
+  // Fewer resident CTAs rather than a ring shallower than two stages.
+  while (ctas > 1 && ((size_t)(220 * 1024) / ctas - 256) < 2 * per_stage) --ctas;
   const size_t budget = (size_t)(220 * 1024) / ctas - 256;
   int stages = t.reduce_stages;
   if ((size_t)stages * per_stage > budget) stages = (int)(budget / per_stage);
