@@ -137,6 +137,36 @@ int tp_nan_any_dim1(const float* x, int64_t B, int64_t C, int64_t inner,
                     int32_t* flags_scratch, int64_t* out_idx, int64_t* out_count,
                     tp_stream_t stream);
 
+/* ---------------------------------------------------------------- no-allocation variant
+ * No counterpart in the reference: this entry point exists for callers of THIS library that
+ * cannot allocate device memory around the call.  Typical cases: a forward hook that runs in the
+ * middle of somebody else's model, where a cudaMalloc/cudaFree pair would synchronise the whole
+ * device and stall every other stream; a process whose GPU memory has been handed in full to a
+ * framework's pool, so a raw cudaMalloc fails; embedded or real-time hosts whose policy forbids
+ * allocation after start-up.  tp_nan_any_dim1 makes such a caller bring a [C] int32 work area;
+ * this variant needs none.
+ *
+ * Same result as tp_nan_any_dim1 (ascending channel list in out_idx, its length in out_count),
+ * but the per-channel flag words live in a file-scope `static __device__` array inside the
+ * library instead of caller memory.  The caller still provides x, out_idx ([C] int64) and
+ * out_count ([1] int64), all on the device.  The call performs no cudaMalloc, no cudaFree and no
+ * other allocating routine.
+ *
+ * Limits and rules:
+ *  - C <= TP_NAN_STATIC_MAX_C (65536 channels, 256 KiB of device memory held by every GPU that
+ *    loads the library, until the process exits).  Larger C returns TP_ERR_LIMIT and touches
+ *    nothing.
+ *  - The first call on each device resolves the array's device address (cudaGetSymbolAddress,
+ *    with that device current, result cached per device).  Make that first call during set-up,
+ *    before any stream capture begins.
+ *  - Every call on a device uses the same array.  It keeps the previous call's contents, so each
+ *    call clears the C words it needs before use; two calls that overlap on the GPU (different
+ *    streams, or several host threads without ordering) race on it and give undefined results.
+ *    Calls ordered on one stream are safe. */
+#define TP_NAN_STATIC_MAX_C 65536
+int tp_nan_any_dim1_static(const float* x, int64_t B, int64_t C, int64_t inner, int64_t* out_idx,
+                           int64_t* out_count, tp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libtorchpruner_b200.so")
 TP_LOSS_GIVEN = 0
 TP_LOSS_CE = 1
 TP_GATHER_MAX_DESCS = 32
+TP_NAN_STATIC_MAX_C = 65536
 
 _i64 = ctypes.c_int64
 _vp = ctypes.c_void_p
@@ -53,6 +54,7 @@ _SIGNATURES = {
     ),
     "tp_multi_gather": (ctypes.c_int, [ctypes.POINTER(GatherDesc), _i64, _vp, _i64, _vp]),
     "tp_nan_any_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "tp_nan_any_dim1_static": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 
 _lib = None
@@ -314,3 +316,18 @@ def nan_any_dim1(x, flags, out_idx, out_count):
         _check(load().tp_nan_any_dim1(x.data_ptr(), B, C, inner, flags.data_ptr(),
                                       out_idx.data_ptr(), out_count.data_ptr(), _stream(x)),
                "tp_nan_any_dim1")
+
+
+def nan_any_dim1_static(x, out_idx, out_count):
+    """`nan_any_dim1` for callers that may not allocate: the flag scratch is a fixed array inside
+    the library (at most TP_NAN_STATIC_MAX_C channels), so only the outputs are passed in.  Calls
+    on one device share that array — keep them ordered on one stream — and the first call on a
+    device does a one-off address lookup, so make it before capturing any CUDA graph."""
+    x = _cuda_f32(x, "x")
+    B, C, inner = _bchw(x)
+    if out_idx.numel() < C:
+        raise TorchPrunerB200Error("nan_any_dim1_static: out_idx is smaller than the channel count")
+    with torch.cuda.device(x.device), _launch("nan_any_dim1_static", 4 * x.numel(), x, 2):
+        _check(load().tp_nan_any_dim1_static(x.data_ptr(), B, C, inner, out_idx.data_ptr(),
+                                             out_count.data_ptr(), _stream(x)),
+               "tp_nan_any_dim1_static")

@@ -9,7 +9,13 @@
 // the 2-sample probe batch of pruner.py:178 on a finite network).
 #include "common.cuh"
 
+#include <mutex>
+
 namespace tp {
+
+// Scratch of tp_nan_any_dim1_static: one flag word per channel, resident in every GPU context
+// that loads this library (TP_NAN_STATIC_MAX_C * 4 bytes = 256 KiB) until the process exits.
+static __device__ __align__(256) int32_t g_static_nan_flags[TP_NAN_STATIC_MAX_C];
 
 enum { FLAG_NAN = 1, FLAG_PINF = 2, FLAG_NINF = 4 };
 
@@ -88,9 +94,53 @@ int nan_any_dim1_impl(const float* x, int64_t B, int64_t C, int64_t inner, int32
   return TP_OK;
 }
 
+// Device address of g_static_nan_flags on the CURRENT device, resolved once per device.  In host
+// code the symbol name is only a handle; the kernels need the address cudaGetSymbolAddress
+// returns for the device that is current when it is called.
+static int static_flags_address(int32_t** out) {
+  static std::mutex mu;
+  static int32_t* addr[64] = {nullptr};
+  int dev = -1;
+  TP_CUDA(cudaGetDevice(&dev));
+  TP_REQUIRE(dev >= 0 && dev < 64, TP_ERR_LIMIT, "device ordinal %d is out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    TP_CUDA(cudaGetSymbolAddress(&p, g_static_nan_flags));
+    TP_REQUIRE(p != nullptr, TP_ERR_CUDA, "cudaGetSymbolAddress returned a NULL address");
+    addr[dev] = static_cast<int32_t*>(p);
+  }
+  *out = addr[dev];
+  return TP_OK;
+}
+
 }  // namespace tp
 
 extern "C" {
+
+int tp_nan_any_dim1_static(const float* x, int64_t B, int64_t C, int64_t inner, int64_t* out_idx,
+                           int64_t* out_count, tp_stream_t stream) {
+  TP_REQUIRE(B >= 0 && C >= 0 && inner >= 0, TP_ERR_INVALID,
+             "tp_nan_any_dim1_static: negative dimension");
+  TP_REQUIRE(C <= TP_NAN_STATIC_MAX_C, TP_ERR_LIMIT,
+             "tp_nan_any_dim1_static: C = %lld exceeds the built-in scratch of %d channels; use "
+             "tp_nan_any_dim1 with caller-provided scratch instead",
+             (long long)C, (int)TP_NAN_STATIC_MAX_C);
+  TP_REQUIRE(out_count != nullptr, TP_ERR_INVALID, "tp_nan_any_dim1_static: out_count is NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (C == 0) {
+    TP_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int64_t), st));
+    return TP_OK;
+  }
+  TP_REQUIRE(out_idx != nullptr, TP_ERR_INVALID, "tp_nan_any_dim1_static: out_idx is NULL");
+  TP_REQUIRE(B * inner == 0 || x != nullptr, TP_ERR_INVALID, "tp_nan_any_dim1_static: x is NULL");
+  int32_t* flags = nullptr;
+  const int rc = tp::static_flags_address(&flags);
+  if (rc != TP_OK) return rc;
+  // The shared array still holds the previous call's flags; the implementation clears the C
+  // words it is about to OR into (stream-ordered memset, no allocation) before the first kernel.
+  return tp::nan_any_dim1_impl(x, B, C, inner, flags, out_idx, out_count, st);
+}
 
 int tp_nan_any_dim1(const float* x, int64_t B, int64_t C, int64_t inner, int32_t* flags_scratch,
                     int64_t* out_idx, int64_t* out_count, tp_stream_t stream) {
