@@ -60,7 +60,7 @@ def workload_description(n_gpus):
                     "(25 steps = the sv_samples=25 job); fp32 downstream layers, TF32 off",
         "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224,
         "sv_samples_per_step": n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
-        "l2": "working set per step (stacked masked activations, up to 1 GiB per chunk) far "
+        "l2": "working set per step (stacked masked activations, up to 512 MiB per chunk) far "
               "exceeds the 126 MB L2; reduction kernels are timed with an L2 flush between "
               "iterations",
     }
@@ -151,67 +151,72 @@ def quiet():
 
 
 # --------------------------------------------------------------------------- product arm
-def flush_l2(buf):
-    buf.add_(1.0)
-
-
 def time_reductions(device, hbm_peak):
     """Taylor / APoZ / Sensitivity kernels on the activation shapes of config 2 (VGG16, bs 256)
-    and the largest config-4 shape, in isolation: CUDA events around each launch, L2 flushed
-    between launches by writing a 512 MB buffer."""
+    and the largest config-4 shape, in isolation, timed with CUDA events on the launch stream.
+
+    * per shape: one launch per timed region;
+    * config-2 sweep: the 13 layers' launches back to back in one timed region (13 distinct
+      tensors, 283-566 MB in total, so nothing is re-read from L2 inside the region).
+    Before every timed region the L2 is refilled with clean lines by READING a 512 MB buffer (a
+    write-based flush would leave 126 MB of dirty lines whose write-back competes with the reads
+    being measured)."""
     from torchpruner_b200 import _lib
 
-    shapes = [(256, 64, 32, 32), (256, 64, 32, 32), (256, 128, 16, 16), (256, 128, 16, 16),
-              (256, 256, 8, 8), (256, 256, 8, 8), (256, 256, 8, 8), (256, 512, 4, 4),
-              (256, 512, 4, 4), (256, 512, 4, 4), (256, 512, 2, 2), (256, 512, 2, 2),
-              (256, 512, 2, 2)]
+    layer_shapes = [(256, 64, 32, 32)] * 2 + [(256, 128, 16, 16)] * 2 + [(256, 256, 8, 8)] * 3 + \
+        [(256, 512, 4, 4)] * 3 + [(256, 512, 2, 2)] * 3
     big = (256, 64, 112, 112)  # ResNet-50 stem output, 822 MB
-    flush = torch.empty(128 << 20, dtype=torch.float32, device=device)
+    flush = torch.empty(128 << 20, dtype=torch.float32, device=device).normal_()
     stream = torch.cuda.current_stream(device)
-    out = {}
 
-    def run(fn, tensors, nbytes, iters):
-        ms = []
+    def timed(fn, iters=9):
         for _ in range(3):
-            fn(*tensors)
+            fn()
+        ms = []
         for _ in range(iters):
-            flush_l2(flush)
+            # ~0.5 ms of queued read-only work: refills the L2 with clean lines and lets the host
+            # enqueue the whole timed region before the GPU reaches it (device-side timing)
+            for _ in range(6):
+                flush.sum()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
-            fn(*tensors)
+            fn()
             b.record(stream)
             b.synchronize()
             ms.append(a.elapsed_time(b))
-        t = statistics.median(ms)
-        return t, nbytes / t / 1e6
+        return statistics.median(ms)
 
-    uniq = sorted(set(shapes), reverse=True)
-    per_shape = {}
-    for shp in uniq + [big]:
-        z = torch.relu(torch.randn(shp, device=device))
-        g = torch.randn(shp, device=device)
-        n, rows = z.numel(), shp[0] * shp[1]
-        res = {}
-        res["taylor"] = run(lambda a, b: _lib.taylor_reduce(a, b), (z, g), 8 * n + 4 * rows, 10)
-        res["apoz"] = run(lambda a: _lib.apoz_count(a), (z,), 4 * n + 4 * rows, 10)
-        res["sensitivity"] = run(lambda a: _lib.abs_sum(a), (g,), 4 * n + 4 * rows, 10)
-        per_shape[shp] = res
-        del z, g
-    for op in ("taylor", "apoz", "sensitivity"):
-        tot_ms = sum(per_shape[s][op][0] for s in shapes)
-        mult = 8 if op == "taylor" else 4
-        tot_bytes = sum(mult * np.prod(s) + 4 * s[0] * s[1] for s in shapes)
+    zs = [torch.relu(torch.randn(s, device=device)) for s in layer_shapes]
+    gs = [torch.randn(s, device=device) for s in layer_shapes]
+    ops = {
+        "taylor": (lambda i: _lib.taylor_reduce(zs[i], gs[i]), 8),
+        "apoz": (lambda i: _lib.apoz_count(zs[i]), 4),
+        "sensitivity": (lambda i: _lib.abs_sum(gs[i]), 4),
+    }
+    out = {}
+    for op, (fn, mult) in ops.items():
+        nbytes = [mult * int(np.prod(s)) + 4 * s[0] * s[1] for s in layer_shapes]
+        sweep_ms = timed(lambda: [fn(i) for i in range(13)])
+        per = {}
+        for i in (0, 2, 4, 7, 10):
+            per["x".join(map(str, layer_shapes[i]))] = round(nbytes[i] / timed(lambda: fn(i)) / 1e6, 1)
         out[op] = {
-            "c2_sweep_gbs": float(tot_bytes / tot_ms / 1e6),
-            "c2_sweep_frac": float(tot_bytes / tot_ms / 1e6 / hbm_peak),
-            "c2_sweep_us": tot_ms * 1e3,
-            "c2_largest_layer_gbs": per_shape[(256, 64, 32, 32)][op][1],
-            "c2_largest_layer_frac": per_shape[(256, 64, 32, 32)][op][1] / hbm_peak,
-            "c4_largest_gbs": per_shape[big][op][1],
-            "c4_largest_frac": per_shape[big][op][1] / hbm_peak,
-            "per_shape_gbs": {"x".join(map(str, s)): round(per_shape[s][op][1], 1) for s in uniq},
+            "c2_sweep_gbs": sum(nbytes) / sweep_ms / 1e6,
+            "c2_sweep_frac": sum(nbytes) / sweep_ms / 1e6 / hbm_peak,
+            "c2_sweep_us": sweep_ms * 1e3, "c2_sweep_bytes": sum(nbytes), "c2_sweep_launches": 13,
+            "per_shape_gbs": per,
         }
-    del flush
+    del zs, gs
+    z = torch.relu(torch.randn(big, device=device))
+    g = torch.randn(big, device=device)
+    n, rows = z.numel(), big[0] * big[1]
+    for op, fn, nb in (("taylor", lambda: _lib.taylor_reduce(z, g), 8 * n + 4 * rows),
+                       ("apoz", lambda: _lib.apoz_count(z), 4 * n + 4 * rows),
+                       ("sensitivity", lambda: _lib.abs_sum(g), 4 * n + 4 * rows)):
+        gbs = nb / timed(fn) / 1e6
+        out[op]["c4_largest_gbs"] = gbs
+        out[op]["c4_largest_frac"] = gbs / hbm_peak
+    del z, g, flush
     torch.cuda.empty_cache()
     return out
 

@@ -74,7 +74,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         self.mask_indices = []
         self.process_group = None
         self.shard = os.environ.get("TORCHPRUNER_B200_SHARD", "0") == "1"
-        self.max_stack_bytes = int(os.environ.get("TORCHPRUNER_B200_STACK_MB", "1024")) << 20
+        self.max_stack_bytes = int(os.environ.get("TORCHPRUNER_B200_STACK_MB", "512")) << 20
         self.max_stack = int(os.environ.get("TORCHPRUNER_B200_MAX_STACK", "512"))
         self.last_run_info = {}
 

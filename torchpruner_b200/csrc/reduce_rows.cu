@@ -72,12 +72,14 @@ __device__ __forceinline__ void add4(typename RowOpTraits<OP>::acc_t& acc, const
 }
 
 // =====================================================================================
-// Direct-load kernel.
-//   LONG == false: a row has n <= LPR units (unit = float4 if VEC else float): one unit per
-//                  lane, 32/LPR rows per warp pass, 4 passes in flight per warp.
-//   LONG == true : LPR == 32, one warp per row, units strided over lanes, 4 loads in flight.
+// Direct-load kernel.  LPR lanes cooperate on a row (unit = float4 if VEC else float).
+//   LOOP == false: a row has n <= LPR units: one unit per lane, 32/LPR rows per warp pass and 4
+//                  passes in flight per warp (row-level memory parallelism for short rows).
+//   LOOP == true : n > LPR: each lane strides over its row's units, 4 loads in flight.
+// LPR is chosen on the host so that a lane sums ~4-8 units before the shuffle tree starts (the
+// tree costs as much as the loads for short rows).
 // =====================================================================================
-template <int OP, int LPR, bool VEC, bool LONG>
+template <int OP, int LPR, bool VEC, bool LOOP>
 __global__ void __launch_bounds__(256)
 reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
                 float* __restrict__ out, int64_t R, int64_t L, int is_signed) {
@@ -85,15 +87,15 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
   using acc_t = typename T::acc_t;
   constexpr bool kTwo = (T::kStreams == 2);
   constexpr int RPW = 32 / LPR;
+  constexpr int U = 4;
   const int lane = threadIdx.x & 31;
   const int sub = lane % LPR;
   const int slot = lane / LPR;
   const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = (gridDim.x * (int64_t)blockDim.x) >> 5;
-  const int64_t n = VEC ? (L >> 2) : L;
+  const int n = (int)(VEC ? (L >> 2) : L);
 
-  if (!LONG) {
-    constexpr int U = 4;
+  if (!LOOP) {
     for (int64_t base = warp * (RPW * U); base < R; base += nwarps * (RPW * U)) {
       acc_t acc[U];
       if (VEC) {
@@ -139,20 +141,21 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
       }
     }
   } else {
-    constexpr int U = 4;
-    for (int64_t row = warp; row < R; row += nwarps) {
+    for (int64_t base = warp * RPW; base < R; base += nwarps * RPW) {
+      const int64_t row = base + slot;
+      const bool live = row < R;
       acc_t acc = 0;
       if (VEC) {
         const float4* pa = reinterpret_cast<const float4*>(a) + row * n;
         const float4* pb = reinterpret_cast<const float4*>(b) + row * n;
-        for (int64_t i = lane; i < n; i += 32 * U) {
+        for (int i = sub; i < n; i += LPR * U) {
           float4 va[U], vb[U];
 #pragma unroll
           for (int u = 0; u < U; ++u) {
-            const int64_t j = i + 32 * u;
+            const int j = i + LPR * u;
             va[u] = make_float4(0.f, 0.f, 0.f, 0.f);
             vb[u] = va[u];
-            if (j < n) {
+            if (live && j < n) {
               va[u] = ldg_stream4(pa + j);
               if (kTwo) vb[u] = ldg_stream4(pb + j);
             }
@@ -163,14 +166,14 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
       } else {
         const float* pa = a + row * n;
         const float* pb = b + row * n;
-        for (int64_t i = lane; i < n; i += 32 * U) {
+        for (int i = sub; i < n; i += LPR * U) {
           float va[U], vb[U];
 #pragma unroll
           for (int u = 0; u < U; ++u) {
-            const int64_t j = i + 32 * u;
+            const int j = i + LPR * u;
             va[u] = 0.f;
             vb[u] = 0.f;
-            if (j < n) {
+            if (live && j < n) {
               va[u] = ldg_stream1(pa + j);
               if (kTwo) vb[u] = ldg_stream1(pb + j);
             }
@@ -179,8 +182,8 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
           for (int u = 0; u < U; ++u) T::add(acc, va[u], vb[u]);
         }
       }
-      const acc_t s = group_reduce(acc, 32);
-      if (lane == 0) out[row] = T::finalize(s, is_signed);
+      const acc_t s = group_reduce(acc, LPR);
+      if (sub == 0 && live) out[row] = T::finalize(s, is_signed);
     }
   }
 }
@@ -213,19 +216,34 @@ reduce_rows_tma(const float* __restrict__ a, const float* __restrict__ b,
   const int lane = tid & 31;
   const int wid = tid >> 5;
   const int64_t G = gridDim.x;
-  const int64_t c = blockIdx.x;
+  const int64_t n_tiles = chunk_mode ? R : (R + tile_rows - 1) / tile_rows;  // units CTAs stride over
+  const int n_chunks = chunk_mode ? (int)((L + tile_floats - 1) / tile_floats) : 1;
 
-  // Work owned by this CTA.
-  int64_t n_chunks = 1;  // chunks per row (chunk mode)
-  int64_t my_count;
-  if (chunk_mode) {
-    n_chunks = (L + tile_floats - 1) / tile_floats;
-    const int64_t my_rows = (R > c) ? (R - c + G - 1) / G : 0;
-    my_count = my_rows * n_chunks;
-  } else {
-    const int64_t n_tiles = (R + tile_rows - 1) / tile_rows;
-    my_count = (n_tiles > c) ? (n_tiles - c + G - 1) / G : 0;
-  }
+  // A cursor over this CTA's tiles.  All index arithmetic is incremental: 64-bit divisions on
+  // the per-tile critical path cost more than the tile's loads.
+  struct Cursor {
+    int64_t unit;  // tile index (row-tile mode) or row index (chunk mode)
+    int ch;        // chunk within the row (chunk mode)
+  };
+  auto valid = [&](const Cursor& c) { return c.unit < n_tiles; };
+  auto advance = [&](Cursor& c) {
+    if (chunk_mode && ++c.ch < n_chunks) return;
+    c.ch = 0;
+    c.unit += G;
+  };
+  auto extent = [&](const Cursor& c, int64_t& first_elem, int& n_floats) {
+    if (chunk_mode) {
+      const int off = c.ch * tile_floats;
+      const int64_t left = L - off;
+      first_elem = c.unit * L + off;
+      n_floats = left < tile_floats ? (int)left : tile_floats;
+    } else {
+      const int64_t r0 = c.unit * tile_rows;
+      const int64_t rows = (R - r0) < tile_rows ? (R - r0) : tile_rows;
+      first_elem = r0 * L;
+      n_floats = (int)(rows * L);
+    }
+  };
 
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) mbar_init(&bars[s], 1);
@@ -233,54 +251,47 @@ reduce_rows_tma(const float* __restrict__ a, const float* __restrict__ b,
   }
   __syncthreads();
 
-  auto tile_extent = [&](int64_t i, int64_t& first_elem, int64_t& n_floats) {
-    if (chunk_mode) {
-      const int64_t row = c + (i / n_chunks) * G;
-      const int64_t ch = i % n_chunks;
-      first_elem = row * L + ch * tile_floats;
-      const int64_t left = L - ch * tile_floats;
-      n_floats = left < tile_floats ? left : tile_floats;
-    } else {
-      const int64_t t = c + i * G;
-      const int64_t r0 = t * tile_rows;
-      const int64_t rows = (R - r0) < tile_rows ? (R - r0) : tile_rows;
-      first_elem = r0 * L;
-      n_floats = rows * L;
-    }
+  Cursor prod{(int64_t)blockIdx.x, 0};  // next tile to request (thread 0 only)
+  int prod_stage = 0;
+  auto issue = [&]() {
+    int64_t first;
+    int nf;
+    extent(prod, first, nf);
+    const uint32_t bytes = (uint32_t)nf * 4u;
+    mbar_arrive_expect_tx(&bars[prod_stage], bytes * kStreams);
+    float* dst = ring + (size_t)prod_stage * kStreams * tile_floats;
+    bulk_g2s(dst, a + first, bytes, &bars[prod_stage]);
+    if (kStreams == 2) bulk_g2s(dst + tile_floats, b + first, bytes, &bars[prod_stage]);
+    advance(prod);
+    if (++prod_stage == stages) prod_stage = 0;
   };
-
-  auto issue = [&](int64_t i) {  // called by thread 0 only
-    const int s = (int)(i % stages);
-    int64_t first, nf;
-    tile_extent(i, first, nf);
-    const uint32_t bytes = (uint32_t)(nf * 4);
-    mbar_arrive_expect_tx(&bars[s], bytes * kStreams);
-    float* dst = ring + (size_t)s * kStreams * tile_floats;
-    bulk_g2s(dst, a + first, bytes, &bars[s]);
-    if (kStreams == 2) bulk_g2s(dst + tile_floats, b + first, bytes, &bars[s]);
-  };
-
   if (tid == 0) {
-    const int64_t pre = my_count < (stages - 1) ? my_count : (stages - 1);
-    for (int64_t i = 0; i < pre; ++i) issue(i);
+    for (int s = 0; s < stages - 1 && valid(prod); ++s) issue();
   }
 
+  Cursor cons{(int64_t)blockIdx.x, 0};
+  int stage = 0;
+  uint32_t phase = 0;
   acc_t row_acc = 0;  // chunk mode: partial of the row in flight
+  const int rpw = 32 / lpr;
+  const int sub = lane % lpr;
+  const int slot = lane / lpr;
+  const int n = VEC ? (int)(L >> 2) : (int)L;
 
-  for (int64_t i = 0; i < my_count; ++i) {
-    // Stage (i-1)%stages was drained by every thread before the barrier that ended the
-    // previous iteration, so it can be refilled now.
-    if (tid == 0 && i + stages - 1 < my_count) issue(i + stages - 1);
-    const int s = (int)(i % stages);
-    mbar_wait(&bars[s], (uint32_t)((i / stages) & 1));
+  for (; valid(cons); advance(cons)) {
+    // The stage consumed in the previous iteration was released by the barrier that ended it,
+    // so it can be refilled now: the ring always has stages-1 tiles in flight.
+    if (tid == 0 && valid(prod)) issue();
+    mbar_wait(&bars[stage], phase);
 
-    const float* sa = ring + (size_t)s * kStreams * tile_floats;
+    const float* sa = ring + (size_t)stage * kStreams * tile_floats;
     const float* sb = sa + tile_floats;
-    int64_t first, nf;
-    tile_extent(i, first, nf);
+    int64_t first;
+    int nf;
+    extent(cons, first, nf);
 
     if (chunk_mode) {
-      const int nv = (int)(nf >> 2);
+      const int nv = nf >> 2;
       const float4* sa4 = reinterpret_cast<const float4*>(sa);
       const float4* sb4 = reinterpret_cast<const float4*>(sb);
       for (int v = tid; v < nv; v += kTmaThreads) {
@@ -288,51 +299,73 @@ reduce_rows_tma(const float* __restrict__ a, const float* __restrict__ b,
         const float4 vb = (kStreams == 2) ? sb4[v] : va;
         add4<OP>(row_acc, va, vb);
       }
-      if ((i % n_chunks) == n_chunks - 1) {
+      if (cons.ch == n_chunks - 1) {
         const acc_t w = group_reduce(row_acc, 32);
         if (lane == 0) red[wid] = w;
         __syncthreads();
         if (tid == 0) {
           acc_t tot = 0;
           for (int k = 0; k < kTmaThreads / 32; ++k) tot += red[k];
-          out[c + (i / n_chunks) * G] = T::finalize(tot, is_signed);
+          out[cons.unit] = T::finalize(tot, is_signed);
         }
         row_acc = 0;
       }
     } else {
-      const int64_t r0 = (c + i * G) * tile_rows;
-      const int rows = (int)(nf / L);
-      const int rpw = 32 / lpr;
-      const int sub = lane % lpr;
-      const int slot = lane / lpr;
-      const int n = VEC ? (int)(L >> 2) : (int)L;
-      for (int rb = wid * rpw; rb < rows; rb += (kTmaThreads / 32) * rpw) {
-        const int r = rb + slot;
-        acc_t acc = 0;
-        if (r < rows) {
-          if (VEC) {
-            const float4* pa = reinterpret_cast<const float4*>(sa) + (size_t)r * n;
-            const float4* pb = reinterpret_cast<const float4*>(sb) + (size_t)r * n;
-            for (int j = sub; j < n; j += lpr) {
-              const float4 va = pa[j];
-              const float4 vb = (kStreams == 2) ? pb[j] : va;
-              add4<OP>(acc, va, vb);
+      const int64_t r0 = cons.unit * tile_rows;
+      const int rows = (int)((R - r0) < tile_rows ? (R - r0) : tile_rows);
+      // Two row groups per warp iteration: independent chains hide the LDS + shuffle latency.
+      for (int rb = wid * rpw; rb < rows; rb += (kTmaThreads / 32) * rpw * 2) {
+        const int r_0 = rb + slot;
+        const int r_1 = r_0 + (kTmaThreads / 32) * rpw;
+        acc_t acc0 = 0, acc1 = 0;
+        if (VEC) {
+          const float4* pa0 = reinterpret_cast<const float4*>(sa) + (size_t)r_0 * n;
+          const float4* pb0 = reinterpret_cast<const float4*>(sb) + (size_t)r_0 * n;
+          const float4* pa1 = reinterpret_cast<const float4*>(sa) + (size_t)r_1 * n;
+          const float4* pb1 = reinterpret_cast<const float4*>(sb) + (size_t)r_1 * n;
+          const bool l0 = r_0 < rows, l1 = r_1 < rows;
+          for (int j = sub; j < n; j += lpr) {
+            if (l0) {
+              const float4 va = pa0[j];
+              const float4 vb = (kStreams == 2) ? pb0[j] : va;
+              add4<OP>(acc0, va, vb);
             }
-          } else {
-            const float* pa = sa + (size_t)r * n;
-            const float* pb = sb + (size_t)r * n;
-            for (int j = sub; j < n; j += lpr) {
-              const float va = pa[j];
-              const float vb = (kStreams == 2) ? pb[j] : va;
-              T::add(acc, va, vb);
+            if (l1) {
+              const float4 va = pa1[j];
+              const float4 vb = (kStreams == 2) ? pb1[j] : va;
+              add4<OP>(acc1, va, vb);
+            }
+          }
+        } else {
+          const float* pa0 = sa + (size_t)r_0 * n;
+          const float* pb0 = sb + (size_t)r_0 * n;
+          const float* pa1 = sa + (size_t)r_1 * n;
+          const float* pb1 = sb + (size_t)r_1 * n;
+          const bool l0 = r_0 < rows, l1 = r_1 < rows;
+          for (int j = sub; j < n; j += lpr) {
+            if (l0) {
+              const float va = pa0[j];
+              const float vb = (kStreams == 2) ? pb0[j] : va;
+              T::add(acc0, va, vb);
+            }
+            if (l1) {
+              const float va = pa1[j];
+              const float vb = (kStreams == 2) ? pb1[j] : va;
+              T::add(acc1, va, vb);
             }
           }
         }
-        acc = group_reduce(acc, lpr);
-        if (sub == 0 && r < rows) out[r0 + r] = T::finalize(acc, is_signed);
+        acc0 = group_reduce(acc0, lpr);
+        acc1 = group_reduce(acc1, lpr);
+        if (sub == 0 && r_0 < rows) out[r0 + r_0] = T::finalize(acc0, is_signed);
+        if (sub == 0 && r_1 < rows) out[r0 + r_1] = T::finalize(acc1, is_signed);
       }
     }
-    __syncthreads();  // stage s fully consumed (and `red` free again)
+    __syncthreads();  // stage fully consumed (and `red` free again)
+    if (++stage == stages) {
+      stage = 0;
+      phase ^= 1u;
+    }
   }
 }
 
@@ -344,6 +377,17 @@ static inline int pow2_ceil(int64_t v) {
   return p;
 }
 
+// Lanes per row for a row of n units (float4 if vec else float).  Short rows: one unit per
+// lane.  Longer rows: each lane sums several units serially so that the shuffle tree (log2 LPR
+// steps, as expensive as the loads for short rows) is amortised; at least 8 lanes per row keeps
+// 128-bit shared-memory reads of a quarter-warp inside one row (bank-conflict free).
+static inline int lanes_per_row(int64_t n, bool vec) {
+  if (n <= 8) return pow2_ceil(n);
+  if (n <= 64) return 8;
+  if (n <= (vec ? 128 : 256)) return 16;
+  return 32;
+}
+
 static inline int64_t gcd64(int64_t x, int64_t y) {
   while (y) {
     int64_t t = x % y;
@@ -353,17 +397,17 @@ static inline int64_t gcd64(int64_t x, int64_t y) {
   return x;
 }
 
-template <int OP, int LPR, bool VEC, bool LONG>
+template <int OP, int LPR, bool VEC, bool LOOP>
 static int launch_ldg_inst(const float* a, const float* b, float* out, int64_t R, int64_t L,
                            int is_signed, cudaStream_t st) {
   constexpr int RPW = 32 / LPR;
-  const int64_t rows_per_warp = LONG ? 1 : RPW * 4;
+  const int64_t rows_per_warp = LOOP ? RPW : RPW * 4;
   const int64_t warps = (R + rows_per_warp - 1) / rows_per_warp;
   int64_t blocks = (warps + 7) / 8;
   const int64_t cap = (int64_t)sm_count() * 8 * 4;  // 8 resident 256-thread CTAs x 4 waves
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  reduce_rows_ldg<OP, LPR, VEC, LONG><<<(unsigned)blocks, 256, 0, st>>>(a, b, out, R, L, is_signed);
+  reduce_rows_ldg<OP, LPR, VEC, LOOP><<<(unsigned)blocks, 256, 0, st>>>(a, b, out, R, L, is_signed);
   TP_LAUNCH_CHECK("reduce_rows_ldg");
   return TP_OK;
 }
@@ -372,14 +416,19 @@ template <int OP, bool VEC>
 static int launch_ldg_vec(const float* a, const float* b, float* out, int64_t R, int64_t L,
                           int is_signed, cudaStream_t st) {
   const int64_t n = VEC ? (L >> 2) : L;
-  if (n > 32) return launch_ldg_inst<OP, 32, VEC, true>(a, b, out, R, L, is_signed, st);
-  switch (pow2_ceil(n)) {
+  const int lpr = lanes_per_row(n, VEC);
+  if (n > lpr) {
+    switch (lpr) {
+      case 8: return launch_ldg_inst<OP, 8, VEC, true>(a, b, out, R, L, is_signed, st);
+      case 16: return launch_ldg_inst<OP, 16, VEC, true>(a, b, out, R, L, is_signed, st);
+      default: return launch_ldg_inst<OP, 32, VEC, true>(a, b, out, R, L, is_signed, st);
+    }
+  }
+  switch (lpr) {
     case 1: return launch_ldg_inst<OP, 1, VEC, false>(a, b, out, R, L, is_signed, st);
     case 2: return launch_ldg_inst<OP, 2, VEC, false>(a, b, out, R, L, is_signed, st);
     case 4: return launch_ldg_inst<OP, 4, VEC, false>(a, b, out, R, L, is_signed, st);
-    case 8: return launch_ldg_inst<OP, 8, VEC, false>(a, b, out, R, L, is_signed, st);
-    case 16: return launch_ldg_inst<OP, 16, VEC, false>(a, b, out, R, L, is_signed, st);
-    default: return launch_ldg_inst<OP, 32, VEC, false>(a, b, out, R, L, is_signed, st);
+    default: return launch_ldg_inst<OP, 8, VEC, false>(a, b, out, R, L, is_signed, st);
   }
 }
 
@@ -415,8 +464,7 @@ static int launch_tma_inst(const float* a, const float* b, float* out, int64_t R
   if (grid > units) grid = units;
   auto kern = reduce_rows_tma<OP, VEC>;
   TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int n = VEC ? (int)(L >> 2) : (int)L;
-  const int lpr = pow2_ceil(n);
+  const int lpr = lanes_per_row(VEC ? (L >> 2) : L, VEC);
   kern<<<(unsigned)grid, kTmaThreads, smem, st>>>(a, b, out, R, L, is_signed, tile_rows, chunk_mode,
                                                   stages, tile_floats, lpr);
   TP_LAUNCH_CHECK("reduce_rows_tma");
@@ -441,8 +489,13 @@ static int launch_reduce(const float* a, const float* b, float* out, int64_t R, 
 
   const Tuning& t = tuning();
   const bool ptr_aligned = ((uintptr_t)a % 16 == 0) && (!two || (uintptr_t)b % 16 == 0);
-  bool use_tma = ptr_aligned && (t.reduce_variant == 2 ||
-                                 (t.reduce_variant == 0 && R * L >= t.reduce_tma_min_elems));
+  // Auto policy (profiles/r01_tune_reduce_v2.txt): the direct-load kernel is at full HBM speed
+  // for rows up to a tile; rows longer than a tile stream fastest through the TMA ring with the
+  // whole CTA on one row (1.05-1.09 of the measured copy bandwidth on 50 KB rows).
+  bool use_tma = ptr_aligned &&
+                 (t.reduce_variant == 2 ||
+                  (t.reduce_variant == 0 && L > t.reduce_tile_floats && L % 4 == 0 &&
+                   R * L >= t.reduce_tma_min_elems));
   if (use_tma) {
     const int tile_floats = t.reduce_tile_floats;
     if (L <= tile_floats) {
