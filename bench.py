@@ -53,6 +53,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tensor_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return float(p["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json)"
+    return 1400.0, "fallback (B200_PROFILING.md)"
+
+
 def workload_description(n_gpus):
     return {
         "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
@@ -310,18 +319,35 @@ def run_product(args, rank, world, local_rank):
         own_ms = {k: v["ms"] for k, v in kernel_summary.items()}
         dominant = max(own_ms, key=own_ms.get)
         dom = kernel_summary[dominant]
-        achieved = dom["bytes"] / dom["ms"] / 1e6 if dom["ms"] > 0 else 0.0
-        roofline = {
-            "kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
-            "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
-            "peak_source": peak_src, "launches": dom["launches"],
-            "avg_launch_ms": dom["ms"] / max(1, dom["launches"]),
-            "share_of_step": dom["ms"] / total_ms,
-            "note": "dominant hand-written kernel of the step; the rest of the step is the "
-                    "user model's downstream layers in fp32 cuDNN/cuBLAS (library code)",
-        }
+        if dominant == "conv_tf32x3":
+            # fp32-accurate layers on tcgen05: every fp32 product is three TF32 MMAs, so the
+            # tensor pipe executes 3x the layer's nominal FLOPs; TF32 runs at half the bf16 rate.
+            bf16 = tensor_peak()
+            executed = 3.0 * dom["flops"] / dom["ms"] / 1e9 if dom["ms"] > 0 else 0.0
+            roofline = {
+                "kernel": dominant, "bound": "tensor", "achieved": executed, "peak": bf16[0] / 2.0,
+                "unit": "TFLOP/s", "frac": executed / (bf16[0] / 2.0), "traffic": None,
+                "peak_source": bf16[1] + " bf16 sustained / 2 (TF32 dense runs at half the bf16 rate)",
+                "useful_tflops": executed / 3.0,
+                "achieved_definition": "3 TF32 MMAs per fp32 product (hi*hi + hi*lo + lo*hi) x "
+                                       "2*MACs of the layer, summed over launches / summed duration",
+                "launches": dom["launches"], "avg_launch_ms": dom["ms"] / max(1, dom["launches"]),
+                "share_of_step": dom["ms"] / total_ms,
+            }
+        else:
+            achieved = dom["bytes"] / dom["ms"] / 1e6 if dom["ms"] > 0 else 0.0
+            roofline = {
+                "kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+                "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "peak_source": peak_src, "launches": dom["launches"],
+                "avg_launch_ms": dom["ms"] / max(1, dom["launches"]),
+                "share_of_step": dom["ms"] / total_ms,
+                "note": "dominant hand-written kernel of the step; the rest of the step is the "
+                        "user model's downstream layers in fp32 cuDNN/cuBLAS (library code)",
+            }
         own = {k: {"launches": v["launches"], "ms_per_step": v["ms"] / args.steps,
-                   "gbs": (v["bytes"] / v["ms"] / 1e6) if v["ms"] > 0 else None}
+                   "gbs": (v["bytes"] / v["ms"] / 1e6) if v["ms"] > 0 else None,
+                   "tflops": (v["flops"] / v["ms"] / 1e9) if v["ms"] > 0 and v["flops"] else None}
                for k, v in kernel_summary.items()}
         with quiet():
             reductions = time_reductions(device, hbm_peak) if (world == 1 and not args.core_only) else None

@@ -137,6 +137,38 @@ int tp_nan_any_dim1(const float* x, int64_t B, int64_t C, int64_t inner,
                     int32_t* flags_scratch, int64_t* out_idx, int64_t* out_count,
                     tp_stream_t stream);
 
+/* ---------------------------------------------------------------- downstream-layer engine
+ * fp32-accurate layers for the batched Shapley evaluations (reference shapley_values.py:57 ->
+ * attributions.py:85 re-runs every layer after the evaluation module once per evaluation; for
+ * recognised conv3x3/BatchNorm/ReLU/MaxPool/Linear tails those layers run here instead of in
+ * cuDNN/cuBLAS).  Activations are NHWC and carried as a TF32 split pair: hi = rn_tf32(x),
+ * lo = rn_tf32(x - hi); products are hi*hi + hi*lo + lo*hi on tcgen05 (3xTF32).
+ *
+ * y = act(conv(x, w) * scale[c] + shift[c]),  conv = 3x3 stride 1 pad 1 (taps == 9) or 1x1 /
+ * linear (taps == 1).  x_hi/x_lo: [N,H,W,Cin]; w_hi/w_lo: [Cout][taps*Cin] with k = tap*Cin + c,
+ * tap = r*3 + s; scale/shift: [Cout] (BatchNorm and bias folded by the caller); y_hi/y_lo:
+ * [N,H,W,Cout].  y_lo == NULL writes the unsplit fp32 result to y_hi (logits, or the input of a
+ * pooling step).  Limits: Cin % 32 == 0; W divides 128 and H*W divides 128 or 128/W divides H. */
+int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
+                   int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
+                   const float* scale, const float* shift, int relu, float* y_hi, float* y_lo,
+                   tp_stream_t stream);
+
+/* hi[i] = rn_tf32(x[i]), lo[i] = rn_tf32(x[i] - hi[i]); hi + lo == x up to 2^-23 relative. */
+int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t stream);
+
+/* K5 for the engine above: z is NCHW [B,C,H,W]; out_hi/out_lo are NHWC [P*B, H', W', C] holding
+ * the TF32 split of the (optionally 2x2 max-pooled, pool != 0) activation with channels c such
+ * that inv_perm[c] <= k0+p zeroed in copy p.  Replaces shapley_values.py:53-56 like
+ * tp_prefix_mask_stack does, plus the layout change and a leading MaxPool2d(2). */
+int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
+                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
+                       tp_stream_t stream);
+
+/* MaxPool2d(2) over NHWC raw fp32 [N,H,W,C] followed by the TF32 split -> [N,H/2,W/2,C]. */
+int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
+                           float* lo, tp_stream_t stream);
+
 /* ---------------------------------------------------------------- no-allocation variant
  * No counterpart in the reference: this entry point exists for callers of THIS library that
  * cannot allocate device memory around the call.  Typical cases: a forward hook that runs in the

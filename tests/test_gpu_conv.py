@@ -1,0 +1,170 @@
+"""The fp32-accurate tensor-core layer engine (tp_conv_tf32x3 and companions) against float64
+convolutions, through the C-ABI."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from torchpruner_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _ref64(x_nhwc, w, taps, scale, shift, relu):
+    """float64 reference: x [N,H,W,Cin], w [Cout, taps*Cin] with k = (r*3+s)*Cin + c."""
+    N, H, W, Cin = x_nhwc.shape
+    Cout = w.shape[0]
+    x = x_nhwc.double().permute(0, 3, 1, 2)
+    if taps == 9:
+        w4 = w.double().view(Cout, 3, 3, Cin).permute(0, 3, 1, 2)
+        y = F.conv2d(x, w4, padding=1)
+    else:
+        y = F.conv2d(x, w.double().view(Cout, Cin, 1, 1))
+    y = y * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)
+    if relu:
+        y = y.relu()
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+def test_tf32_split():
+    x = torch.randn(100003, device=DEV) * 37.0
+    hi, lo = _lib.tf32_split(x)
+    assert int((hi.view(torch.int32) & 0x1FFF).abs().max()) == 0      # both terms are TF32-exact
+    assert int((lo.view(torch.int32) & 0x1FFF).abs().max()) == 0
+    rel = ((hi.double() + lo.double() - x.double()).abs() / x.double().abs().clamp_min(1e-30))
+    assert float(rel.max()) <= 2.0 ** -22
+    assert float((lo.abs() / x.abs().clamp_min(1e-30)).max()) <= 2.0 ** -11 * 1.001
+    assert abs(float(((hi + lo).double() - x.double()).mean())) < 37.0 * 2e-9   # unbiased
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout,taps,relu", [
+    (4, 32, 32, 64, 64, 9, True),      # VGG features.3-style layer
+    (3, 16, 16, 128, 256, 9, True),
+    (5, 8, 8, 256, 256, 9, True),      # 2 images per 128-pixel tile
+    (19, 4, 4, 512, 512, 9, True),     # 8 images per tile, ragged last tile
+    (70, 2, 2, 512, 512, 9, False),    # 32 images per tile, ragged
+    (300, 1, 1, 512, 512, 1, True),    # linear layer
+    (130, 1, 1, 512, 10, 1, False),    # logits: 10 outputs, unsplit result
+    (2, 16, 16, 32, 64, 9, True),      # one k-block per tap
+])
+@pytest.mark.parametrize("promote", [1, 2, 8])
+def test_conv_tf32x3_matches_float64(N, H, W, Cin, Cout, taps, relu, promote):
+    _lib.set_tuning("conv_promote", promote)
+    try:
+        _conv_case(N, H, W, Cin, Cout, taps, relu, promote)
+    finally:
+        _lib.set_tuning("conv_promote", 2)
+
+
+def _conv_case(N, H, W, Cin, Cout, taps, relu, promote):
+    gen = torch.Generator(device=DEV).manual_seed(N * 1000 + Cin)
+    x = torch.randn((N, H, W, Cin), device=DEV, generator=gen)
+    x = x * (torch.rand((N, H, W, Cin), device=DEV, generator=gen) > 0.3)   # ReLU-like zeros
+    w = torch.randn((Cout, taps * Cin), device=DEV, generator=gen) / (taps * Cin) ** 0.5
+    scale = torch.rand(Cout, device=DEV, generator=gen) + 0.5
+    shift = torch.randn(Cout, device=DEV, generator=gen) * 0.1
+    x_hi, x_lo = _lib.tf32_split(x)
+    w_hi, w_lo = _lib.tf32_split(w)
+    split = Cout != 10
+    y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=split)
+    y = y_hi + y_lo if split else y_hi
+    want = _ref64(x, w, taps, scale, shift, relu)
+    scale_ref = float(want.abs().max())
+    err = float((y.double() - want).abs().max())
+    # fp32 library convolution on the same data, for scale: 3xTF32 must be in the same class
+    x32 = x.permute(0, 3, 1, 2)
+    saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        if taps == 9:
+            y32 = F.conv2d(x32, w.view(Cout, 3, 3, Cin).permute(0, 3, 1, 2), padding=1)
+        else:
+            y32 = F.conv2d(x32, w.view(Cout, Cin, 1, 1))
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+    y32 = y32 * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
+    if relu:
+        y32 = y32.relu()
+    err32 = float((y32.permute(0, 2, 3, 1).double() - want).abs().max())
+    print(f"K={taps * Cin} promote={promote} max abs err: 3xTF32 {err:.3e}  fp32 library {err32:.3e}  "
+          f"(scale {scale_ref:.3f})")
+    # the tensor core's accumulator truncates: the bound scales with the k-blocks per partial sum
+    assert err <= (1e-6 if promote <= 2 else 4e-6) * scale_ref, (err, err32, scale_ref)
+    if split:
+        assert int((y_hi.view(torch.int32) & 0x1FFF).abs().max()) == 0   # hi is TF32-exact
+
+
+def test_mask_stack_nhwc_and_pool():
+    gen = torch.Generator().manual_seed(5)
+    B, C, H, W, P, k0 = 3, 32, 4, 4, 5, 7
+    z = torch.randn((B, C, H, W), generator=gen)
+    perm = np.random.RandomState(1).permutation(C)
+    inv = np.empty(C, np.int32)
+    inv[perm] = np.arange(C, dtype=np.int32)
+    for pool in (False, True):
+        Ho, Wo = (H // 2, W // 2) if pool else (H, W)
+        hi = torch.empty(P * B * Ho * Wo * C, device=DEV)
+        lo = torch.empty_like(hi)
+        ghi, glo = _lib.mask_stack_nhwc(z.to(DEV), torch.from_numpy(inv).to(DEV), k0, P, pool, hi, lo)
+        src = F.max_pool2d(z, 2) if pool else z
+        for p in range(P):
+            want = src.clone()
+            want[:, perm[:k0 + p + 1]] = 0.0
+            got = (ghi + glo)[p * B:(p + 1) * B].permute(0, 3, 1, 2).cpu()
+            assert torch.equal(got == 0, want == 0)            # the mask is exact
+            assert float((got - want).abs().max()) <= 2.0 ** -22 * float(want.abs().max())
+    x = torch.randn((6, 8, 8, 64), generator=gen)
+    phi, plo = _lib.maxpool2_split_nhwc(x.to(DEV))
+    want = F.max_pool2d(x.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+    assert float(((phi + plo).cpu() - want).abs().max()) <= 2.0 ** -22 * float(want.abs().max())
+
+
+@pytest.mark.parametrize("tag", ["features.0", "features.10", "features.27", "features.40", "classifier.1"])
+def test_native_tail_agrees_with_forward_partial(tag):
+    """Whole-run check of the tcgen05 layer engine: same seed, engine on vs engine off."""
+    import numpy as np
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+        layer = dict(model.named_modules())[tag]
+        tables = {}
+        for native in ("auto", False):
+            np.random.seed(3)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                         reduction="none")
+            m.native_tail = native
+            m.max_stack = 48   # several chunks per permutation
+            tables[native] = m.run(layer, find_best_evaluation_module=True)
+            assert m.last_run_info["native_tail"] is bool(native), m.last_run_info
+            if native:
+                print(tag, "verify rel err", m.last_run_info["native"])
+        diff = np.abs(tables["auto"] - tables[False]).max()
+        print(tag, "max |native - forward_partial| =", diff, "max |score| =", np.abs(tables[False]).max())
+        assert diff <= 2e-5   # differences of losses ~2.3: a few fp32 ulps of the loss
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+def test_native_tail_declines_unsupported_models():
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions.native_tail import NativeTail
+
+    model, shape = workloads.build("small_cnn")   # conv with padding 2 downstream of conv1
+    model.to(DEV)
+    x = torch.randn((4,) + shape, device=DEV)
+    with torch.no_grad():
+        z = model.forward_partial(x, to_module=model.features[1])
+    assert NativeTail.build(model, model.features[1], z) is None
+    with torch.no_grad():
+        z = model.forward_partial(x, to_module=model.features[4])   # pool -> flatten -> fc -> fc
+    tail = NativeTail.build(model, model.features[4], z)
+    assert tail is not None and tail.pool_first and len(tail.steps) == 2

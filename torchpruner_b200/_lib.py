@@ -55,6 +55,12 @@ _SIGNATURES = {
     "tp_multi_gather": (ctypes.c_int, [ctypes.POINTER(GatherDesc), _i64, _vp, _i64, _vp]),
     "tp_nan_any_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "tp_nan_any_dim1_static": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "tp_conv_tf32x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
+                                      _vp, _vp, ctypes.c_int, _vp, _vp, _vp]),
+    "tp_tf32_split": (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
+    "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
+                                          _vp, _vp, _vp]),
+    "tp_maxpool2_split_nhwc": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
 }
 
 _lib = None
@@ -104,16 +110,16 @@ class LaunchProfile:
     recorded.  Inactive (the default) it costs one attribute test per call."""
 
     def __init__(self):
-        self.records = {}   # name -> [launches, bytes, [(start_event, stop_event), ...]]
+        self.records = {}   # name -> [launches, bytes, [(start_event, stop_event), ...], flops]
         self.timed = True
 
     def summary(self):
         """{name: {"launches", "bytes", "ms"}}; synchronises the device."""
         torch.cuda.synchronize()
         out = {}
-        for name, (n, nbytes, pairs) in self.records.items():
+        for name, (n, nbytes, pairs, flops) in self.records.items():
             ms = sum(a.elapsed_time(b) for a, b in pairs)
-            out[name] = {"launches": n, "bytes": nbytes, "ms": ms}
+            out[name] = {"launches": n, "bytes": nbytes, "ms": ms, "flops": flops}
         return out
 
 
@@ -136,10 +142,10 @@ def profile_end():
 class _launch:
     """with _launch(name, algorithmic_bytes, tensor, kernels): <C-ABI call>"""
 
-    __slots__ = ("name", "nbytes", "t", "kernels", "ev")
+    __slots__ = ("name", "nbytes", "t", "kernels", "ev", "flops")
 
-    def __init__(self, name, nbytes, t, kernels=1):
-        self.name, self.nbytes, self.t, self.kernels = name, nbytes, t, kernels
+    def __init__(self, name, nbytes, t, kernels=1, flops=0):
+        self.name, self.nbytes, self.t, self.kernels, self.flops = name, nbytes, t, kernels, flops
 
     def __enter__(self):
         self.ev = None
@@ -149,9 +155,10 @@ class _launch:
 
     def __exit__(self, et, ev, tb):
         if _profile is not None and et is None:
-            rec = _profile.records.setdefault(self.name, [0, 0, []])
+            rec = _profile.records.setdefault(self.name, [0, 0, [], 0])
             rec[0] += self.kernels
             rec[1] += int(self.nbytes)
+            rec[3] += int(self.flops)
             if self.ev is not None:
                 stop = torch.cuda.Event(enable_timing=True)
                 stop.record(torch.cuda.current_stream(self.t.device))
@@ -331,3 +338,67 @@ def nan_any_dim1_static(x, out_idx, out_count):
         _check(load().tp_nan_any_dim1_static(x.data_ptr(), B, C, inner, out_idx.data_ptr(),
                                              out_count.data_ptr(), _stream(x)),
                "tp_nan_any_dim1_static")
+
+
+# ---------------------------------------------------------------- fp32-accurate layer engine
+def tf32_split(x):
+    """(hi, lo) with hi = x truncated to TF32 and lo = x - hi (both fp32, x = hi + lo exactly)."""
+    x = _cuda_f32(x, "x")
+    hi, lo = torch.empty_like(x), torch.empty_like(x)
+    with torch.cuda.device(x.device), _launch("tf32_split", 12 * x.numel(), x):
+        _check(load().tp_tf32_split(x.data_ptr(), x.numel(), hi.data_ptr(), lo.data_ptr(), _stream(x)),
+               "tp_tf32_split")
+    return hi, lo
+
+
+def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, out=None):
+    """y = act(conv(x, w) * scale + shift) on tcgen05 with 3xTF32 products.  x_*: NHWC
+    [N,H,W,Cin]; w_*: [Cout, taps*Cin].  Returns (y_hi, y_lo) or (y, None) when split=False."""
+    x_hi, x_lo = _cuda_f32(x_hi, "x_hi"), _cuda_f32(x_lo, "x_lo")
+    N, H, W, Cin = x_hi.shape
+    Cout = w_hi.shape[0]
+    if w_hi.shape[1] != taps * Cin or w_lo.shape != w_hi.shape or x_lo.shape != x_hi.shape:
+        raise TorchPrunerB200Error("conv_tf32x3: operand shapes do not match")
+    if out is None:
+        y_hi = torch.empty((N, H, W, Cout), dtype=torch.float32, device=x_hi.device)
+        y_lo = torch.empty_like(y_hi) if split else None
+    else:
+        y_hi, y_lo = out
+    flops = 2 * N * H * W * Cout * taps * Cin
+    nbytes = 4 * (2 * x_hi.numel() + 2 * w_hi.numel() + (2 if split else 1) * y_hi.numel())
+    with torch.cuda.device(x_hi.device), _launch("conv_tf32x3", nbytes, x_hi, 1, flops):
+        _check(load().tp_conv_tf32x3(
+            x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
+            int(taps), Cout, scale.data_ptr(), shift.data_ptr(), int(bool(relu)), y_hi.data_ptr(),
+            y_lo.data_ptr() if y_lo is not None else 0, _stream(x_hi)), "tp_conv_tf32x3")
+    return y_hi, y_lo
+
+
+def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo):
+    """NHWC TF32-split stack of P prefix-masked copies of the NCHW activation z (optionally
+    2x2 max-pooled first).  out_*: preallocated, at least P*B*H'*W'*C floats."""
+    z = _cuda_f32(z, "z")
+    if z.dim() != 4:
+        raise TorchPrunerB200Error("mask_stack_nhwc expects a [B,C,H,W] activation")
+    B, C, H, W = z.shape
+    Ho, Wo = (H // 2, W // 2) if pool else (H, W)
+    need = P * B * Ho * Wo * C
+    if out_hi.numel() < need or out_lo.numel() < need:
+        raise TorchPrunerB200Error("mask_stack_nhwc: output buffers too small")
+    with torch.cuda.device(z.device), _launch("mask_stack_nhwc", 4 * z.numel() + 8 * need, z):
+        _check(load().tp_mask_stack_nhwc(z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H,
+                                         W, int(bool(pool)), out_hi.data_ptr(), out_lo.data_ptr(),
+                                         _stream(z)), "tp_mask_stack_nhwc")
+    shape = (P * B, Ho, Wo, C)
+    return out_hi[:need].view(shape), out_lo[:need].view(shape)
+
+
+def maxpool2_split_nhwc(x):
+    x = _cuda_f32(x, "x")
+    N, H, W, C = x.shape
+    hi = torch.empty((N, H // 2, W // 2, C), dtype=torch.float32, device=x.device)
+    lo = torch.empty_like(hi)
+    with torch.cuda.device(x.device), _launch("maxpool2_split_nhwc", 4 * x.numel() + 8 * hi.numel(), x):
+        _check(load().tp_maxpool2_split_nhwc(x.data_ptr(), N, H, W, C, hi.data_ptr(), lo.data_ptr(),
+                                             _stream(x)), "tp_maxpool2_split_nhwc")
+    return hi, lo

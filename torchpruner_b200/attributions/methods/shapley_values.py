@@ -8,6 +8,7 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
+from ..native_tail import NativeTail
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -76,6 +77,9 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         self.shard = os.environ.get("TORCHPRUNER_B200_SHARD", "0") == "1"
         self.max_stack_bytes = int(os.environ.get("TORCHPRUNER_B200_STACK_MB", "512")) << 20
         self.max_stack = int(os.environ.get("TORCHPRUNER_B200_MAX_STACK", "512"))
+        # "auto": run recognised conv/BN/ReLU/pool/linear tails on the tcgen05 3xTF32 engine after
+        # checking it against forward_partial; False: always call forward_partial.
+        self.native_tail = os.environ.get("TORCHPRUNER_B200_NATIVE", "1") != "0" and "auto"
         self.last_run_info = {}
 
     def run(self, module, sv_samples=None, **kwargs):
@@ -150,6 +154,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         row = 0
         n_evals = 0
         stack_safe = self._stack_safe()
+        native = None
+        native_info = {}
 
         with torch.no_grad():
             for x, y in self._batches():
@@ -174,23 +180,46 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
 
                 loss0 = self._per_example(original_loss, B)
                 fused_ce = self._fused_ce_ok(logits0, y, loss0)
-                bytes_per_copy = max(1, z.numel() * 4)
-                P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // bytes_per_copy)))
-                stack = torch.empty((P_max * B,) + tuple(z.shape[1:]), dtype=torch.float32,
-                                    device=z.device)
                 prev_a = torch.empty(B, dtype=torch.float32, device=z.device)
                 prev_b = torch.empty_like(prev_a)
                 y_stack = None
 
+                # --- how the layers after `module` are executed for this batch
+                native = None
+                if self.native_tail and stack_safe and spans:
+                    native = NativeTail.build(self.model, module, z)
+                if native is not None:
+                    per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
+                    P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
+                    buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
+                                         dtype=torch.float32, device=z.device)
+                    buf_lo = torch.empty_like(buf_hi)
+                    j0, k0v, _ = spans[0]
+                    ok, verr = native.verify(self.model, module, z, inv_dev[j0], k0v, min(2, n),
+                                             buf_hi, buf_lo)
+                    native_info = {"verified": ok, "verify_rel_err": verr}
+                    if not ok:
+                        native = None
+                        del buf_hi, buf_lo
+                if native is None:
+                    bytes_per_copy = max(1, z.numel() * 4)
+                    P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // bytes_per_copy)))
+                    stack = torch.empty((P_max * B,) + tuple(z.shape[1:]), dtype=torch.float32,
+                                        device=z.device)
+
                 def evaluate(j, k0, P, prev_in, prev_out, scatter_from):
                     nonlocal y_stack
-                    masked = _lib.prefix_mask_stack(z, inv_dev[j], k0, P, out=stack)[:P * B]
-                    if stack_safe:
-                        out = self.model.forward_partial(masked, to_module=None, from_module=module)
+                    if native is not None:
+                        out = native.logits(z, inv_dev[j], k0, P, buf_hi, buf_lo)
                     else:
-                        out = torch.cat([
-                            self.model.forward_partial(masked[p * B:(p + 1) * B], to_module=None,
-                                                       from_module=module) for p in range(P)], 0)
+                        masked = _lib.prefix_mask_stack(z, inv_dev[j], k0, P, out=stack)[:P * B]
+                        if stack_safe:
+                            out = self.model.forward_partial(masked, to_module=None,
+                                                             from_module=module)
+                        else:
+                            out = torch.cat([
+                                self.model.forward_partial(masked[p * B:(p + 1) * B], to_module=None,
+                                                           from_module=module) for p in range(P)], 0)
                     if fused_ce:
                         _lib.loss_delta_scatter(out.float().contiguous(), y, _lib.TP_LOSS_CE,
                                                 prev_in, prev_out, perm_dev[j], k0, P, B,
@@ -224,7 +253,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
             if world > 1:
                 allreduce_scores(sv, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
-                                  "stacked": stack_safe}
+                                  "stacked": stack_safe, "native_tail": native is not None,
+                                  "native": native_info}
             return sv
 
     # ------------------------------------------------------------------ slow path

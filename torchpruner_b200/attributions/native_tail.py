@@ -1,0 +1,223 @@
+"""fp32-accurate tensor-core execution of the layers after the evaluation module.
+
+The reference evaluates every Shapley mask by calling the user's ``forward_partial`` — an opaque
+callback (attributions.py:85).  When the layers it runs form a plain chain of
+Conv2d(3x3, stride 1, pad 1) / BatchNorm2d / ReLU / MaxPool2d(2) / Flatten / Dropout / Linear
+modules in eval mode (every VGG-style tail does), the same arithmetic is executed here by
+``tp_conv_tf32x3`` (tcgen05, 3xTF32, NHWC) instead of by cuDNN/cuBLAS kernels:
+
+* the chain is *discovered*, not assumed: one ``forward_partial`` call on the unmasked
+  activation is traced with forward hooks; anything that is not a supported leaf module applied
+  to the previous module's output disqualifies the tail and the generic path is used;
+* the plan is *verified* before it is trusted: its logits for the first masks of the run are
+  compared with the user's ``forward_partial`` on the same masked activations.
+
+BatchNorm (eval) and the conv/linear bias are folded into one per-channel scale/shift applied in
+the kernel's epilogue; ReLU is fused; a MaxPool that follows is a separate NHWC kernel that also
+re-splits the result into its TF32 hi/lo pair.
+"""
+import torch
+import torch.nn as nn
+
+from .. import _lib
+
+VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+
+
+class _Unsupported(Exception):
+    pass
+
+
+def _trace_chain(model, z, module):
+    """Leaf modules executed by ``model.forward_partial(z, from_module=module)``, in order, with
+    the tensors they consumed and produced."""
+    calls = []
+    handles = []
+
+    def hook(mod, inputs, output):
+        if len(inputs) != 1 or not isinstance(inputs[0], torch.Tensor) or \
+                not isinstance(output, torch.Tensor):
+            raise _Unsupported(f"{type(mod).__name__} is not a single-tensor layer")
+        calls.append((mod, inputs[0], output))
+
+    for m in model.modules():
+        if len(list(m.children())) == 0:
+            handles.append(m.register_forward_hook(hook))
+    try:
+        with torch.no_grad():
+            logits = model.forward_partial(z, to_module=None, from_module=module)
+    finally:
+        for h in handles:
+            h.remove()
+    return calls, logits
+
+
+def _is_pool2(m):
+    def pair(v):
+        return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+    return (isinstance(m, nn.MaxPool2d) and pair(m.kernel_size) == (2, 2) and
+            pair(m.stride if m.stride is not None else m.kernel_size) == (2, 2) and
+            pair(m.padding) == (0, 0) and pair(m.dilation) == (1, 1) and not m.ceil_mode and
+            not m.return_indices)
+
+
+class NativeTail:
+    """Execution plan for one evaluation module of one model."""
+
+    def __init__(self, steps, pool_first, in_shape, n_out):
+        self.steps = steps            # list of dicts
+        self.pool_first = pool_first
+        self.in_shape = in_shape      # (C, H, W) of the evaluation module's output
+        self.n_out = n_out
+        self.flops_per_example = sum(s["flops"] for s in steps)
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def build(cls, model, module, z):
+        """Plan for the layers after ``module`` given a sample activation ``z`` — or None when
+        the tail is not a supported chain.  Never raises for an unsupported model."""
+        try:
+            return cls._build(model, module, z)
+        except _Unsupported:
+            return None
+
+    @classmethod
+    def _build(cls, model, module, z):
+        if z.dim() not in (2, 4) or z.dtype != torch.float32:
+            raise _Unsupported("activation rank/dtype")
+        calls, logits = _trace_chain(model, z, module)
+        if not calls or logits.dim() != 2:
+            raise _Unsupported("empty tail or non-matrix output")
+        # must be a chain: each layer consumes the previous layer's output (possibly reshaped)
+        prev = z
+        for mod, inp, out in calls:
+            same = inp is prev or (inp.data_ptr() == prev.data_ptr() and inp.numel() == prev.numel())
+            if not same:
+                raise _Unsupported("tail is not a simple chain")
+            if mod.training and isinstance(mod, (nn.modules.batchnorm._BatchNorm,
+                                                 nn.modules.dropout._DropoutNd)):
+                raise _Unsupported("train-mode BatchNorm/Dropout")
+            prev = out
+        if prev is not logits and prev.data_ptr() != logits.data_ptr():
+            raise _Unsupported("output is not the last layer's output")
+
+        mods = [c[0] for c in calls]
+        C = z.shape[1]
+        H, W = (z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1)
+        i = 0
+        pool_first = False
+        if mods and _is_pool2(mods[0]):
+            if H % 2 or W % 2:
+                raise _Unsupported("odd spatial size before pooling")
+            pool_first, H, W, i = True, H // 2, W // 2, 1
+        steps = []
+        flat = z.dim() == 2
+        dev = z.device
+        while i < len(mods):
+            m = mods[i]
+            if isinstance(m, (nn.Dropout, nn.Dropout2d, nn.Identity)):
+                i += 1
+                continue
+            if isinstance(m, nn.Flatten):
+                if m.start_dim != 1 or m.end_dim not in (-1, 3):
+                    raise _Unsupported("Flatten dims")
+                flat = True
+                i += 1
+                continue
+            if isinstance(m, nn.Conv2d):
+                if flat or m.kernel_size != (3, 3) or m.stride != (1, 1) or m.padding != (1, 1) or \
+                        m.dilation != (1, 1) or m.groups != 1 or m.padding_mode != "zeros" or \
+                        m.in_channels != C:
+                    raise _Unsupported("conv geometry")
+                w = m.weight.detach().float().permute(0, 2, 3, 1).reshape(m.out_channels, 9 * C)
+                taps, cout = 9, m.out_channels
+                bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
+            elif isinstance(m, nn.Linear):
+                calls_in = calls[i][1]
+                if calls_in.dim() != 2 or m.in_features != C * H * W:
+                    raise _Unsupported("linear geometry")
+                w = m.weight.detach().float()
+                if H * W > 1:  # NCHW flatten order -> NHWC flatten order
+                    w = w.view(m.out_features, C, H * W).permute(0, 2, 1).reshape(m.out_features, -1)
+                C, H, W = C * H * W, 1, 1
+                flat = True
+                taps, cout = 1, m.out_features
+                bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
+            else:
+                raise _Unsupported(f"unsupported layer {type(m).__name__}")
+            if C % 32 or 128 % W or not ((128 // W) % H == 0 or H % (128 // W) == 0):
+                raise _Unsupported("channel / spatial size not tileable")
+            scale = torch.ones(cout, device=dev)
+            shift = bias.clone()
+            i += 1
+            if i < len(mods) and isinstance(mods[i], nn.BatchNorm2d) and taps == 9:
+                bn = mods[i]
+                if not bn.track_running_stats or bn.running_mean is None:
+                    raise _Unsupported("BatchNorm without running statistics")
+                a = (bn.running_var.detach().double() + bn.eps).rsqrt()
+                if bn.affine:
+                    a = a * bn.weight.detach().double()
+                shift = (bias.double() - bn.running_mean.detach().double()) * a
+                if bn.affine:
+                    shift = shift + bn.bias.detach().double()
+                scale, shift = a.float(), shift.float()
+                i += 1
+            relu = False
+            if i < len(mods) and isinstance(mods[i], nn.ReLU):
+                relu = True
+                i += 1
+            pool = False
+            if i < len(mods) and _is_pool2(mods[i]) and taps == 9:
+                if H % 2 or W % 2:
+                    raise _Unsupported("odd spatial size before pooling")
+                pool = True
+                i += 1
+            w_hi, w_lo = _lib.tf32_split(w.contiguous())
+            steps.append({"taps": taps, "cin": C, "cout": cout, "H": H, "W": W, "relu": relu,
+                          "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale.contiguous(),
+                          "shift": shift.contiguous(), "flops": 2 * H * W * cout * taps * C})
+            C = cout
+            if pool:
+                H, W = H // 2, W // 2
+        if not steps or steps[-1]["relu"] or steps[-1]["pool"] or steps[-1]["cout"] != logits.shape[1] \
+                or H * W != 1:
+            raise _Unsupported("tail does not end in a linear read-out")
+        in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
+        return cls(steps, pool_first, in_shape, logits.shape[1])
+
+    # ------------------------------------------------------------------ execution
+    def stack_elems(self, B, P):
+        C, H, W = self.in_shape
+        if self.pool_first:
+            H, W = H // 2, W // 2
+        return P * B * C * H * W
+
+    def logits(self, z, inv_perm, k0, P, buf_hi, buf_lo):
+        """[P*B, n_out] fp32 logits of the P prefix masks k0 .. k0+P-1 of one permutation."""
+        z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
+        x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo)
+        last = len(self.steps) - 1
+        for idx, s in enumerate(self.steps):
+            n = x_hi.shape[0]
+            if s["taps"] == 1 and x_hi.dim() == 4 and x_hi.shape[1] * x_hi.shape[2] != 1:
+                x_hi = x_hi.reshape(n, 1, 1, -1)
+                x_lo = x_lo.reshape(n, 1, 1, -1)
+            split = not (idx == last or s["pool"])
+            y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w_hi"], s["w_lo"], s["taps"], s["scale"],
+                                          s["shift"], s["relu"], split=split)
+            if s["pool"]:
+                y_hi, y_lo = _lib.maxpool2_split_nhwc(y_hi)
+            x_hi, x_lo = y_hi, y_lo
+        return x_hi.view(x_hi.shape[0], self.n_out)
+
+    def verify(self, model, module, z, inv_perm, k0, P, buf_hi, buf_lo):
+        """True iff the plan reproduces ``forward_partial`` on P real masks of this run."""
+        mine = self.logits(z, inv_perm, k0, P, buf_hi, buf_lo)
+        stacked = _lib.prefix_mask_stack(z, inv_perm, k0, P)
+        with torch.no_grad():
+            ref = model.forward_partial(stacked, to_module=None, from_module=module)
+        if ref.shape != mine.shape:
+            return False, float("inf")
+        scale = float(ref.abs().max().clamp_min(1e-30))
+        err = float((ref - mine).abs().max()) / scale
+        return err <= VERIFY_RTOL, err

@@ -1,0 +1,632 @@
+// fp32-accurate conv3x3 / linear + per-channel affine (+ReLU) on the 5th-gen tensor cores.
+//
+// This is the downstream-layer engine of batched Shapley scoring (reference
+// shapley_values.py:57 -> attributions.py:85: every marginal evaluation re-runs all layers after
+// the evaluation module).  Scores are sums of differences of losses, so TF32/BF16 rounding of the
+// operands is not admissible; the layers must be fp32-accurate.  Each fp32 operand
+// x is therefore carried as two TF32-exact terms, hi = rn_tf32(x) and lo = rn_tf32(x - hi)
+// (x = hi + lo up to 2^-23 relative), and a product is formed as hi*hi + hi*lo + lo*hi on
+// tcgen05.mma.kind::tf32 with fp32 accumulation in TMEM ("3xTF32"; the dropped lo*lo term is
+// 2^-22 relative).
+//
+// Formulation: implicit GEMM over NHWC activations.  D[m, n] = sum_k A[m, k] * B[n, k] with
+//   m = output pixel (image, y, x), n = output channel, k = (tap r, s; input channel c).
+// One CTA computes a 128-pixel x BLOCK_N-channel tile.  A 128-pixel tile is a rectangular box of
+// the [N, H, W] pixel grid (bn images x bh rows x all W columns), so for tap (r, s) its A operand
+// is ONE 4-D TMA tile load at coordinates (c0, s-1, h0+r-1, n0): out-of-range coordinates are
+// zero-filled by the TMA unit, which is exactly the conv's zero padding.  Weights are stored
+// [Cout][taps*Cin] (K-major) and arrive by 2-D TMA.  Both land in shared memory in the 128-byte
+// swizzled K-major layout the UMMA shared-memory descriptors expect.
+//
+// Accumulation.  The tensor core adds into its fp32 accumulator with truncation, not
+// round-to-nearest: left alone, the error of a K-long dot product grows linearly with the number
+// of MMA steps (measured 4e-6 relative at K = 576, 3.5e-5 at K = 4608 — far from fp32).  So the
+// TMEM accumulator is only trusted over `promote` k-blocks (64 inputs by default): after that the
+// partial sum is read out by the epilogue warps and added, with IEEE rounding, into per-thread
+// fp32 registers while the next partial sum accumulates in a second TMEM buffer.
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA
+// issuer (one lane), warps 2-5 = epilogue (TMEM -> registers -> scale/shift/ReLU -> hi/lo split
+// -> global).  smem ring of 3-4 stages with full/empty mbarriers; tcgen05.commit releases a stage
+// when the MMAs that read it have finished, and signals the epilogue after the last k-block.
+#include "common.cuh"
+
+#include <cuda.h>
+
+namespace tp {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 32;  // fp32 per k-block: 128 bytes = one swizzle row
+constexpr int kConvThreads = 192;
+
+struct ConvGeom {
+  int N, H, W, Cin, Cout;
+  int taps;      // 9: 3x3 stride 1 pad 1;  1: 1x1 / linear
+  int bw, bh, bn;  // pixel box of an M tile, bw*bh*bn == 128, bw == W
+  int tiles_h;   // M tiles per image (bn == 1) else 1
+  int num_kb;    // taps * Cin / 32
+  int relu;
+  int split;     // 1: y_hi/y_lo get the TF32 split of the result; 0: y_hi gets the raw fp32
+  int promote;   // k-blocks accumulated in TMEM before the partial sum is folded into registers
+  long long m_total;
+};
+
+template <int BLOCK_N>
+struct ConvCfg {
+  static constexpr int kABytes = kBlockM * kBlockK * 4;
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 4;
+  static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
+  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;
+  static constexpr int kTmemCols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;  // two accumulators
+  static constexpr int kSmemBytes =
+      kStages * kStageBytes + 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BLOCK_N * 4;
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, int c0, int c1,
+                                            int c2, int c3, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int c1,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_dst)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+               : "memory");
+}
+// tcgen05.commit: the mbarrier gets one arrival when every MMA issued so far by this thread has
+// completed (implies tcgen05.fence::before_thread_sync).
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], TF32 inputs, fp32 accumulate.
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Shared-memory matrix descriptor, K-major, 128-byte swizzle: rows of 128 bytes, 8-row swizzle
+// atoms 1024 bytes apart (SBO), version 1 (Blackwell), layout type 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void* smem_tile) {
+  const uint64_t addr = (uint64_t)((smem_u32(smem_tile) & 0x3FFFFu) >> 4);
+  return addr | (1ull << 16) /*LBO (ignored for swizzled K-major)*/ |
+         ((uint64_t)(1024 >> 4) << 32) /*SBO*/ | (1ull << 46) /*version*/ | (2ull << 61);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, "
+      "%20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Round-to-nearest TF32 (10 explicit mantissa bits, low 13 bits of the fp32 pattern zero).
+// Both terms of the split are rounded to nearest: truncation would bias every product the same
+// way and the bias grows like K instead of sqrt(K) over a K-long dot product (measured: 5e-6
+// relative with truncation vs < 1e-6 with rounding at K = 576).
+__device__ __forceinline__ float tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float tf32_lo(float x, float hi) { return tf32_hi(x - hi); }
+
+// ---- the kernel ------------------------------------------------------------------------
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
+                   const __grid_constant__ CUtensorMap tm_a_lo,
+                   const __grid_constant__ CUtensorMap tm_b_hi,
+                   const __grid_constant__ CUtensorMap tm_b_lo, const ConvGeom g,
+                   const float* __restrict__ scale, const float* __restrict__ shift,
+                   float* __restrict__ y_hi, float* __restrict__ y_lo) {
+  using Cfg = ConvCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  // 128-byte swizzle atoms must sit on 1024-byte boundaries of the shared address space.
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty = full + Cfg::kStages;
+  uint64_t* acc_full = empty + Cfg::kStages;   // [2] MMA -> epilogue: partial sum complete
+  uint64_t* acc_empty = acc_full + 2;          // [2] epilogue -> MMA: TMEM buffer drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* s_scale = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
+  float* s_shift = s_scale + BLOCK_N;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int mt = blockIdx.x;
+  const int nt = blockIdx.y;
+  int n0, h0;
+  if (g.bn == 1) {
+    n0 = mt / g.tiles_h;
+    h0 = (mt - n0 * g.tiles_h) * g.bh;
+  } else {
+    n0 = mt * g.bn;
+    h0 = 0;
+  }
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tm_a_hi);
+    prefetch_tensormap(&tm_a_lo);
+    prefetch_tensormap(&tm_b_hi);
+    prefetch_tensormap(&tm_b_lo);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);  // one arrival per epilogue warp
+    }
+    fence_mbar_init();
+  } else if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  } else if (warp >= 2) {
+    for (int j = threadIdx.x - 64; j < BLOCK_N; j += kConvThreads - 64) {
+      const int col = nt * BLOCK_N + j;
+      s_scale[j] = col < g.Cout ? scale[col] : 0.f;
+      s_shift[j] = col < g.Cout ? shift[col] : 0.f;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      const int kc = g.Cin / kBlockK;
+      int stage = 0;
+      uint32_t phase = 0;
+      int tap = 0, cb = 0;
+      for (int kb = 0; kb < g.num_kb; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1u);
+        mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+        uint8_t* st = smem + stage * Cfg::kStageBytes;
+        const int r = (g.taps == 9) ? tap / 3 : 1;
+        const int s = (g.taps == 9) ? tap - r * 3 : 1;
+        tma_load_4d(st, &tm_a_hi, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
+        tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
+        tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
+        tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK, nt * BLOCK_N,
+                    &full[stage]);
+        if (++cb == kc) {
+          cb = 0;
+          ++tap;
+        }
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      // Instruction descriptor: D=F32 (bits 4-5 = 1), A=B=TF32 (bits 7-9, 10-12 = 2), both
+      // K-major, N>>3 at bit 17, M>>4 at bit 24.
+      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
+                                 ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int chunk = 0, in_chunk = 0;
+      for (int kb = 0; kb < g.num_kb; ++kb) {
+        const int buf = chunk & 1;
+        if (in_chunk == 0) {  // this TMEM buffer must have been drained (2 chunks ago)
+          mbar_wait(&acc_empty[buf], (uint32_t)(((chunk >> 1) & 1) ^ 1));
+          tc_fence_after();
+        }
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        uint8_t* st = smem + stage * Cfg::kStageBytes;
+        const uint64_t a_hi = umma_desc_sw128(st);
+        const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
+        const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
+        const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+#pragma unroll
+        for (int kk = 0; kk < kBlockK / 8; ++kk) {
+          const uint64_t off = (uint64_t)(kk * 32 >> 4);  // 8 tf32 = 32 bytes inside the swizzle row
+          // small cross terms first, the dominant hi*hi term last
+          umma_tf32(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+          umma_tf32(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+          umma_tf32(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+        }
+        umma_commit(&empty[stage]);  // stage reusable once these MMAs have read it
+        if (++stage == Cfg::kStages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+        if (++in_chunk == g.promote || kb == g.num_kb - 1) {
+          umma_commit(&acc_full[buf]);  // partial sum of this chunk complete
+          in_chunk = 0;
+          ++chunk;
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: fold partial sums (TMEM -> registers), then affine / ReLU / split =====
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    const long long m = (long long)mt * kBlockM + row;
+    const bool live = m < g.m_total;
+    constexpr int kChunk = BLOCK_N >= 32 ? 32 : 16;
+    float acc[BLOCK_N];
+#pragma unroll
+    for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
+    const int n_chunks = (g.num_kb + g.promote - 1) / g.promote;
+    for (int chunk = 0; chunk < n_chunks; ++chunk) {
+      const int buf = chunk & 1;
+      mbar_wait(&acc_full[buf], (uint32_t)((chunk >> 1) & 1));
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+#pragma unroll
+      for (int c0 = 0; c0 < BLOCK_N; c0 += kChunk) {
+        uint32_t v[32];
+        if (kChunk == 32) {
+          tmem_ld32(taddr + c0, v);
+        } else {
+          tmem_ld16(taddr + c0, v);
+        }
+#pragma unroll
+        for (int j = 0; j < kChunk; ++j) acc[c0 + j] += __uint_as_float(v[j]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+    float* out_hi = y_hi + m * g.Cout + (long long)nt * BLOCK_N;
+    float* out_lo = y_lo ? y_lo + m * g.Cout + (long long)nt * BLOCK_N : nullptr;
+    const bool vec_ok = (g.Cout % 4 == 0);
+#pragma unroll
+    for (int c0 = 0; c0 < BLOCK_N; c0 += kChunk) {
+      float y[kChunk];
+#pragma unroll
+      for (int j = 0; j < kChunk; ++j) {
+        float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+        if (g.relu) t = fmaxf(t, 0.f);
+        y[j] = t;
+      }
+      if (live) {
+        const int col0 = nt * BLOCK_N + c0;
+        if (vec_ok && col0 + kChunk <= g.Cout) {
+#pragma unroll
+          for (int j = 0; j < kChunk; j += 4) {
+            if (g.split) {
+              const float4 hi = make_float4(tf32_hi(y[j]), tf32_hi(y[j + 1]), tf32_hi(y[j + 2]),
+                                            tf32_hi(y[j + 3]));
+              const float4 lo = make_float4(tf32_lo(y[j], hi.x), tf32_lo(y[j + 1], hi.y),
+                                            tf32_lo(y[j + 2], hi.z), tf32_lo(y[j + 3], hi.w));
+              *reinterpret_cast<float4*>(out_hi + c0 + j) = hi;
+              *reinterpret_cast<float4*>(out_lo + c0 + j) = lo;
+            } else {
+              *reinterpret_cast<float4*>(out_hi + c0 + j) =
+                  make_float4(y[j], y[j + 1], y[j + 2], y[j + 3]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < kChunk; ++j) {
+            if (col0 + j < g.Cout) {
+              if (g.split) {
+                const float hi = tf32_hi(y[j]);
+                out_hi[c0 + j] = hi;
+                out_lo[c0 + j] = tf32_lo(y[j], hi);
+              } else {
+                out_hi[c0 + j] = y[j];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---- small elementwise companions ------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tf32_split_kernel(const float* __restrict__ x, long long n, float* __restrict__ hi,
+                  float* __restrict__ lo) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += gridDim.x * (long long)blockDim.x) {
+    const float v = x[i];
+    const float h = tf32_hi(v);
+    hi[i] = h;
+    lo[i] = tf32_lo(v, h);
+  }
+}
+
+// z: NCHW [B, C, H, W].  out: NHWC [P*B, Ho, Wo, C] hi/lo of the (optionally 2x2 max-pooled)
+// activation with the first (k0+p+1) channels of the permutation zeroed.  Pooling commutes with
+// the per-channel mask, so it is applied once, before the P-fold replication.
+__global__ void __launch_bounds__(256)
+mask_stack_nhwc_kernel(const float* __restrict__ z, const int32_t* __restrict__ inv_perm,
+                       long long k0, int P, int B, int C, int H, int W, int pool,
+                       float* __restrict__ out_hi, float* __restrict__ out_lo) {
+  const int Ho = pool ? H / 2 : H, Wo = pool ? W / 2 : W;
+  const long long per_copy = (long long)B * Ho * Wo * C;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < per_copy;
+       e += gridDim.x * (long long)blockDim.x) {
+    const int c = (int)(e % C);
+    long long t = e / C;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int b = (int)(t / Ho);
+    const float* src = z + (((long long)b * C + c) * H) * W;
+    float v;
+    if (pool) {
+      const float* p0 = src + (2 * ho) * W + 2 * wo;
+      v = fmaxf(fmaxf(p0[0], p0[1]), fmaxf(p0[W], p0[W + 1]));
+    } else {
+      v = src[ho * W + wo];
+    }
+    const float h = tf32_hi(v);
+    const float l = tf32_lo(v, h);
+    const long long pos = (long long)inv_perm[c] - k0;  // masked for every p >= pos
+    for (int p = 0; p < P; ++p) {
+      const bool masked = p >= pos;
+      out_hi[p * per_copy + e] = masked ? 0.f : h;
+      out_lo[p * per_copy + e] = masked ? 0.f : l;
+    }
+  }
+}
+
+// x: NHWC raw fp32 [N, H, W, C] -> 2x2 max pool -> hi/lo [N, H/2, W/2, C].  C % 4 == 0.
+__global__ void __launch_bounds__(256)
+maxpool2_split_nhwc_kernel(const float* __restrict__ x, long long N, int H, int W, int C,
+                           float* __restrict__ hi, float* __restrict__ lo) {
+  const int Ho = H / 2, Wo = W / 2, C4 = C / 4;
+  const long long total = N * Ho * Wo * C4;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += gridDim.x * (long long)blockDim.x) {
+    const int c4 = (int)(e % C4);
+    long long t = e / C4;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const long long n = t / Ho;
+    const long long base = ((n * H + 2 * ho) * W + 2 * wo) * C4 + c4;
+    const float4 a = x4[base], b = x4[base + C4], c = x4[base + (long long)W * C4],
+                 d = x4[base + (long long)W * C4 + C4];
+    float4 m;
+    m.x = fmaxf(fmaxf(a.x, b.x), fmaxf(c.x, d.x));
+    m.y = fmaxf(fmaxf(a.y, b.y), fmaxf(c.y, d.y));
+    m.z = fmaxf(fmaxf(a.z, b.z), fmaxf(c.z, d.z));
+    m.w = fmaxf(fmaxf(a.w, b.w), fmaxf(c.w, d.w));
+    const float4 h = make_float4(tf32_hi(m.x), tf32_hi(m.y), tf32_hi(m.z), tf32_hi(m.w));
+    reinterpret_cast<float4*>(hi)[e] = h;
+    reinterpret_cast<float4*>(lo)[e] = make_float4(tf32_lo(m.x, h.x), tf32_lo(m.y, h.y),
+                                                   tf32_lo(m.z, h.z), tf32_lo(m.w, h.w));
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+static int make_map(CUtensorMap* map, const float* base, int rank, const cuuint64_t* dims,
+                    const cuuint32_t* box) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  TP_REQUIRE(fn != nullptr, TP_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+  cuuint64_t strides[4];
+  cuuint64_t acc = 4;
+  for (int i = 0; i < rank - 1; ++i) {
+    acc *= dims[i];
+    strides[i] = acc;
+  }
+  const cuuint32_t ones[4] = {1, 1, 1, 1};
+  const CUresult rc =
+      fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float*>(base), dims,
+         strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TP_REQUIRE(rc == CUDA_SUCCESS, TP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d",
+             (int)rc);
+  return TP_OK;
+}
+
+template <int BLOCK_N>
+static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const float* w_hi,
+                       const float* w_lo, const ConvGeom& g, const float* scale,
+                       const float* shift, float* y_hi, float* y_lo, cudaStream_t st) {
+  using Cfg = ConvCfg<BLOCK_N>;
+  CUtensorMap b_hi, b_lo;
+  const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
+  const cuuint32_t bbox[2] = {kBlockK, BLOCK_N};
+  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox);
+  if (rc != TP_OK) return rc;
+  rc = make_map(&b_lo, w_lo, 2, bdims, bbox);
+  if (rc != TP_OK) return rc;
+  auto kern = conv_tf32x3_kernel<BLOCK_N>;
+  TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  const long long m_tiles = (g.m_total + kBlockM - 1) / kBlockM;
+  const int n_tiles = (g.Cout + BLOCK_N - 1) / BLOCK_N;
+  dim3 grid((unsigned)m_tiles, (unsigned)n_tiles);
+  kern<<<grid, kConvThreads, Cfg::kSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g, scale, shift, y_hi,
+                                                    y_lo);
+  TP_LAUNCH_CHECK("conv_tf32x3_kernel");
+  return TP_OK;
+}
+
+static inline unsigned ew_grid(long long items) {
+  long long blocks = (items + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+}  // namespace tp
+
+extern "C" {
+
+int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
+                   int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
+                   const float* scale, const float* shift, int relu, float* y_hi, float* y_lo,
+                   tp_stream_t stream) {
+  using namespace tp;
+  TP_REQUIRE(N >= 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, TP_ERR_INVALID,
+             "tp_conv_tf32x3: bad dimension");
+  TP_REQUIRE(taps == 1 || taps == 9, TP_ERR_INVALID, "tp_conv_tf32x3: taps must be 1 or 9");
+  TP_REQUIRE(Cin % kBlockK == 0, TP_ERR_LIMIT, "tp_conv_tf32x3: Cin must be a multiple of 32");
+  TP_REQUIRE(W <= 128 && (128 % W) == 0, TP_ERR_LIMIT,
+             "tp_conv_tf32x3: W must divide 128 (got %lld)", (long long)W);
+  if (N == 0) return TP_OK;
+  TP_REQUIRE(x_hi && x_lo && w_hi && w_lo && scale && shift && y_hi, TP_ERR_INVALID,
+             "tp_conv_tf32x3: NULL pointer");
+  TP_REQUIRE(N * H * W < (1ll << 31) && N < (1ll << 31), TP_ERR_LIMIT,
+             "tp_conv_tf32x3: too many pixels");
+  ConvGeom g;
+  g.N = (int)N;
+  g.H = (int)H;
+  g.W = (int)W;
+  g.Cin = (int)Cin;
+  g.Cout = (int)Cout;
+  g.taps = taps;
+  g.bw = (int)W;
+  const int rows = 128 / (int)W;  // pixel rows per tile
+  if (rows <= H) {
+    TP_REQUIRE(H % rows == 0, TP_ERR_LIMIT, "tp_conv_tf32x3: H must be a multiple of %d", rows);
+    g.bh = rows;
+    g.bn = 1;
+    g.tiles_h = (int)H / rows;
+  } else {
+    TP_REQUIRE(rows % H == 0, TP_ERR_LIMIT, "tp_conv_tf32x3: H*W must divide 128");
+    g.bh = (int)H;
+    g.bn = rows / (int)H;
+    g.tiles_h = 1;
+  }
+  g.num_kb = taps * (int)(Cin / kBlockK);
+  g.relu = relu;
+  g.split = (y_lo != nullptr);
+  g.promote = tuning().conv_promote;
+  g.m_total = N * H * W;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  CUtensorMap a_hi, a_lo;
+  const cuuint64_t adims[4] = {(cuuint64_t)Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  const cuuint32_t abox[4] = {kBlockK, (cuuint32_t)g.bw, (cuuint32_t)g.bh, (cuuint32_t)g.bn};
+  int rc = make_map(&a_hi, x_hi, 4, adims, abox);
+  if (rc != TP_OK) return rc;
+  rc = make_map(&a_lo, x_lo, 4, adims, abox);
+  if (rc != TP_OK) return rc;
+  if (Cout <= 16)
+    return launch_conv<16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+  if (Cout <= 64)
+    return launch_conv<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+  return launch_conv<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+}
+
+int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t stream) {
+  TP_REQUIRE(n >= 0, TP_ERR_INVALID, "tp_tf32_split: negative size");
+  if (n == 0) return TP_OK;
+  TP_REQUIRE(x && hi && lo, TP_ERR_INVALID, "tp_tf32_split: NULL pointer");
+  tp::tf32_split_kernel<<<tp::ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, hi, lo);
+  TP_LAUNCH_CHECK("tf32_split_kernel");
+  return TP_OK;
+}
+
+int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
+                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
+                       tp_stream_t stream) {
+  TP_REQUIRE(P >= 0 && B >= 0 && C >= 0 && H >= 0 && W >= 0 && k0 >= 0, TP_ERR_INVALID,
+             "tp_mask_stack_nhwc: negative dimension");
+  TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
+             "tp_mask_stack_nhwc: pooling needs even H and W");
+  const long long per_copy = B * (pool ? H / 2 : H) * (pool ? W / 2 : W) * C;
+  if (per_copy == 0 || P == 0) return TP_OK;
+  TP_REQUIRE(z && inv_perm && out_hi && out_lo, TP_ERR_INVALID, "tp_mask_stack_nhwc: NULL pointer");
+  tp::mask_stack_nhwc_kernel<<<tp::ew_grid(per_copy), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, out_hi, out_lo);
+  TP_LAUNCH_CHECK("mask_stack_nhwc_kernel");
+  return TP_OK;
+}
+
+int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
+                           float* lo, tp_stream_t stream) {
+  TP_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0, TP_ERR_INVALID,
+             "tp_maxpool2_split_nhwc: negative dimension");
+  TP_REQUIRE(H % 2 == 0 && W % 2 == 0 && C % 4 == 0, TP_ERR_LIMIT,
+             "tp_maxpool2_split_nhwc: needs even H, W and C %% 4 == 0");
+  const long long total = N * (H / 2) * (W / 2) * (C / 4);
+  if (total == 0) return TP_OK;
+  TP_REQUIRE(x && hi && lo, TP_ERR_INVALID, "tp_maxpool2_split_nhwc: NULL pointer");
+  tp::maxpool2_split_nhwc_kernel<<<tp::ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, N, (int)H, (int)W, (int)C, hi, lo);
+  TP_LAUNCH_CHECK("maxpool2_split_nhwc_kernel");
+  return TP_OK;
+}
+
+}  // extern "C"
