@@ -459,6 +459,12 @@ def main():
     ap.add_argument("--core-only", action="store_true",
                     help="timed Shapley steps only (no e2e / reductions / CPU legs); for ncu runs")
     args = ap.parse_args()
+    # Everything any library prints to fd 1 (NCCL's version banner, the reference-compatible
+    # "... detected: shifting evaluation ..." lines) goes to stderr; the JSON line alone goes to
+    # the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -470,9 +476,9 @@ def main():
         if args.warmup < 3:
             log("bench.py: timing rules ask for >= 3 warm-up steps")
         result = run_product(args, rank, world, local_rank)
+    sys.stdout.flush()
     if rank == 0 and result is not None:
-        sys.stdout.write(json.dumps(result) + "\n")
-        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(result) + "\n").encode())
 
 
 if __name__ == "__main__":
