@@ -403,3 +403,49 @@ def test_cascading_prune_is_bit_exact(cfg, capsys):
     model.train()
     model(x).sum().backward()
     opt.step()
+
+
+# ------------------------------------------------------------------ config 4: ResNet-50
+def test_resnet50_all_convs_taylor_apoz_sensitivity():
+    """Config 4 on the hook-friendly ResNet-50 (53 convolutions, find_best_evaluation_module=True):
+    the API's hook plumbing — including the clone that an in-place ReLU after the BatchNorm evaluation
+    module makes necessary — against the same quantities computed with plain torch ops on the
+    tensors the hooks see (the reference's arithmetic, taylor.py:40-44 / apoz.py:31-33)."""
+    torch.manual_seed(0)
+    model, shape = workloads.build("resnet50")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=12, batch_size=6)
+    convs = model.conv_layers()
+    assert len(convs) == 53
+    mk = lambda cls, **kw: cls(model, loader, workloads.cross_entropy, DEV, **kw)
+    from torchpruner_b200.utils import find_best_module_for_attributions
+    checked = 0
+    for conv in convs[::4] + convs[-2:]:
+        eval_module = find_best_module_for_attributions(model, conv)
+        want_t, want_a, want_s = [], [], []
+
+        def fwd(mod, _inp, out):
+            z = out.detach().clone()
+            want_a.append((z > 0).float().flatten(2).sum(-1))
+            def bwd(g, z=z):
+                want_t.append((-1.0 * (g * z)).flatten(2).sum(-1).abs())
+                want_s.append(g.abs().flatten(2).sum(-1))
+            out.register_hook(bwd)
+
+        h = eval_module.register_forward_hook(fwd)
+        for x, y in loader:
+            model.zero_grad()
+            workloads.cross_entropy(model(x.to(DEV)), y.to(DEV)).backward()
+        h.remove()
+        model.zero_grad()
+        t = mk(TaylorAttributionMetric, reduction="none").run(conv, find_best_evaluation_module=True)
+        model.zero_grad()
+        s = mk(SensitivityAttributionMetric, reduction="none").run(conv, find_best_evaluation_module=True)
+        model.zero_grad()
+        a = mk(APoZAttributionMetric, reduction="none").run(conv, find_best_evaluation_module=True)
+        wt, ws, wa = (torch.cat(v).cpu().numpy() for v in (want_t, want_s, want_a))
+        assert t.shape == wt.shape == (12, eval_module.num_features if hasattr(eval_module, "num_features") else wt.shape[1])
+        assert norm_err(t, wt) <= 1e-5 and norm_err(s, ws) <= 1e-5
+        np.testing.assert_array_equal(a, wa)
+        checked += 1
+    assert checked >= 15

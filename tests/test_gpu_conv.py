@@ -47,14 +47,19 @@ def test_tf32_split():
     (300, 1, 1, 512, 512, 1, True),    # linear layer
     (130, 1, 1, 512, 10, 1, False),    # logits: 10 outputs, unsplit result
     (2, 16, 16, 32, 64, 9, True),      # one k-block per tap
+    (40, 32, 32, 64, 64, 9, True),     # 320 tiles: several tiles per persistent CTA
+    (150, 8, 8, 256, 512, 9, False),   # 75 x 4 tiles, ragged M
 ])
+@pytest.mark.parametrize("variant", [0, 1], ids=["persistent", "tile-per-cta"])
 @pytest.mark.parametrize("promote", [1, 2, 8])
-def test_conv_tf32x3_matches_float64(N, H, W, Cin, Cout, taps, relu, promote):
+def test_conv_tf32x3_matches_float64(N, H, W, Cin, Cout, taps, relu, promote, variant):
     _lib.set_tuning("conv_promote", promote)
+    _lib.set_tuning("conv_variant", variant)
     try:
         _conv_case(N, H, W, Cin, Cout, taps, relu, promote)
     finally:
         _lib.set_tuning("conv_promote", 2)
+        _lib.set_tuning("conv_variant", 0)
 
 
 def _conv_case(N, H, W, Cin, Cout, taps, relu, promote):

@@ -8,7 +8,7 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
-from ..native_tail import NativeTail
+from ..native_tail import NativeTail, cached_plan, remember_plan
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -187,20 +187,27 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 # --- how the layers after `module` are executed for this batch
                 native = None
                 if self.native_tail and stack_safe and spans:
-                    native = NativeTail.build(self.model, module, z)
+                    found, native, info = cached_plan(self.model, module, z)
+                    if found:
+                        native_info = dict(info, cached=True)
+                    else:
+                        native = NativeTail.build(self.model, module, z)
                 if native is not None:
                     per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
                     P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
                     buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
                                          dtype=torch.float32, device=z.device)
                     buf_lo = torch.empty_like(buf_hi)
-                    j0, k0v, _ = spans[0]
-                    ok, verr = native.verify(self.model, module, z, inv_dev[j0], k0v, min(2, n),
-                                             buf_hi, buf_lo)
-                    native_info = {"verified": ok, "verify_rel_err": verr}
-                    if not ok:
-                        native = None
-                        del buf_hi, buf_lo
+                    if not found:
+                        j0, k0v, _ = spans[0]
+                        ok, verr = native.verify(self.model, module, z, inv_dev[j0], k0v, min(2, n),
+                                                 buf_hi, buf_lo)
+                        native_info = {"verified": ok, "verify_rel_err": verr}
+                        if not ok:
+                            native = None
+                            del buf_hi, buf_lo
+                if self.native_tail and stack_safe and spans and not found:
+                    remember_plan(self.model, module, z, native, native_info or {"verified": False})
                 if native is None:
                     bytes_per_copy = max(1, z.numel() * 4)
                     P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // bytes_per_copy)))

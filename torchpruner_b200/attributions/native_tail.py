@@ -16,6 +16,8 @@ BatchNorm (eval) and the conv/linear bias are folded into one per-channel scale/
 the kernel's epilogue; ReLU is fused; a MaxPool that follows is a separate NHWC kernel that also
 re-splits the result into its TF32 hi/lo pair.
 """
+import weakref
+
 import torch
 import torch.nn as nn
 
@@ -26,6 +28,36 @@ VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
 
 class _Unsupported(Exception):
     pass
+
+
+# model -> {(id(module), activation shape): (signature, plan or None, info)}.  A plan (traced,
+# weight-prepared and verified against forward_partial) stays valid exactly as long as no
+# parameter or buffer of the model has been written, replaced or resized and no BatchNorm/Dropout
+# changed mode — which is what the signature captures (in-place writes bump `_version`, pruning
+# replaces `.data`).
+_PLANS = weakref.WeakKeyDictionary()
+
+
+def _signature(model):
+    sig = []
+    for t in list(model.parameters()) + list(model.buffers()):
+        sig.append((id(t), t._version, t.data_ptr(), tuple(t.shape)))
+    for m in model.modules():
+        if isinstance(m, (nn.modules.batchnorm._BatchNorm, nn.modules.dropout._DropoutNd)):
+            sig.append((id(m), m.training))
+    return tuple(sig)
+
+
+def cached_plan(model, module, z):
+    """(found, plan, info) for this model state."""
+    entry = _PLANS.get(model, {}).get((id(module), tuple(z.shape[1:])))
+    if entry is not None and entry[0] == _signature(model):
+        return True, entry[1], entry[2]
+    return False, None, None
+
+
+def remember_plan(model, module, z, plan, info):
+    _PLANS.setdefault(model, {})[(id(module), tuple(z.shape[1:]))] = (_signature(model), plan, info)
 
 
 def _trace_chain(model, z, module):

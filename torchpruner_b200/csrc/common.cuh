@@ -51,6 +51,7 @@ struct Tuning {
   int reduce_ctas_per_sm = 2;    // persistent CTAs per SM (TMA variant)
   int reduce_tma_min_elems = 1 << 20;
   int conv_promote = 2;          // k-blocks (of 32 inputs) per TMEM partial sum
+  int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
 };
 Tuning& tuning();
 

@@ -379,6 +379,271 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
 }
 
+
+// =====================================================================================
+// Persistent variant (default): one CTA per SM walks output tiles (n-tile fastest, so the CTAs
+// that share an activation tile run at the same time and hit it in L2); four TMEM accumulators
+// let the MMA issuer run up to three partial sums ahead of the epilogue warps, so the epilogue
+// of tile i — scale/shift/ReLU/split, staged through swizzled shared memory and written with
+// TMA stores (full 128-byte lines instead of one scattered row per thread) — overlaps the MMAs
+// of tile i+1.
+// =====================================================================================
+template <int BLOCK_N>
+struct ConvCfgP {
+  static constexpr int kABytes = kBlockM * kBlockK * 4;
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 4;
+  static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
+  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;
+  static constexpr int kNumAcc = 4;
+  static constexpr int kTmemCols = kNumAcc * BLOCK_N;  // 512 / 256
+  static constexpr int kStoreBytes = kBlockM * 32 * 4;  // one [128 rows][32 cols] staging tile
+  static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kStoreBytes + 1024 /*align*/ +
+                                    512 /*barriers*/ + 2 * BLOCK_N * 4;
+};
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0,
+                                             int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
+                       const __grid_constant__ CUtensorMap tm_a_lo,
+                       const __grid_constant__ CUtensorMap tm_b_hi,
+                       const __grid_constant__ CUtensorMap tm_b_lo,
+                       const __grid_constant__ CUtensorMap tm_y_hi,
+                       const __grid_constant__ CUtensorMap tm_y_lo, const ConvGeom g,
+                       const float* __restrict__ scale, const float* __restrict__ shift,
+                       int m_tiles, int n_tiles) {
+  using Cfg = ConvCfgP<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* store_buf = smem + Cfg::kStages * Cfg::kStageBytes;  // 2 x 16 KB, 1024-aligned
+  uint64_t* full = reinterpret_cast<uint64_t*>(store_buf + 2 * Cfg::kStoreBytes);
+  uint64_t* empty = full + Cfg::kStages;
+  uint64_t* acc_full = empty + Cfg::kStages;
+  uint64_t* acc_empty = acc_full + Cfg::kNumAcc;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + Cfg::kNumAcc);
+  float* s_scale = reinterpret_cast<float*>(store_buf + 2 * Cfg::kStoreBytes + 512);
+  float* s_shift = s_scale + BLOCK_N;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = m_tiles * n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tm_a_hi);
+    prefetch_tensormap(&tm_a_lo);
+    prefetch_tensormap(&tm_b_hi);
+    prefetch_tensormap(&tm_b_lo);
+    prefetch_tensormap(&tm_y_hi);
+    prefetch_tensormap(&tm_y_lo);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int b = 0; b < Cfg::kNumAcc; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);
+    }
+    fence_mbar_init();
+  } else if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int chunks_per_tile = (g.num_kb + g.promote - 1) / g.promote;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      const int kc = g.Cin / kBlockK;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
+        int n0, h0;
+        if (g.bn == 1) {
+          n0 = mt / g.tiles_h;
+          h0 = (mt - n0 * g.tiles_h) * g.bh;
+        } else {
+          n0 = mt * g.bn;
+          h0 = 0;
+        }
+        int tap = 0, cb = 0;
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1u);
+          mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+          uint8_t* st = smem + stage * Cfg::kStageBytes;
+          const int r = (g.taps == 9) ? tap / 3 : 1;
+          const int s = (g.taps == 9) ? tap - r * 3 : 1;
+          tma_load_4d(st, &tm_a_hi, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
+          tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, s - 1, h0 + r - 1, n0,
+                      &full[stage]);
+          tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
+          tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK, nt * BLOCK_N,
+                      &full[stage]);
+          if (++cb == kc) {
+            cb = 0;
+            ++tap;
+          }
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
+                                 ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int buf = 0;
+      uint32_t acc_phase = 0;  // flips every time buf wraps
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int in_chunk = 0;
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          if (in_chunk == 0) {
+            mbar_wait(&acc_empty[buf], acc_phase ^ 1u);
+            tc_fence_after();
+          }
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          uint8_t* st = smem + stage * Cfg::kStageBytes;
+          const uint64_t a_hi = umma_desc_sw128(st);
+          const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
+          const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
+          const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
+          const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+#pragma unroll
+          for (int kk = 0; kk < kBlockK / 8; ++kk) {
+            const uint64_t off = (uint64_t)(kk * 32 >> 4);
+            umma_tf32(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+            umma_tf32(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+            umma_tf32(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == Cfg::kStages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+          if (++in_chunk == g.promote || kb == g.num_kb - 1) {
+            umma_commit(&acc_full[buf]);
+            in_chunk = 0;
+            if (++buf == Cfg::kNumAcc) {
+              buf = 0;
+              acc_phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue warps =====
+    const int et = threadIdx.x - 64;  // 0..127
+    const int q = warp & 3;
+    const int row = q * 32 + lane;    // row of the tile == TMEM lane
+    const bool issuer = (et == 0);
+    int buf = 0;
+    uint32_t acc_phase = 0;
+    uint32_t stores = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
+      // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
+      for (int j = et; j < BLOCK_N; j += 128) {
+        const int col = nt * BLOCK_N + j;
+        s_scale[j] = col < g.Cout ? scale[col] : 0.f;
+        s_shift[j] = col < g.Cout ? shift[col] : 0.f;
+      }
+      float acc[BLOCK_N];
+#pragma unroll
+      for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
+      for (int chunk = 0; chunk < chunks_per_tile; ++chunk) {
+        mbar_wait(&acc_full[buf], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+#pragma unroll
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c0, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c0 + j] += __uint_as_float(v[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+        if (++buf == Cfg::kNumAcc) {
+          buf = 0;
+          acc_phase ^= 1u;
+        }
+      }
+      epi_barrier();  // scale/shift of this tile visible to all epilogue threads
+      const int passes = g.split ? 2 : 1;
+#pragma unroll
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        float y[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+          if (g.relu) t = fmaxf(t, 0.f);
+          y[j] = t;
+        }
+        for (int pass = 0; pass < passes; ++pass) {
+          uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
+          // the TMA store that used this staging tile two stores ago must have read it out
+          if (issuer) bulk_wait_read<1>();
+          epi_barrier();
+          uint8_t* rowp = sbuf + row * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            float4 o;
+            if (g.split) {
+              const float h0 = tf32_hi(y[4 * c]), h1 = tf32_hi(y[4 * c + 1]),
+                          h2 = tf32_hi(y[4 * c + 2]), h3 = tf32_hi(y[4 * c + 3]);
+              if (pass == 0) {
+                o = make_float4(h0, h1, h2, h3);
+              } else {
+                o = make_float4(tf32_lo(y[4 * c], h0), tf32_lo(y[4 * c + 1], h1),
+                                tf32_lo(y[4 * c + 2], h2), tf32_lo(y[4 * c + 3], h3));
+              }
+            } else {
+              o = make_float4(y[4 * c], y[4 * c + 1], y[4 * c + 2], y[4 * c + 3]);
+            }
+            *reinterpret_cast<float4*>(rowp + ((c ^ (row & 7)) << 4)) = o;  // 128B swizzle
+          }
+          fence_proxy_async();
+          epi_barrier();
+          if (issuer) {
+            tma_store_2d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, mt * kBlockM);
+            bulk_commit();
+          }
+          ++stores;
+        }
+      }
+    }
+    if (issuer) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
 // ---- small elementwise companions ------------------------------------------------------
 __global__ void __launch_bounds__(256)
 tf32_split_kernel(const float* __restrict__ x, long long n, float* __restrict__ hi,
@@ -520,6 +785,38 @@ static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const f
   return TP_OK;
 }
 
+
+template <int BLOCK_N>
+static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_lo,
+                                  const float* w_hi, const float* w_lo, const ConvGeom& g,
+                                  const float* scale, const float* shift, float* y_hi, float* y_lo,
+                                  cudaStream_t st) {
+  using Cfg = ConvCfgP<BLOCK_N>;
+  CUtensorMap b_hi, b_lo, o_hi, o_lo;
+  const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
+  const cuuint32_t bbox[2] = {kBlockK, BLOCK_N};
+  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox);
+  if (rc != TP_OK) return rc;
+  rc = make_map(&b_lo, w_lo, 2, bdims, bbox);
+  if (rc != TP_OK) return rc;
+  const cuuint64_t ydims[2] = {(cuuint64_t)g.Cout, (cuuint64_t)g.m_total};
+  const cuuint32_t ybox[2] = {32, kBlockM};
+  rc = make_map(&o_hi, y_hi, 2, ydims, ybox);
+  if (rc != TP_OK) return rc;
+  rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 2, ydims, ybox);
+  if (rc != TP_OK) return rc;
+  auto kern = conv_tf32x3_persistent<BLOCK_N>;
+  TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  const long long m_tiles = (g.m_total + kBlockM - 1) / kBlockM;
+  const int n_tiles = (g.Cout + BLOCK_N - 1) / BLOCK_N;
+  long long grid = m_tiles * n_tiles;
+  if (grid > sm_count()) grid = sm_count();
+  kern<<<(unsigned)grid, kConvThreads, Cfg::kSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, o_hi, o_lo, g,
+                                                             scale, shift, (int)m_tiles, n_tiles);
+  TP_LAUNCH_CHECK("conv_tf32x3_persistent");
+  return TP_OK;
+}
+
 static inline unsigned ew_grid(long long items) {
   long long blocks = (items + 255) / 256;
   const long long cap = (long long)sm_count() * 16;
@@ -584,6 +881,15 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
   if (rc != TP_OK) return rc;
   if (Cout <= 16)
     return launch_conv<16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+  // The persistent kernel writes through TMA stores: row pitch must be a multiple of 16 bytes and
+  // the 32-column store box must not straddle the end of a row.
+  const bool persistent = tuning().conv_variant != 1 && (Cout % 32 == 0) &&
+                          ((uintptr_t)y_hi % 16 == 0) && (!y_lo || (uintptr_t)y_lo % 16 == 0);
+  if (persistent) {
+    if (Cout <= 64)
+      return launch_conv_persistent<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+    return launch_conv_persistent<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+  }
   if (Cout <= 64)
     return launch_conv<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
   return launch_conv<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
