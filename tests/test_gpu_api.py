@@ -449,3 +449,32 @@ def test_resnet50_all_convs_taylor_apoz_sensitivity():
         np.testing.assert_array_equal(a, wa)
         checked += 1
     assert checked >= 15
+
+
+def test_shapley_full_size_telescopes():
+    """Size-independent property at BASELINE config 3 size (bs 256, 512 channels): along one
+    permutation the marginal contributions telescope, so every example's scores sum to
+    loss(all channels removed) - loss(nothing removed)."""
+    model, shape = workloads.build("vgg16_cifar")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=256, batch_size=256)
+    layer = dict(model.named_modules())["features.24"]
+    np.random.seed(2)
+    m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1, reduction="none")
+    sv = m.run(layer, find_best_evaluation_module=True)
+    assert sv.shape == (256, 512) and m.last_run_info["evaluations"] == 512
+    assert m.last_run_info["native_tail"] is True
+    x, y = next(iter(loader))
+    x, y = x.to(DEV), y.to(DEV)
+    relu = model.features[26]
+    with torch.no_grad():
+        z = model.forward_partial(x, to_module=relu)
+        l0 = workloads.cross_entropy(model.forward_partial(z, from_module=relu), y, reduction="none")
+        l1 = workloads.cross_entropy(model.forward_partial(torch.zeros_like(z), from_module=relu), y,
+                                     reduction="none")
+    want = (l1 - l0).double().cpu().numpy()
+    # Adjacent losses differ by far less than a factor of two, so every fp32 difference is exact
+    # (Sterbenz) and the fp64 sum telescopes exactly: what is left is the few-ulp difference
+    # between the engine's and torch's loss for the fully masked activation (ulp(2.3) = 2.4e-7).
+    assert np.abs(sv.sum(1) - want).max() <= 2e-6, np.abs(sv.sum(1) - want).max()
+    assert np.abs(want).max() > 1e-4   # random-init VGG: the signal itself is only ~2e-4
