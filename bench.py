@@ -206,6 +206,21 @@ def time_reductions(device, hbm_peak):
     for op, (fn, mult) in ops.items():
         nbytes = [mult * int(np.prod(s)) + 4 * s[0] * s[1] for s in layer_shapes]
         sweep_ms = timed(lambda: [fn(i) for i in range(13)])
+        # the same 13 launches captured once in a CUDA graph and replayed: launch-bound inner
+        # loops belong in graphs; this removes the host enqueue cost from the device timeline
+        graph_ms = None
+        try:
+            side = torch.cuda.Stream(device)
+            side.wait_stream(stream)
+            with torch.cuda.stream(side):
+                [fn(i) for i in range(13)]
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    [fn(i) for i in range(13)]
+            stream.wait_stream(side)
+            graph_ms = timed(g.replay)
+        except Exception as e:  # noqa: BLE001 - capture support is a bonus, not a requirement
+            log(f"bench.py: CUDA-graph sweep skipped for {op}: {e}")
         per = {}
         for i in (0, 2, 4, 7, 10):
             per["x".join(map(str, layer_shapes[i]))] = round(nbytes[i] / timed(lambda: fn(i)) / 1e6, 1)
@@ -213,6 +228,8 @@ def time_reductions(device, hbm_peak):
             "c2_sweep_gbs": sum(nbytes) / sweep_ms / 1e6,
             "c2_sweep_frac": sum(nbytes) / sweep_ms / 1e6 / hbm_peak,
             "c2_sweep_us": sweep_ms * 1e3, "c2_sweep_bytes": sum(nbytes), "c2_sweep_launches": 13,
+            "c2_sweep_graph_gbs": (sum(nbytes) / graph_ms / 1e6) if graph_ms else None,
+            "c2_sweep_graph_frac": (sum(nbytes) / graph_ms / 1e6 / hbm_peak) if graph_ms else None,
             "per_shape_gbs": per,
         }
     del zs, gs

@@ -106,6 +106,14 @@ int tp_loss_delta_scatter(const float* src, const int64_t* target, int kind,
                           double* sv, int64_t ld_sv, int64_t row0, int64_t scatter_from,
                           float* losses_out, tp_stream_t stream);
 
+/* Ablation / robustness curve (reference experiments notebook "CIFAR-10 - VGG16 - Layerwise
+ * robustness", cell 8: per removed unit a forward_partial, a mean cross entropy, an argmax
+ * accuracy and two .item() syncs).  For each of P masked copies: mean_loss[p] = mean over the
+ * batch of cross_entropy(logits[p,b,:], target[b]); correct[p] = #{b : argmax == target[b]}
+ * (first maximum wins ties).  logits: [P,B,K] fp32; target: [B] int64; outputs on the device. */
+int tp_ce_mean_acc(const float* logits, const int64_t* target, int64_t P, int64_t B, int64_t K,
+                   float* mean_loss, int32_t* correct, tp_stream_t stream);
+
 /* ---------------------------------------------------------------- K7
  * Fused index_select of many tensors in one launch.  Descriptor i copies
  *   dst[o, j, :] = src[o, keep[keep_offset + j], :]   o < outer, j < n_keep

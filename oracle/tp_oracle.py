@@ -226,6 +226,24 @@ def shapley_without_partial(model, batches, criterion, samples, module):
     return sv
 
 
+def ablation_curve(model, x, y, criterion, module_nl, ranking):
+    """Experiments notebook "CIFAR-10 - VGG16 - Layerwise robustness", cell 8 (:1272-1277),
+    restated: activation at `module_nl`, then for each unit of `ranking` zero it (cumulatively),
+    run the remaining layers, record the mean loss and the top-1 accuracy."""
+    losses, accs = [], []
+    with torch.no_grad():
+        z = model.forward_partial(x, to_module=module_nl)
+        for i in ranking:
+            z.index_fill_(1, torch.tensor([int(i)]), 0.)
+            y_pred = model.forward_partial(z, from_module=module_nl)
+            new_loss = criterion(y_pred, y)
+            current_pred = y_pred.argmax(dim=1, keepdim=True)
+            new_acc = current_pred.eq(y.view_as(current_pred)).sum().float() / len(y)
+            losses.append(new_loss.item())
+            accs.append(new_acc.item())
+    return np.asarray(losses, np.float32), np.asarray(accs, np.float32)
+
+
 # --------------------------------------------------------------------------- K7 / K8
 
 

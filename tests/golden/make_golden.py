@@ -218,7 +218,34 @@ def gen_prune():
     print("prune:", len(lines), "lines")
 
 
-GROUPS = {"ops": gen_ops, "max_model": gen_max_model, "small_cnn": gen_small_cnn, "vgg": gen_vgg,
+def gen_ablation():
+    """The notebook's ablation loop (cell 8) run literally with the reference's helpers."""
+    out = {}
+    for cfg, tag, n in (("small_cnn", "features.3", 32), ("vgg16_cifar", "features.34", 32)):
+        model, shape = workloads.build(cfg)
+        x, y = next(iter(workloads.synthetic_batches(shape, n=n, batch_size=n, seed=8)))
+        module = dict(model.named_modules())[tag]
+        ranking = np.random.RandomState(4).permutation(module.out_channels)
+        loss = workloads.cross_entropy
+        losses, accs = [], []
+        with torch.no_grad():
+            module_nl = quiet(find_best_module_for_attributions, model, module)
+            z = model.forward_partial(x, to_module=module_nl)
+            for i in ranking:
+                z.index_fill_(1, torch.tensor([i]), 0.)
+                y_pred = model.forward_partial(z, from_module=module_nl)
+                new_loss = loss(y_pred, y)
+                current_pred = y_pred.argmax(dim=1, keepdim=True)
+                new_acc = current_pred.eq(y.view_as(current_pred)).sum().float() / len(y)
+                losses.append(new_loss.item())
+                accs.append(new_acc.item())
+        out[f"{cfg}/loss"] = np.asarray(losses, np.float32)
+        out[f"{cfg}/acc"] = np.asarray(accs, np.float32)
+    np.savez_compressed(os.path.join(HERE, "ablation.npz"), **out)
+    print("ablation:", len(out), "arrays")
+
+
+GROUPS = {"ablation": gen_ablation, "ops": gen_ops, "max_model": gen_max_model, "small_cnn": gen_small_cnn, "vgg": gen_vgg,
           "graph": gen_graph, "prune": gen_prune}
 
 if __name__ == "__main__":

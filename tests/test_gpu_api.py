@@ -478,3 +478,35 @@ def test_shapley_full_size_telescopes():
     # between the engine's and torch's loss for the fully masked activation (ulp(2.3) = 2.4e-7).
     assert np.abs(sv.sum(1) - want).max() <= 2e-6, np.abs(sv.sum(1) - want).max()
     assert np.abs(want).max() > 1e-4   # random-init VGG: the signal itself is only ~2e-4
+
+
+# ------------------------------------------------------------------ ablation curve
+@pytest.mark.parametrize("cfg,tag,n", [("small_cnn", "features.3", 32), ("vgg16_cifar", "features.34", 32)])
+@pytest.mark.parametrize("native", [True, False])
+def test_ablation_curve_matches_reference(cfg, tag, n, native):
+    from torchpruner_b200.ablation import ablation_curve
+
+    g = gold("ablation.npz")
+    model, shape = workloads.build(cfg)
+    model.to(DEV)
+    x, y = next(iter(workloads.synthetic_batches(shape, n=n, batch_size=n, seed=8)))
+    module = dict(model.named_modules())[tag]
+    ranking = np.random.RandomState(4).permutation(module.out_channels)
+    loss, acc = ablation_curve(model, x.to(DEV), y.to(DEV), module, ranking,
+                               criterion=workloads.cross_entropy, native_tail=native, max_stack=37)
+    assert loss.shape == g[f"{cfg}/loss"].shape and loss.dtype == np.float32
+    np.testing.assert_allclose(loss, g[f"{cfg}/loss"], rtol=2e-6)     # mean losses, ~2.3
+    flips = int((acc != g[f"{cfg}/acc"]).sum())   # an argmax can flip on a near-tie
+    assert flips <= max(1, len(acc) // 100), flips
+    # against the oracle on the CPU copy as well, with a partial ranking and a generic criterion
+    cpu_model, _ = workloads.build(cfg)
+    part = ranking[:9]
+    from torchpruner_b200.utils import find_best_module_for_attributions
+    cpu_module = dict(cpu_model.named_modules())[tag]
+    want_loss, want_acc = oracle.ablation_curve(cpu_model, x, y, workloads.cross_entropy,
+                                                find_best_module_for_attributions(cpu_model, cpu_module), part)
+    odd = lambda o, t, reduction="mean": F.cross_entropy(o, t, reduction=reduction) * 2.0
+    loss2, acc2 = ablation_curve(model, x.to(DEV), y.to(DEV), module, part, criterion=odd,
+                                 native_tail=native)
+    np.testing.assert_allclose(loss2 / 2.0, want_loss, rtol=2e-6)
+    assert int((acc2 != want_acc).sum()) <= 1

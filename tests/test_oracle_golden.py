@@ -180,3 +180,18 @@ def test_oracle_pruner_matches_reference_digests(cfg):
     for module, cascade in graph:
         pruner.prune_model(module, cases.prune_choice(module.weight.shape[0]), cascade)
     assert cases.model_digest(model, opt) == gold
+
+
+@pytest.mark.parametrize("cfg,tag,n", [("small_cnn", "features.3", 32), ("vgg16_cifar", "features.34", 32)])
+def test_ablation_curve_matches_notebook_loop(cfg, tag, n):
+    from torchpruner_b200.utils import find_best_module_for_attributions
+
+    gold = load("ablation.npz")
+    model, shape = workloads.build(cfg)
+    x, y = next(iter(workloads.synthetic_batches(shape, n=n, batch_size=n, seed=8)))
+    module = dict(model.named_modules())[tag]
+    ranking = np.random.RandomState(4).permutation(module.out_channels)
+    loss, acc = oracle.ablation_curve(model, x, y, workloads.cross_entropy,
+                                      find_best_module_for_attributions(model, module), ranking)
+    np.testing.assert_allclose(loss, gold[f"{cfg}/loss"], rtol=1e-6)
+    np.testing.assert_array_equal(acc, gold[f"{cfg}/acc"])

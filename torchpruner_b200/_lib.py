@@ -52,6 +52,7 @@ _SIGNATURES = {
         [_vp, _vp, ctypes.c_int, _vp, _vp, _vp, _i64, _i64, _i64, _i64, ctypes.c_float, _vp,
          _i64, _i64, _i64, _vp, _vp],
     ),
+    "tp_ce_mean_acc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "tp_multi_gather": (ctypes.c_int, [ctypes.POINTER(GatherDesc), _i64, _vp, _i64, _vp]),
     "tp_nan_any_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "tp_nan_any_dim1_static": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
@@ -402,3 +403,18 @@ def maxpool2_split_nhwc(x):
         _check(load().tp_maxpool2_split_nhwc(x.data_ptr(), N, H, W, C, hi.data_ptr(), lo.data_ptr(),
                                              _stream(x)), "tp_maxpool2_split_nhwc")
     return hi, lo
+
+
+def ce_mean_acc(logits, target, P, B):
+    """(mean cross entropy [P] fp32, correct top-1 count [P] int32) of P stacked batches."""
+    logits = _cuda_f32(logits, "logits")
+    K = logits.shape[-1]
+    if logits.numel() != P * B * K or target.dtype != torch.int64 or target.numel() != B:
+        raise TorchPrunerB200Error("ce_mean_acc: shapes do not match")
+    mean_loss = torch.empty(P, dtype=torch.float32, device=logits.device)
+    correct = torch.empty(P, dtype=torch.int32, device=logits.device)
+    with torch.cuda.device(logits.device), _launch("ce_mean_acc", 4 * logits.numel(), logits):
+        _check(load().tp_ce_mean_acc(logits.data_ptr(), target.data_ptr(), int(P), int(B), K,
+                                     mean_loss.data_ptr(), correct.data_ptr(), _stream(logits)),
+               "tp_ce_mean_acc")
+    return mean_loss, correct

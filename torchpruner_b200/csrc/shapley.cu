@@ -104,6 +104,57 @@ loss_delta_scatter_kernel(const float* __restrict__ src, const int64_t* __restri
   }
 }
 
+// Ablation curve (reference experiments "Layerwise robustness" notebook, cell 8, lines
+// 1272-1277): for each of P cumulatively masked copies, the MEAN cross entropy over the batch and
+// the number of correct top-1 predictions (first maximum wins ties, like torch.argmax).
+// One CTA per mask; fixed-order fp32 summation (per-thread partials, shuffle tree, 8 warp sums).
+__global__ void __launch_bounds__(256)
+ce_mean_acc_kernel(const float* __restrict__ logits, const int64_t* __restrict__ target, int64_t P,
+                   int64_t B, int64_t K, float* __restrict__ mean_loss,
+                   int32_t* __restrict__ correct) {
+  __shared__ float s_sum[8];
+  __shared__ int s_cnt[8];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int64_t p = blockIdx.x; p < P; p += gridDim.x) {
+    float sum = 0.f;
+    int cnt = 0;
+    for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+      const float* x = logits + (p * B + b) * K;
+      const int64_t t = target[b];
+      sum += ce_row(x, K, t);
+      int64_t best = 0;
+      float bv = x[0];
+      for (int64_t k = 1; k < K; ++k) {
+        if (x[k] > bv) {
+          bv = x[k];
+          best = k;
+        }
+      }
+      cnt += (best == t);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    }
+    if (lane == 0) {
+      s_sum[wid] = sum;
+      s_cnt[wid] = cnt;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float tot = 0.f;
+      int c = 0;
+      for (int w = 0; w < 8; ++w) {
+        tot += s_sum[w];
+        c += s_cnt[w];
+      }
+      mean_loss[p] = tot / (float)B;
+      correct[p] = c;
+    }
+    __syncthreads();
+  }
+}
+
 static inline unsigned grid_for(int64_t work_items, int threads, int waves = 8) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = (int64_t)sm_count() * waves;
@@ -178,6 +229,22 @@ int tp_loss_delta_scatter(const float* src, const int64_t* target, int kind, con
         scatter_from, losses_out);
   }
   TP_LAUNCH_CHECK("loss_delta_scatter_kernel");
+  return TP_OK;
+}
+
+int tp_ce_mean_acc(const float* logits, const int64_t* target, int64_t P, int64_t B, int64_t K,
+                   float* mean_loss, int32_t* correct, tp_stream_t stream) {
+  TP_REQUIRE(P >= 0 && B >= 0 && K >= 1, TP_ERR_INVALID, "tp_ce_mean_acc: bad dimension");
+  if (P == 0) return TP_OK;
+  TP_REQUIRE(B > 0, TP_ERR_INVALID, "tp_ce_mean_acc: empty batch");
+  TP_REQUIRE(logits && target && mean_loss && correct, TP_ERR_INVALID,
+             "tp_ce_mean_acc: NULL pointer");
+  int64_t blocks = P;
+  const int64_t cap = (int64_t)tp::sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  tp::ce_mean_acc_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, target, P, B, K, mean_loss, correct);
+  TP_LAUNCH_CHECK("ce_mean_acc_kernel");
   return TP_OK;
 }
 
