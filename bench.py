@@ -368,6 +368,7 @@ def run_product(args, rank, world, local_rank):
                for k, v in kernel_summary.items()}
         with quiet():
             reductions = time_reductions(device, hbm_peak) if (world == 1 and not args.core_only) else None
+            secondary = secondary_configs(device) if (world == 1 and not args.core_only) else None
         cpu = cpu_sample(steps=1, warmup=0) if (world == 1 and not args.core_only) else None
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -382,6 +383,7 @@ def run_product(args, rank, world, local_rank):
             "own_kernels": own,
             "roofline": roofline,
             "reductions": reductions,
+            "secondary": secondary,
             "cpu_baseline": cpu,
             "clocks": clocks.summary(),
         }
@@ -389,6 +391,86 @@ def run_product(args, rank, world, local_rank):
         dist.barrier()
         dist.destroy_process_group()
     return result
+
+
+def secondary_configs(device):
+    """The other BASELINE configs, end to end through the public API with the CPU port beside
+    them: config 2 = Taylor / APoZ / Sensitivity `run()` over all 13 conv
+    layers at bs 256 (model forward/backward included); config 5 = the 15-module cascading prune
+    of VGG16 with SGD momentum.  CPU legs are bounded samples, stated."""
+    from oracle import tp_oracle as oracle
+    from tests import cases
+    from torchpruner_b200 import _lib
+    from torchpruner_b200.attributions import (APoZAttributionMetric, SensitivityAttributionMetric,
+                                               TaylorAttributionMetric)
+    from torchpruner_b200.pruner import Pruner
+    from torchpruner_b200.utils import find_best_module_for_attributions, get_vgg_pruning_graph
+
+    out = {}
+    model, shape = build_model(device)
+    hx, hy = host_batch(shape, pin=True)
+    loader = OneBatch(hx, hy)
+    convs = model.conv_layers()
+    classes = {"taylor": TaylorAttributionMetric, "apoz": APoZAttributionMetric,
+               "sensitivity": SensitivityAttributionMetric}
+    gpu = {}
+    for name, cls in classes.items():
+        m = cls(model, loader, workloads.cross_entropy, device)
+        for conv in convs[:2]:
+            m.run(conv, find_best_evaluation_module=True)  # warm-up
+        model.zero_grad()
+        torch.cuda.synchronize(device)
+        prof = _lib.profile_begin(timed=False)
+        t0 = time.perf_counter()
+        for conv in convs:
+            m.run(conv, find_best_evaluation_module=True)
+        torch.cuda.synchronize(device)
+        gpu[name] = {"seconds_13_layers": time.perf_counter() - t0,
+                     "own_kernel_launches": sum(v[0] for v in prof.records.values())}
+        _lib.profile_end()
+        model.zero_grad()
+    # CPU port: first, middle and last conv layer (3 of 13; every layer costs one full
+    # forward(+backward) of the same model, so the 13-layer time is 13/3 of the sample)
+    cpu_model = _CPU_STATE.setdefault("model", workloads.build("vgg16_cifar", seed=1)[0])
+    cx, cy = host_batch(shape, pin=False)
+    sample = [cpu_model.conv_layers()[i] for i in (0, 6, 12)]
+    for name in classes:
+        t0 = time.perf_counter()
+        for conv in sample:
+            module = find_best_module_for_attributions(cpu_model, conv)
+            oracle.hook_scores(cpu_model, [(cx, cy)], workloads.cross_entropy, module, name)
+        dt = time.perf_counter() - t0
+        cpu_model.zero_grad()
+        gpu[name]["cpu_port_seconds_13_layers_extrapolated"] = dt * 13.0 / 3.0
+        gpu[name]["speedup_vs_cpu_port"] = gpu[name]["cpu_port_seconds_13_layers_extrapolated"] / \
+            gpu[name]["seconds_13_layers"]
+    out["c2_scores_e2e"] = dict(gpu, cpu_cores=torch.get_num_threads(),
+                                cpu_sample="layers features.0/20/40 of 13, x13/3")
+
+    # config 5
+    def cascade(pruner_factory, dev):
+        mdl, shp, opt = cases.prune_setup("vgg16_cifar", device=dev)
+        pr = pruner_factory(mdl, shp, opt)
+        graph = get_vgg_pruning_graph(mdl)
+        np.random.seed(21)
+        if dev != "cpu":
+            torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        for module, casc in graph:
+            pr.prune_model(module, cases.prune_choice(module.weight.shape[0]), casc)
+        if dev != "cpu":
+            torch.cuda.synchronize(device)
+        return time.perf_counter() - t0
+
+    cascade(lambda m, s_, o: Pruner(m, s_, device, optimizer=o), device)  # warm-up
+    prof = _lib.profile_begin(timed=False)
+    t_gpu = cascade(lambda m, s_, o: Pruner(m, s_, device, optimizer=o), device)
+    launches = {k: v[0] for k, v in prof.records.items()}
+    _lib.profile_end()
+    t_cpu = cascade(lambda m, s_, o: oracle.OraclePruner(m, s_, optimizer=o), "cpu")
+    out["c5_prune_cascade"] = {"seconds": t_gpu, "cpu_port_seconds": t_cpu, "modules": 15,
+                               "own_kernel_launches": launches, "cpu_cores": torch.get_num_threads()}
+    return out
 
 
 # --------------------------------------------------------------------------- CPU arm
@@ -405,9 +487,9 @@ def cpu_sample(steps, warmup, evals_per_layer=2):
 
     threads = torch.get_num_threads()
     if "model" not in _CPU_STATE:
-        model, shape = workloads.build("vgg16_cifar", seed=1)
-        _CPU_STATE["model"] = model
-        _CPU_STATE["batch"] = host_batch(shape, pin=False)
+        _CPU_STATE["model"] = workloads.build("vgg16_cifar", seed=1)[0]
+    if "batch" not in _CPU_STATE:
+        _CPU_STATE["batch"] = host_batch((3, 32, 32), pin=False)
     model = _CPU_STATE["model"]
     x, y = _CPU_STATE["batch"]
     convs = model.conv_layers()

@@ -87,6 +87,41 @@ def weight_norm_f64(w):
     return a.reshape(a.shape[0], -1).sum(-1)
 
 
+def hook_scores(model, batches, criterion, module, kind, signed=False):
+    """Whole-metric restatement (taylor.py:18-49, apoz.py:15-39, sensitivity.py:13-34): hooks on
+    `module`, one forward(+backward) per batch, per-batch host copy + concatenate.  Returns the
+    [N, C] table before aggregation.  Used as the timed CPU baseline of config 2."""
+    rows = []
+    state = {}
+
+    def fwd(mod, _inp, out):
+        if kind == "apoz":
+            rows.append(apoz_rows(out.detach()))
+            return
+        if kind == "taylor":
+            state["z"] = out.detach().clone()
+
+        def bwd(g):
+            if kind == "taylor":
+                rows.append(taylor_rows(state["z"], g.detach(), signed))
+            else:
+                rows.append(abs_sum_rows(g.detach()))
+        out.register_hook(bwd)
+
+    h = module.register_forward_hook(fwd)
+    try:
+        if kind == "apoz":
+            with torch.no_grad():
+                for x, y in batches:
+                    criterion(model(x), y, reduction="none")
+        else:
+            for x, y in batches:
+                criterion(model(x), y).backward()
+    finally:
+        h.remove()
+    return np.concatenate(rows, 0)
+
+
 # --------------------------------------------------------------------------- K5 / K6
 
 

@@ -510,3 +510,26 @@ def test_ablation_curve_matches_reference(cfg, tag, n, native):
                                  native_tail=native)
     np.testing.assert_allclose(loss2 / 2.0, want_loss, rtol=2e-6)
     assert int((acc2 != want_acc).sum()) <= 1
+
+
+def test_adam_state_is_sliced_with_the_parameter():
+    """optimizer state beyond SGD / param_groups[0] follows the pruned parameter."""
+    (x, y), _ = simple_model()
+    model = nn.Sequential(nn.Linear(3, 4), nn.BatchNorm1d(4), nn.Linear(4, 1)).to(DEV)
+    opt = torch.optim.Adam([{"params": model[0].parameters()}, {"params": model[1].parameters()},
+                            {"params": model[2].parameters()}], lr=1e-3)
+
+    def step():
+        opt.zero_grad()
+        model(x).mean().backward()
+        opt.step()
+
+    step()
+    before = {k: v.clone() for k, v in opt.state[model[0].weight].items() if torch.is_tensor(v) and v.dim()}
+    Pruner(model, (3,), DEV, optimizer=opt).prune_model(model[0], [1, 3], [model[1], model[2]])
+    st = opt.state[model[0].weight]
+    assert list(st["exp_avg"].shape) == [2, 3] and list(st["exp_avg_sq"].shape) == [2, 3]
+    assert torch.equal(st["exp_avg"], before["exp_avg"][[0, 2]])
+    assert list(opt.state[model[2].weight]["exp_avg"].shape) == [1, 2]
+    assert list(opt.state[model[1].weight]["exp_avg"].shape) == [2]
+    step()   # shapes are consistent: training continues

@@ -20,6 +20,31 @@ def sgd_momentum_buffer(optimizer, param):
     return None
 
 
+def optimizer_state_tensors(optimizer, param):
+    """Every per-parameter state tensor that has to be sliced together with ``param``.
+
+    The reference covers ``torch.optim.SGD`` and its first parameter group only
+    (opt_pruner.py:8-13).  That case is kept verbatim (``sgd_momentum_buffer``); in addition, for
+    any optimizer and any parameter group, state tensors shaped like the parameter (Adam's
+    ``exp_avg`` / ``exp_avg_sq``, RMSprop's ``square_avg``, SGD momentum in later groups, ...) are
+    returned too, so a pruned model keeps training without a shape error.  Scalar
+    state such as ``step`` is left alone.
+    """
+    if optimizer is None:
+        return []
+    found = []
+    buf = sgd_momentum_buffer(optimizer, param)
+    if buf is not None:
+        found.append(buf)
+    state = optimizer.state.get(param, None)
+    if state:
+        for value in state.values():
+            if isinstance(value, torch.Tensor) and value.shape == param.shape and \
+                    value.dim() > 0 and not any(value is f for f in found):
+                found.append(value)
+    return found
+
+
 class OptimizerPruner:
     """Slice optimizer state along with a pruned parameter (reference pruner/opt_pruner.py)."""
 

@@ -16,7 +16,7 @@ from torch.nn.modules.conv import _ConvNd
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import _lib
-from .opt_pruner import OptimizerPruner, sgd_momentum_buffer  # noqa: F401
+from .opt_pruner import OptimizerPruner, optimizer_state_tensors, sgd_momentum_buffer  # noqa: F401
 
 SUPPORTED_IN_PRUNING_MODULES = [nn.Linear, _ConvNd, nn.Dropout, _BatchNorm]
 SUPPORTED_OUT_PRUNING_MODULES = [nn.Linear, _ConvNd]
@@ -208,10 +208,8 @@ class Pruner:
             targets = [param]
             if param.grad is not None:
                 targets.append(param.grad)
-            if self.optimizer is not None:
-                momentum = sgd_momentum_buffer(self.optimizer, param)
-                if momentum is not None:
-                    targets.append(momentum)
+            if self.optimizer is not None and isinstance(param, torch.nn.Parameter):
+                targets.extend(optimizer_state_tensors(self.optimizer, param))
             if any(plan.touches(t) for t in targets):
                 plan.execute()  # a second slice of the same tensor must see the first one
             for t in targets:
