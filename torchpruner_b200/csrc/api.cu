@@ -71,6 +71,9 @@ int tp_set_tuning(const char* key, int64_t value) {
   } else if (!strcmp(key, "reduce_tma_min_elems")) {
     TP_REQUIRE(value >= 0, TP_ERR_INVALID, "reduce_tma_min_elems must be >= 0");
     t.reduce_tma_min_elems = (int)(value > (1ll << 30) ? (1ll << 30) : value);
+  } else if (!strcmp(key, "reduce_ldg_waves")) {
+    TP_REQUIRE(value >= 1 && value <= 64, TP_ERR_INVALID, "reduce_ldg_waves must be in [1,64]");
+    t.reduce_ldg_waves = (int)value;
   } else if (!strcmp(key, "conv_variant")) {
     TP_REQUIRE(value == 0 || value == 1, TP_ERR_INVALID, "conv_variant must be 0 or 1");
     t.conv_variant = (int)value;

@@ -50,6 +50,7 @@ struct Tuning {
   int reduce_tile_floats = 4096; // floats per stream per stage
   int reduce_ctas_per_sm = 2;    // persistent CTAs per SM (TMA variant)
   int reduce_tma_min_elems = 1 << 20;
+  int reduce_ldg_waves = 4;      // grid cap of the direct-load kernel, in waves of 8 CTAs/SM
   int conv_promote = 2;          // k-blocks (of 32 inputs) per TMEM partial sum
   int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
 };

@@ -87,7 +87,9 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
   using acc_t = typename T::acc_t;
   constexpr bool kTwo = (T::kStreams == 2);
   constexpr int RPW = 32 / LPR;
-  constexpr int U = 4;
+  // loads in flight per lane: 4 x 16 B vectors, or 8 x 4 B scalars (unaligned / odd-length rows
+  // need the deeper unroll to keep enough bytes in flight)
+  constexpr int U = VEC ? 4 : 8;
   const int lane = threadIdx.x & 31;
   const int sub = lane % LPR;
   const int slot = lane / LPR;
@@ -401,10 +403,10 @@ template <int OP, int LPR, bool VEC, bool LOOP>
 static int launch_ldg_inst(const float* a, const float* b, float* out, int64_t R, int64_t L,
                            int is_signed, cudaStream_t st) {
   constexpr int RPW = 32 / LPR;
-  const int64_t rows_per_warp = LOOP ? RPW : RPW * 4;
+  const int64_t rows_per_warp = LOOP ? RPW : RPW * (VEC ? 4 : 8);
   const int64_t warps = (R + rows_per_warp - 1) / rows_per_warp;
   int64_t blocks = (warps + 7) / 8;
-  const int64_t cap = (int64_t)sm_count() * 8 * 4;  // 8 resident 256-thread CTAs x 4 waves
+  const int64_t cap = (int64_t)sm_count() * 8 * tuning().reduce_ldg_waves;  // 8 resident CTAs/SM
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   reduce_rows_ldg<OP, LPR, VEC, LOOP><<<(unsigned)blocks, 256, 0, st>>>(a, b, out, R, L, is_signed);
