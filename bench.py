@@ -369,7 +369,7 @@ def run_product(args, rank, world, local_rank):
         with quiet():
             reductions = time_reductions(device, hbm_peak) if (world == 1 and not args.core_only) else None
             secondary = secondary_configs(device) if (world == 1 and not args.core_only) else None
-        cpu = cpu_sample(steps=1, warmup=0) if (world == 1 and not args.core_only) else None
+        cpu = cpu_sample(steps=2, warmup=1) if (world == 1 and not args.core_only) else None
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -477,7 +477,7 @@ def secondary_configs(device):
 _CPU_STATE = {}
 
 
-def cpu_sample(steps, warmup, evals_per_layer=2):
+def cpu_sample(steps, warmup, evals_per_layer=6):
     """The reference's algorithm for the path (oracle port: the loop body of
     shapley_values.py:55-61 on torch CPU ops) on this host's cores, on a bounded sample:
     `evals_per_layer` prefix evaluations of one permutation for each of the 13 layers at bs 256.

@@ -48,6 +48,16 @@ def _signature(model):
     return tuple(sig)
 
 
+# Prepared (permuted, folded, TF32-split) weights of one layer, shared by every tail that runs
+# through it: key = identities and versions of the tensors they were made from.
+_LAYERS = weakref.WeakKeyDictionary()
+
+
+def _tensor_key(*tensors):
+    return tuple(None if t is None else (id(t), t._version, t.data_ptr(), tuple(t.shape))
+                 for t in tensors)
+
+
 def cached_plan(model, module, z):
     """(found, plan, info) for this model state."""
     entry = _PLANS.get(model, {}).get((id(module), tuple(z.shape[1:])))
@@ -181,9 +191,10 @@ class NativeTail:
                 raise _Unsupported("channel / spatial size not tileable")
             scale = torch.ones(cout, device=dev)
             shift = bias.clone()
+            bn_used = None
             i += 1
             if i < len(mods) and isinstance(mods[i], nn.BatchNorm2d) and taps == 9:
-                bn = mods[i]
+                bn = bn_used = mods[i]
                 if not bn.track_running_stats or bn.running_mean is None:
                     raise _Unsupported("BatchNorm without running statistics")
                 a = (bn.running_var.detach().double() + bn.eps).rsqrt()
@@ -204,10 +215,19 @@ class NativeTail:
                     raise _Unsupported("odd spatial size before pooling")
                 pool = True
                 i += 1
-            w_hi, w_lo = _lib.tf32_split(w.contiguous())
+            key = (_tensor_key(m.weight, m.bias) + (
+                _tensor_key(bn_used.weight, bn_used.bias, bn_used.running_mean, bn_used.running_var)
+                if bn_used is not None else ()), w.shape[1], H * W if taps == 1 else 0)
+            store = _LAYERS.setdefault(model, {})
+            prep = store.get(id(m))
+            if prep is None or prep[0] != key:
+                w_hi, w_lo = _lib.tf32_split(w.contiguous())
+                prep = (key, w_hi, w_lo, scale.contiguous(), shift.contiguous())
+                store[id(m)] = prep
+            _, w_hi, w_lo, scale, shift = prep
             steps.append({"taps": taps, "cin": C, "cout": cout, "H": H, "W": W, "relu": relu,
-                          "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale.contiguous(),
-                          "shift": shift.contiguous(), "flops": 2 * H * W * cout * taps * C})
+                          "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale,
+                          "shift": shift, "flops": 2 * H * W * cout * taps * C})
             C = cout
             if pool:
                 H, W = H // 2, W // 2
