@@ -177,6 +177,27 @@ int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int6
 int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
                            float* lo, tp_stream_t stream);
 
+/* ---------------------------------------------------------------- incremental first layer
+ * Along one permutation the Shapley masks are nested and the first layer after the evaluation
+ * module is linear in the activation, so its pre-activation under mask k is
+ * S_k = S_all - sum_{j<=k} T_{perm[j]} with T_c the layer applied to channel c alone.  The
+ * reference re-runs the whole layer for every k (shapley_values.py:55-57).
+ *
+ * tp_channel_contrib: T[c][pixel][o] for every channel c.  z: NCHW [B,C,H,W] (pool != 0: take
+ *   MaxPool2d(2) of it first); wt: [C][taps][C1]; mode 0 = conv3x3 stride 1 pad 1 (taps = 9,
+ *   pixel = (b,h,w)), mode 1 = dense over all spatial positions (taps = H'*W', pixel = b).
+ * tp_contrib_sum: s_all[e] = sum_c T[c][e] in float64 (M1 = pixels*C1 elements).
+ * tp_prefix_contrib_stack: for p in [0,P): base -= T[perm[k0+p]] (float64, carried in `base`
+ *   between calls); out[p] = tf32_split(act(base*scale + shift)), optionally max-pooled 2x2
+ *   (pool != 0, spatial Hp x Wp).  out_hi == out_lo == NULL only advances `base`. */
+int tp_channel_contrib(const float* z, const float* wt, int64_t B, int64_t C, int64_t H, int64_t W,
+                       int pool, int mode, int64_t C1, float* T, tp_stream_t stream);
+int tp_contrib_sum(const float* T, int64_t C, int64_t M1, double* s_all, tp_stream_t stream);
+int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                            double* base, const float* scale, const float* shift, int64_t pixels,
+                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int relu, float* out_hi,
+                            float* out_lo, tp_stream_t stream);
+
 /* ---------------------------------------------------------------- no-allocation variant
  * No counterpart in the reference: this entry point exists for callers of THIS library that
  * cannot allocate device memory around the call.  Typical cases: a forward hook that runs in the

@@ -142,19 +142,25 @@ def test_native_tail_agrees_with_forward_partial(tag):
         loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
         layer = dict(model.named_modules())[tag]
         tables = {}
-        for native in ("auto", False):
+        for native, incremental in (("auto", True), ("auto", False), (False, False)):
             np.random.seed(3)
             m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
                                          reduction="none")
             m.native_tail = native
+            m.incremental_first = incremental
             m.max_stack = 48   # several chunks per permutation
-            tables[native] = m.run(layer, find_best_evaluation_module=True)
+            tables[(native, incremental)] = m.run(layer, find_best_evaluation_module=True)
             assert m.last_run_info["native_tail"] is bool(native), m.last_run_info
+            # classifier.1's tail is a single ReLU->Dropout->Linear->ReLU->Linear chain: its first
+            # layer is chained to another one, so every tag here has an incremental form
+            assert m.last_run_info["incremental_first"] is bool(native and incremental), m.last_run_info
             if native:
-                print(tag, "verify rel err", m.last_run_info["native"])
-        diff = np.abs(tables["auto"] - tables[False]).max()
-        print(tag, "max |native - forward_partial| =", diff, "max |score| =", np.abs(tables[False]).max())
-        assert diff <= 2e-5   # differences of losses ~2.3: a few fp32 ulps of the loss
+                print(tag, "incremental" if incremental else "direct", m.last_run_info["native"])
+        ref = tables[(False, False)]
+        for key in (("auto", True), ("auto", False)):
+            diff = np.abs(tables[key] - ref).max()
+            print(tag, key, "max |native - forward_partial| =", diff, "max |score| =", np.abs(ref).max())
+            assert diff <= 2e-5   # differences of losses ~2.3: a few fp32 ulps of the loss
     finally:
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 

@@ -62,6 +62,11 @@ _SIGNATURES = {
     "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
                                           _vp, _vp, _vp]),
     "tp_maxpool2_split_nhwc": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "tp_channel_contrib": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, ctypes.c_int, ctypes.c_int,
+                                          _i64, _vp, _vp]),
+    "tp_contrib_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
+    "tp_prefix_contrib_stack": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64, _i64,
+                                               _i64, ctypes.c_int, ctypes.c_int, _vp, _vp, _vp]),
 }
 
 _lib = None
@@ -418,3 +423,42 @@ def ce_mean_acc(logits, target, P, B):
                                      mean_loss.data_ptr(), correct.data_ptr(), _stream(logits)),
                "tp_ce_mean_acc")
     return mean_loss, correct
+
+
+# ---------------------------------------------------------------- incremental first layer
+def channel_contrib(z4, wt, pool, mode, out):
+    """out[c] = first layer applied to channel c of z4 alone ([C, pixels*C1] fp32)."""
+    z4 = _cuda_f32(z4, "z")
+    B, C, H, W = z4.shape
+    C1 = wt.shape[2]
+    Hp, Wp = (H // 2, W // 2) if pool else (H, W)
+    pixels = B * Hp * Wp if mode == 0 else B
+    if out.numel() < C * pixels * C1:
+        raise TorchPrunerB200Error("channel_contrib: output buffer too small")
+    flops = 2 * C * pixels * C1 * wt.shape[1]
+    with torch.cuda.device(z4.device), _launch("channel_contrib", 4 * C * pixels * C1, z4, 1, flops):
+        _check(load().tp_channel_contrib(z4.data_ptr(), wt.data_ptr(), B, C, H, W, int(bool(pool)),
+                                         int(mode), C1, out.data_ptr(), _stream(z4)),
+               "tp_channel_contrib")
+    return pixels
+
+
+def contrib_sum(T, C, M1, s_all):
+    with torch.cuda.device(T.device), _launch("contrib_sum", 4 * C * M1, T):
+        _check(load().tp_contrib_sum(T.data_ptr(), int(C), int(M1), s_all.data_ptr(), _stream(T)),
+               "tp_contrib_sum")
+
+
+def prefix_contrib_stack(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp, pool, relu,
+                         out_hi=None, out_lo=None):
+    m_out = (pixels // 4 if pool else pixels) * C1
+    if out_hi is not None and (out_hi.numel() < P * m_out or out_lo.numel() < P * m_out):
+        raise TorchPrunerB200Error("prefix_contrib_stack: output buffers too small")
+    nbytes = 4 * P * pixels * C1 + (8 * P * m_out if out_hi is not None else 0)
+    with torch.cuda.device(T.device), _launch("prefix_contrib_stack", nbytes, T):
+        _check(load().tp_prefix_contrib_stack(
+            T.data_ptr(), perm.data_ptr(), int(k0), int(P), base.data_ptr(), scale.data_ptr(),
+            shift.data_ptr(), int(pixels), int(C1), int(Hp), int(Wp), int(bool(pool)),
+            int(bool(relu)), out_hi.data_ptr() if out_hi is not None else 0,
+            out_lo.data_ptr() if out_lo is not None else 0, _stream(T)), "tp_prefix_contrib_stack")
+    return m_out

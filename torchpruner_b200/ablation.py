@@ -20,7 +20,8 @@ from .utils import find_best_module_for_attributions
 
 
 def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evaluation_module=True,
-                   max_stack_bytes=512 << 20, max_stack=512, native_tail=True):
+                   max_stack_bytes=512 << 20, max_stack=512, native_tail=True,
+                   incremental_first=True):
     """Losses and accuracies after removing ``ranking[0]``, ``ranking[:2]``, ... of ``module``.
 
     x, y: one batch on the model's CUDA device (the notebook uses 1000 test images).
@@ -56,14 +57,17 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
             found, native, info = cached_plan(model, module_nl, z)
             if not found:
                 native = NativeTail.build(model, module_nl, z)
+        ranking_dev = torch.from_numpy(ranking).to(z.device)
         if native is not None:
+            native.prepare_batch(z, allow_incremental=incremental_first)
             per_copy = 8 * native.stack_elems(B, 1)
             P_max = int(max(1, min(max_stack, n, max_stack_bytes // per_copy)))
             buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))), dtype=torch.float32,
                                  device=z.device)
             buf_lo = torch.empty_like(buf_hi)
             if not found:
-                ok, err = native.verify(model, module_nl, z, inv_dev, 0, min(2, n), buf_hi, buf_lo)
+                ok, err = native.verify(model, module_nl, z, ranking_dev, inv_dev, 0, min(2, n),
+                                        buf_hi, buf_lo)
                 info = {"verified": ok, "verify_rel_err": err}
                 if not ok:
                     native = None
@@ -76,6 +80,8 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
             stack = torch.empty((P_max * B,) + tuple(z.shape[1:]), dtype=torch.float32, device=z.device)
 
         losses, counts = [], []
+        if native is not None:
+            native.begin(ranking_dev, 0)
         for k0 in range(0, n, P_max):
             P = min(P_max, n - k0)
             if native is not None:

@@ -80,6 +80,9 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         # "auto": run recognised conv/BN/ReLU/pool/linear tails on the tcgen05 3xTF32 engine after
         # checking it against forward_partial; False: always call forward_partial.
         self.native_tail = os.environ.get("TORCHPRUNER_B200_NATIVE", "1") != "0" and "auto"
+        # first layer of the tail evaluated incrementally along each permutation (one channel's
+        # contribution subtracted per mask) instead of once per mask
+        self.incremental_first = os.environ.get("TORCHPRUNER_B200_INCREMENTAL", "1") != "0"
         self.last_run_info = {}
 
     def run(self, module, sv_samples=None, **kwargs):
@@ -193,6 +196,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                     else:
                         native = NativeTail.build(self.model, module, z)
                 if native is not None:
+                    native.prepare_batch(z, allow_incremental=self.incremental_first)
                     per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
                     P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
                     buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
@@ -200,8 +204,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                     buf_lo = torch.empty_like(buf_hi)
                     if not found:
                         j0, k0v, _ = spans[0]
-                        ok, verr = native.verify(self.model, module, z, inv_dev[j0], k0v, min(2, n),
-                                                 buf_hi, buf_lo)
+                        ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0], k0v,
+                                                 min(2, n), buf_hi, buf_lo)
                         native_info = {"verified": ok, "verify_rel_err": verr}
                         if not ok:
                             native = None
@@ -242,6 +246,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 self.set_deterministic()
                 for (j, k_begin, k_end) in spans:
                     prev_in, prev_out = prev_a, prev_b
+                    if native is not None:
+                        native.begin(perm_dev[j], max(k_begin - 1, 0))
                     if k_begin == 0:
                         prev_in.copy_(loss0)
                     else:  # halo: loss with the first k_begin channels of permutation j removed
@@ -261,6 +267,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 allreduce_scores(sv, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
+                                  "incremental_first": bool(native is not None and native.incremental),
                                   "native": native_info}
             return sv
 

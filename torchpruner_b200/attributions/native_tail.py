@@ -24,6 +24,7 @@ import torch.nn as nn
 from .. import _lib
 
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+INCREMENTAL_MAX_BYTES = 12 << 30   # per-channel contributions of the first layer, per batch
 
 
 class _Unsupported(Exception):
@@ -106,12 +107,20 @@ def _is_pool2(m):
 class NativeTail:
     """Execution plan for one evaluation module of one model."""
 
-    def __init__(self, steps, pool_first, in_shape, n_out):
+    def __init__(self, steps, pool_first, in_shape, n_out, first=None):
         self.steps = steps            # list of dicts
         self.pool_first = pool_first
         self.in_shape = in_shape      # (C, H, W) of the evaluation module's output
         self.n_out = n_out
         self.flops_per_example = sum(s["flops"] for s in steps)
+        # Incremental first layer (csrc/incremental.cu): the masks of one permutation are
+        # nested and the first layer is linear in the activation, so its output for mask k is
+        # the previous one minus the contribution of one channel.
+        self.first = first            # dict or None
+        self.incremental = False      # decided per batch in prepare_batch()
+        self._T = self._s_all = self._base = None
+        self._perm = None
+        self._pos = 0
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -153,6 +162,7 @@ class NativeTail:
                 raise _Unsupported("odd spatial size before pooling")
             pool_first, H, W, i = True, H // 2, W // 2, 1
         steps = []
+        first = None
         flat = z.dim() == 2
         dev = z.device
         while i < len(mods):
@@ -228,6 +238,17 @@ class NativeTail:
             steps.append({"taps": taps, "cin": C, "cout": cout, "H": H, "W": W, "relu": relu,
                           "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale,
                           "shift": shift, "flops": 2 * H * W * cout * taps * C})
+            if len(steps) == 1 and cout % 4 == 0:
+                if taps == 9:   # [Cout, Cin, 3, 3] -> [Cin, 9, Cout]
+                    wt = m.weight.detach().float().permute(1, 2, 3, 0).reshape(C, 9, cout)
+                    first = {"mode": 0, "Hp": H, "Wp": W}
+                else:           # [Cout, Cz*S] (NCHW flatten order) -> [Cz, S, Cout]
+                    cz = z.shape[1]
+                    sp = m.in_features // cz
+                    wt = m.weight.detach().float().view(cout, cz, sp).permute(1, 2, 0)
+                    first = {"mode": 1, "Hp": 1, "Wp": 1}
+                first.update(wt=wt.contiguous(), C1=cout, scale=scale, shift=shift, relu=relu,
+                             pool=pool)
             C = cout
             if pool:
                 H, W = H // 2, W // 2
@@ -235,21 +256,86 @@ class NativeTail:
                 or H * W != 1:
             raise _Unsupported("tail does not end in a linear read-out")
         in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
-        return cls(steps, pool_first, in_shape, logits.shape[1])
+        if len(steps) < 2:
+            first = None   # the only layer produces the logits: nothing to chain after it
+        return cls(steps, pool_first, in_shape, logits.shape[1], first)
 
     # ------------------------------------------------------------------ execution
+    def _first_out_geometry(self, B):
+        """(pixels of the first layer's output, elements of its post-pool output) per mask."""
+        f = self.first
+        pixels = B * f["Hp"] * f["Wp"]
+        return pixels, (pixels // 4 if f["pool"] else pixels) * f["C1"]
+
+    def prepare_batch(self, z, allow_incremental=True):
+        """Once per batch: per-channel contributions of the first layer and their float64 sum."""
+        self.incremental = False
+        if self.first is None or not allow_incremental:
+            return
+        f = self.first
+        z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
+        B, C = z4.shape[0], z4.shape[1]
+        pixels, _ = self._first_out_geometry(B)
+        M1 = pixels * f["C1"]
+        if C * M1 * 4 > INCREMENTAL_MAX_BYTES:
+            return
+        if self._T is None or self._T.numel() < C * M1 or self._T.device != z.device:
+            self._T = torch.empty(C * M1, dtype=torch.float32, device=z.device)
+            self._s_all = torch.empty(M1, dtype=torch.float64, device=z.device)
+            self._base = torch.empty(M1, dtype=torch.float64, device=z.device)
+        _lib.channel_contrib(z4, f["wt"], self.pool_first, f["mode"], self._T)
+        _lib.contrib_sum(self._T, C, M1, self._s_all)
+        self._M1, self._pixels = M1, pixels
+        self.incremental = True
+
+    def begin(self, perm, k_start):
+        """Start (or restart) a run of consecutive prefixes of permutation `perm` at k_start."""
+        self._perm, self._pos = perm, int(k_start)
+        if not self.incremental:
+            return
+        f = self.first
+        base = self._base[:self._M1]
+        base.copy_(self._s_all[:self._M1])
+        if k_start > 0:   # a sharded rank starts mid-permutation: skip the prefix without output
+            _lib.prefix_contrib_stack(self._T, perm, 0, int(k_start), base, f["scale"], f["shift"],
+                                      self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"])
+
     def stack_elems(self, B, P):
+        """Floats (per hi / lo buffer) of the stacked input of the chained layers for P masks."""
+        if self.first is not None:
+            direct = self._direct_stack_elems(B, P)
+            return max(direct, P * self._first_out_geometry(B)[1])
+        return self._direct_stack_elems(B, P)
+
+    def _direct_stack_elems(self, B, P):
         C, H, W = self.in_shape
         if self.pool_first:
             H, W = H // 2, W // 2
         return P * B * C * H * W
 
     def logits(self, z, inv_perm, k0, P, buf_hi, buf_lo):
-        """[P*B, n_out] fp32 logits of the P prefix masks k0 .. k0+P-1 of one permutation."""
-        z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
-        x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo)
-        last = len(self.steps) - 1
-        for idx, s in enumerate(self.steps):
+        """[P*B, n_out] fp32 logits of the P prefix masks k0 .. k0+P-1 of the current
+        permutation.  In incremental mode calls must walk the prefixes consecutively from the
+        position given to begin()."""
+        B = z.shape[0]
+        if self.incremental:
+            if k0 != self._pos:
+                raise RuntimeError("incremental tail evaluated out of order")
+            f = self.first
+            m_out = _lib.prefix_contrib_stack(
+                self._T, self._perm, k0, P, self._base[:self._M1], f["scale"], f["shift"],
+                self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"], buf_hi, buf_lo)
+            self._pos += P
+            Ho, Wo = (f["Hp"] // 2, f["Wp"] // 2) if f["pool"] else (f["Hp"], f["Wp"])
+            shape = (P * B, Ho, Wo, f["C1"])
+            x_hi, x_lo = buf_hi[:P * m_out].view(shape), buf_lo[:P * m_out].view(shape)
+            steps = self.steps[1:]
+        else:
+            z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
+            x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo)
+            steps = self.steps
+        last = len(steps) - 1
+        for idx, s in enumerate(steps):
             n = x_hi.shape[0]
             if s["taps"] == 1 and x_hi.dim() == 4 and x_hi.shape[1] * x_hi.shape[2] != 1:
                 x_hi = x_hi.reshape(n, 1, 1, -1)
@@ -262,14 +348,22 @@ class NativeTail:
             x_hi, x_lo = y_hi, y_lo
         return x_hi.view(x_hi.shape[0], self.n_out)
 
-    def verify(self, model, module, z, inv_perm, k0, P, buf_hi, buf_lo):
-        """True iff the plan reproduces ``forward_partial`` on P real masks of this run."""
-        mine = self.logits(z, inv_perm, k0, P, buf_hi, buf_lo)
+    def verify(self, model, module, z, perm, inv_perm, k0, P, buf_hi, buf_lo):
+        """True iff the plan reproduces ``forward_partial`` on P real masks of this run (both the
+        incremental and the direct form of the first layer are checked)."""
         stacked = _lib.prefix_mask_stack(z, inv_perm, k0, P)
         with torch.no_grad():
             ref = model.forward_partial(stacked, to_module=None, from_module=module)
-        if ref.shape != mine.shape:
-            return False, float("inf")
         scale = float(ref.abs().max().clamp_min(1e-30))
-        err = float((ref - mine).abs().max()) / scale
-        return err <= VERIFY_RTOL, err
+        worst = 0.0
+        was_incremental = self.incremental
+        for mode in ([True, False] if was_incremental else [False]):
+            self.incremental = mode
+            self.begin(perm, k0)
+            mine = self.logits(z, inv_perm, k0, P, buf_hi, buf_lo)
+            if ref.shape != mine.shape:
+                self.incremental = was_incremental
+                return False, float("inf")
+            worst = max(worst, float((ref - mine).abs().max()) / scale)
+        self.incremental = was_incremental
+        return worst <= VERIFY_RTOL, worst

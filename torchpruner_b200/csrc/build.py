@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 LIB_NAME = "libtorchpruner_b200.so"
 LIB_PATH = os.path.join(HERE, LIB_NAME)
 
-SOURCES = ["api.cu", "reduce_rows.cu", "shapley.cu", "gather.cu", "nan_trick.cu", "conv_tf32x3.cu"]
+SOURCES = ["api.cu", "reduce_rows.cu", "shapley.cu", "gather.cu", "nan_trick.cu", "conv_tf32x3.cu", "incremental.cu"]
 HEADERS = ["common.cuh", os.path.join(ROOT, "include", "torchpruner_b200.h")]
 
 NVCC_FLAGS = [

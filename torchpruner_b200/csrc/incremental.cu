@@ -1,0 +1,338 @@
+// Incremental evaluation of the FIRST layer after the evaluation module.
+//
+// Along one Shapley permutation the masks are nested: mask k removes channels pi_0..pi_k of the
+// cached activation z.  The first downstream layer (conv3x3 or linear) is linear in z, so its
+// pre-activation under mask k is
+//        S_k = S_all - sum_{j<=k} T_{pi_j},      T_c = layer(z restricted to channel c),
+// and the whole ladder S_0..S_{C-1} costs ONE layer evaluation (the C per-channel contributions
+// T_c, computed once per batch in exact fp32 FMA arithmetic) plus a memory-bound prefix sweep,
+// instead of C tensor-core evaluations of the layer — 26 % of all FLOPs of the VGG16 job
+// (reference shapley_values.py:55-57 re-runs the full layer for every k).
+//
+//  * channel_contrib_kernel   T[c][pixel][o]  = sum_taps z'(pixel+tap, c) * Wt[c][tap][o]
+//  * contrib_sum_kernel       S_all[e]        = sum_c T[c][e]            (float64)
+//  * prefix_contrib_stack     for p < P:  run -= T[perm[k0+p]];  out[p] = split(act(run*a+b))
+//                             with the running sum carried in float64 between chunks, the optional
+//                             MaxPool2d(2) that follows the layer folded in, and an
+//                             accumulate-only mode (no output) to position a sharded rank at the
+//                             start of its span.
+#include "common.cuh"
+
+namespace tp {
+
+__device__ __forceinline__ float inc_tf32_hi(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+// z: NCHW [B, C, H, W]; pool != 0 => z' = MaxPool2d(2)(z), spatial Hp x Wp.
+__device__ __forceinline__ float zprime(const float* __restrict__ z, int b, int c, int h, int w,
+                                        int C, int H, int W, int pool) {
+  const float* src = z + (((long long)b * C + c) * H) * W;
+  if (!pool) return src[h * W + w];
+  const float* p0 = src + (2 * h) * W + 2 * w;
+  return fmaxf(fmaxf(p0[0], p0[1]), fmaxf(p0[W], p0[W + 1]));
+}
+
+// mode 0: conv3x3 pad 1 over the Hp x Wp grid, 9 taps, output pixel = (b, h, w)
+// mode 1: dense over all Hp*Wp positions (taps = Hp*Wp), output "pixel" = b
+// wt: [C][taps][C1]; T: [C][pixels][C1].  One thread per (pixel, 4 outputs).
+__global__ void __launch_bounds__(256)
+channel_contrib_kernel(const float* __restrict__ z, const float* __restrict__ wt,
+                       float* __restrict__ T, int B, int C, int H, int W, int pool, int mode,
+                       int C1, long long pixels) {
+  const int c = blockIdx.y;
+  const int Hp = pool ? H / 2 : H, Wp = pool ? W / 2 : W;
+  const int taps = mode == 0 ? 9 : Hp * Wp;
+  const unsigned opp = (unsigned)C1 >> 2;  // float4 groups per pixel
+  // per-channel work fits 32-bit indices (checked on the host): 64-bit divisions per item would
+  // cost more than the 36 FMAs the item performs
+  const unsigned items = (unsigned)pixels * opp;
+  const float4* w4 = reinterpret_cast<const float4*>(wt) + (long long)c * taps * opp;
+  float4* out4 = reinterpret_cast<float4*>(T) + (long long)c * pixels * opp;
+  for (unsigned it = blockIdx.x * blockDim.x + threadIdx.x; it < items; it += gridDim.x * blockDim.x) {
+    const unsigned pix = it / opp;
+    const unsigned o4 = it - pix * opp;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (mode == 0) {
+      const int w = (int)(pix % (unsigned)Wp);
+      const unsigned t = pix / (unsigned)Wp;
+      const int h = (int)(t % (unsigned)Hp);
+      const int b = (int)(t / (unsigned)Hp);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int hh = h + r - 1;
+        if (hh < 0 || hh >= Hp) continue;
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          const int ww = w + s - 1;
+          if (ww < 0 || ww >= Wp) continue;
+          const float zv = zprime(z, b, c, hh, ww, C, H, W, pool);
+          const float4 wv = w4[(r * 3 + s) * opp + o4];
+          acc.x = fmaf(zv, wv.x, acc.x);
+          acc.y = fmaf(zv, wv.y, acc.y);
+          acc.z = fmaf(zv, wv.z, acc.z);
+          acc.w = fmaf(zv, wv.w, acc.w);
+        }
+      }
+    } else {
+      const int b = (int)pix;
+      for (int tp = 0; tp < taps; ++tp) {
+        const float zv = zprime(z, b, c, tp / Wp, tp % Wp, C, H, W, pool);
+        const float4 wv = w4[tp * opp + o4];
+        acc.x = fmaf(zv, wv.x, acc.x);
+        acc.y = fmaf(zv, wv.y, acc.y);
+        acc.z = fmaf(zv, wv.z, acc.z);
+        acc.w = fmaf(zv, wv.w, acc.w);
+      }
+    }
+    out4[it] = acc;
+  }
+}
+
+// conv3x3 specialisation: a thread keeps the 9 x 4 weights of its output group in registers and
+// walks pixels, so per pixel it issues 9 (warp-broadcast) activation loads, 36 FMAs and one
+// 16-byte store.  (The generic kernel above re-reads the 18 KB weight slab of the channel from L1
+// for every pixel and is L1-bandwidth bound.)  Requires C1/4 to be a power of two <= 256.
+__global__ void __launch_bounds__(256)
+channel_contrib_conv_kernel(const float* __restrict__ z, const float* __restrict__ wt,
+                            float* __restrict__ T, int B, int C, int H, int W, int pool, int C1,
+                            unsigned pixels) {
+  const int c = blockIdx.y;
+  const int Hp = pool ? H / 2 : H, Wp = pool ? W / 2 : W;
+  const unsigned opp = (unsigned)C1 >> 2;
+  const unsigned o4 = threadIdx.x % opp;
+  const unsigned pl = threadIdx.x / opp;
+  const unsigned ppb = blockDim.x / opp;
+  const float4* w4 = reinterpret_cast<const float4*>(wt) + (long long)c * 9 * opp;
+  float4 wreg[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wreg[t] = w4[t * opp + o4];
+  float4* out4 = reinterpret_cast<float4*>(T) + (long long)c * pixels * opp;
+  for (unsigned pix = blockIdx.x * ppb + pl; pix < pixels; pix += gridDim.x * ppb) {
+    const int w = (int)(pix % (unsigned)Wp);
+    const unsigned t = pix / (unsigned)Wp;
+    const int h = (int)(t % (unsigned)Hp);
+    const int b = (int)(t / (unsigned)Hp);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int hh = h + r - 1;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int ww = w + s - 1;
+        const bool in = hh >= 0 && hh < Hp && ww >= 0 && ww < Wp;
+        const float zv = in ? zprime(z, b, c, hh, ww, C, H, W, pool) : 0.f;
+        const float4 wv = wreg[r * 3 + s];
+        acc.x = fmaf(zv, wv.x, acc.x);
+        acc.y = fmaf(zv, wv.y, acc.y);
+        acc.z = fmaf(zv, wv.z, acc.z);
+        acc.w = fmaf(zv, wv.w, acc.w);
+      }
+    }
+    out4[(unsigned long long)pix * opp + o4] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+contrib_sum_kernel(const float* __restrict__ T, int C, long long M1, double* __restrict__ s_all) {
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < M1;
+       e += gridDim.x * (long long)blockDim.x) {
+    double s = 0.0;
+    for (int c = 0; c < C; ++c) s += (double)T[(long long)c * M1 + e];
+    s_all[e] = s;
+  }
+}
+
+struct PrefixGeom {
+  long long M1;      // elements of one contribution / of the running sum: pixels * C1
+  int C1;
+  int pool;          // MaxPool2d(2) after the activation: output [B, Hp/2, Wp/2, C1]
+  int Hp, Wp;        // spatial size of the layer's output (before that pool)
+  int relu;
+  int emit;          // 0: accumulate only (advance the running sum), 1: write out_hi / out_lo
+};
+
+__device__ __forceinline__ float affine_act(double run, float a, float b, int relu) {
+  float t = fmaf((float)run, a, b);
+  return relu ? fmaxf(t, 0.f) : t;
+}
+
+// One thread owns 4 consecutive output channels of one output position (after the optional pool)
+// and walks the P masks of the chunk with its running sums in float64 registers.
+template <bool POOL>
+__global__ void __launch_bounds__(256)
+prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restrict__ perm,
+                            long long k0, int P, double* __restrict__ base,
+                            const float* __restrict__ scale, const float* __restrict__ shift,
+                            PrefixGeom g, float* __restrict__ out_hi, float* __restrict__ out_lo) {
+  constexpr int NSRC = POOL ? 4 : 1;
+  const int opp = g.C1 >> 2;
+  const long long out_pos = POOL ? (g.M1 / g.C1) / 4 : (g.M1 / g.C1);  // output positions
+  const long long items = out_pos * opp;
+  const long long m_out = out_pos * g.C1;
+  for (long long it = blockIdx.x * (long long)blockDim.x + threadIdx.x; it < items;
+       it += gridDim.x * (long long)blockDim.x) {
+    const long long pos = it / opp;
+    const int o4 = (int)(it - pos * opp);
+    const float4 a = reinterpret_cast<const float4*>(scale)[o4];
+    const float4 b = reinterpret_cast<const float4*>(shift)[o4];
+    long long src[NSRC];
+    if (POOL) {
+      const int Wo = g.Wp / 2, Ho = g.Hp / 2;
+      const int wo = (int)(pos % Wo);
+      const long long t = pos / Wo;
+      const int ho = (int)(t % Ho);
+      const long long bi = t / Ho;
+      const long long p00 = (bi * g.Hp + 2 * ho) * g.Wp + 2 * wo;
+      src[0] = p00;
+      src[NSRC > 1 ? 1 : 0] = p00 + 1;
+      src[NSRC > 1 ? 2 : 0] = p00 + g.Wp;
+      src[NSRC > 1 ? 3 : 0] = p00 + g.Wp + 1;
+      src[0] = p00;
+    } else {
+      src[0] = pos;
+    }
+    double run[NSRC][4];
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      const double* bp = base + src[s] * g.C1 + o4 * 4;
+      run[s][0] = bp[0];
+      run[s][1] = bp[1];
+      run[s][2] = bp[2];
+      run[s][3] = bp[3];
+    }
+    for (int p = 0; p < P; ++p) {
+      const long long c = perm[k0 + p];
+      const float* Tc = T + c * g.M1;
+      float4 y = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+      for (int s = 0; s < NSRC; ++s) {
+        const float4 t = *reinterpret_cast<const float4*>(Tc + src[s] * g.C1 + o4 * 4);
+        run[s][0] -= (double)t.x;
+        run[s][1] -= (double)t.y;
+        run[s][2] -= (double)t.z;
+        run[s][3] -= (double)t.w;
+        if (g.emit) {
+          y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu));
+          y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu));
+          y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu));
+          y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu));
+        }
+      }
+      if (g.emit) {
+        const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
+                                      inc_tf32_hi(y.w));
+        const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
+                                      inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
+        const long long o = (long long)p * m_out + pos * g.C1 + o4 * 4;
+        *reinterpret_cast<float4*>(out_hi + o) = hi;
+        *reinterpret_cast<float4*>(out_lo + o) = lo;
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      double* bp = base + src[s] * g.C1 + o4 * 4;
+      bp[0] = run[s][0];
+      bp[1] = run[s][1];
+      bp[2] = run[s][2];
+      bp[3] = run[s][3];
+    }
+  }
+}
+
+static inline unsigned inc_grid(long long items, int waves = 16) {
+  long long blocks = (items + 255) / 256;
+  const long long cap = (long long)sm_count() * waves;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+}  // namespace tp
+
+extern "C" {
+
+int tp_channel_contrib(const float* z, const float* wt, int64_t B, int64_t C, int64_t H, int64_t W,
+                       int pool, int mode, int64_t C1, float* T, tp_stream_t stream) {
+  using namespace tp;
+  TP_REQUIRE(B >= 0 && C >= 0 && H > 0 && W > 0 && C1 > 0, TP_ERR_INVALID,
+             "tp_channel_contrib: bad dimension");
+  TP_REQUIRE(mode == 0 || mode == 1, TP_ERR_INVALID, "tp_channel_contrib: mode must be 0 or 1");
+  TP_REQUIRE(C1 % 4 == 0, TP_ERR_LIMIT, "tp_channel_contrib: C1 must be a multiple of 4");
+  TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
+             "tp_channel_contrib: pooling needs even H and W");
+  TP_REQUIRE(C <= 65535, TP_ERR_LIMIT, "tp_channel_contrib: too many channels");
+  if (B == 0 || C == 0) return TP_OK;
+  TP_REQUIRE(z && wt && T, TP_ERR_INVALID, "tp_channel_contrib: NULL pointer");
+  const int Hp = pool ? (int)H / 2 : (int)H, Wp = pool ? (int)W / 2 : (int)W;
+  const long long pixels = mode == 0 ? (long long)B * Hp * Wp : (long long)B;
+  TP_REQUIRE(pixels * (C1 / 4) < (1ll << 31), TP_ERR_LIMIT,
+             "tp_channel_contrib: more than 2^31 items per channel");
+  const long long opp = C1 / 4;
+  if (mode == 0 && opp <= 256 && (opp & (opp - 1)) == 0) {
+    const long long ppb = 256 / opp;
+    long long bx = (pixels + ppb - 1) / ppb;
+    const long long cap = ((long long)sm_count() * 8 + C - 1) / C;  // ~8 CTAs/SM over all channels
+    if (bx > cap) bx = cap < 1 ? 1 : cap;
+    dim3 grid((unsigned)bx, (unsigned)C);
+    channel_contrib_conv_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        z, wt, T, (int)B, (int)C, (int)H, (int)W, pool, (int)C1, (unsigned)pixels);
+    TP_LAUNCH_CHECK("channel_contrib_conv_kernel");
+    return TP_OK;
+  }
+  dim3 grid(inc_grid(pixels * (C1 / 4), 4), (unsigned)C);
+  channel_contrib_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, wt, T, (int)B, (int)C, (int)H, (int)W, pool, mode, (int)C1, pixels);
+  TP_LAUNCH_CHECK("channel_contrib_kernel");
+  return TP_OK;
+}
+
+int tp_contrib_sum(const float* T, int64_t C, int64_t M1, double* s_all, tp_stream_t stream) {
+  TP_REQUIRE(C >= 0 && M1 >= 0, TP_ERR_INVALID, "tp_contrib_sum: negative size");
+  if (M1 == 0) return TP_OK;
+  TP_REQUIRE(T && s_all, TP_ERR_INVALID, "tp_contrib_sum: NULL pointer");
+  tp::contrib_sum_kernel<<<tp::inc_grid(M1), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      T, (int)C, M1, s_all);
+  TP_LAUNCH_CHECK("contrib_sum_kernel");
+  return TP_OK;
+}
+
+int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                            double* base, const float* scale, const float* shift, int64_t pixels,
+                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int relu, float* out_hi,
+                            float* out_lo, tp_stream_t stream) {
+  using namespace tp;
+  TP_REQUIRE(P >= 0 && k0 >= 0 && pixels >= 0 && C1 > 0, TP_ERR_INVALID,
+             "tp_prefix_contrib_stack: bad dimension");
+  TP_REQUIRE(C1 % 4 == 0, TP_ERR_LIMIT, "tp_prefix_contrib_stack: C1 must be a multiple of 4");
+  TP_REQUIRE(!pool || (Hp % 2 == 0 && Wp % 2 == 0 && Hp > 0 && Wp > 0 && pixels % (Hp * Wp) == 0),
+             TP_ERR_INVALID, "tp_prefix_contrib_stack: pooling needs even Hp, Wp dividing pixels");
+  TP_REQUIRE((out_hi == nullptr) == (out_lo == nullptr), TP_ERR_INVALID,
+             "tp_prefix_contrib_stack: out_hi and out_lo must both be given or both be NULL");
+  if (P == 0 || pixels == 0) return TP_OK;
+  TP_REQUIRE(T && perm && base && scale && shift, TP_ERR_INVALID,
+             "tp_prefix_contrib_stack: NULL pointer");
+  PrefixGeom g;
+  g.M1 = pixels * C1;
+  g.C1 = (int)C1;
+  g.pool = pool;
+  g.Hp = (int)Hp;
+  g.Wp = (int)Wp;
+  g.relu = relu;
+  g.emit = out_hi != nullptr;
+  const long long items = (pool ? pixels / 4 : pixels) * (C1 / 4);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (pool) {
+    prefix_contrib_stack_kernel<true><<<inc_grid(items), 256, 0, st>>>(
+        T, perm, k0, (int)P, base, scale, shift, g, out_hi, out_lo);
+  } else {
+    prefix_contrib_stack_kernel<false><<<inc_grid(items), 256, 0, st>>>(
+        T, perm, k0, (int)P, base, scale, shift, g, out_hi, out_lo);
+  }
+  TP_LAUNCH_CHECK("prefix_contrib_stack_kernel");
+  return TP_OK;
+}
+
+}  // extern "C"
