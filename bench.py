@@ -66,7 +66,8 @@ def workload_description(n_gpus):
     return {
         "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
                     "BN+ReLU, one permutation per GPU per step = 4224 channel-evals/GPU/step "
-                    "(25 steps = the sv_samples=25 job); fp32 downstream layers, TF32 off",
+                    "(25 steps = the sv_samples=25 job); layers after the scored module run fp32-accurate "
+                    "(tcgen05 3xTF32 engine, verified against forward_partial; cuDNN/cuBLAS TF32 off)",
         "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224,
         "sv_samples_per_step": n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
         "l2": "working set per step (stacked masked activations, up to 512 MiB per chunk) far "

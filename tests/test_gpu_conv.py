@@ -179,3 +179,65 @@ def test_native_tail_declines_unsupported_models():
         z = model.forward_partial(x, to_module=model.features[4])   # pool -> flatten -> fc -> fc
     tail = NativeTail.build(model, model.features[4], z)
     assert tail is not None and tail.pool_first and len(tail.steps) == 2
+
+
+@pytest.mark.parametrize("B,C,H,W,C1,pool_first,mode,pool_after", [
+    (3, 8, 8, 8, 32, False, 0, False),
+    (2, 6, 8, 8, 16, True, 0, True),     # MaxPool before the layer and after it
+    (4, 5, 4, 4, 64, False, 0, True),
+    (5, 12, 4, 4, 24, True, 1, False),   # pool -> flatten -> Linear (taps = 4 positions)
+    (7, 16, 1, 1, 32, False, 1, False),  # plain Linear on a [B, C] activation
+])
+def test_incremental_first_layer_kernels(B, C, H, W, C1, pool_first, mode, pool_after):
+    """tp_channel_contrib / tp_contrib_sum / tp_prefix_contrib_stack against float64 torch."""
+    gen = torch.Generator().manual_seed(B * 100 + C)
+    z = torch.relu(torch.randn((B, C, H, W), generator=gen))
+    zp = F.max_pool2d(z, 2) if pool_first else z
+    Hp, Wp = zp.shape[2], zp.shape[3]
+    if mode == 0:
+        w = torch.randn((C1, C, 3, 3), generator=gen) / 3.0
+        wt = w.permute(1, 2, 3, 0).reshape(C, 9, C1).contiguous()
+        per_channel = [F.conv2d(zp[:, c:c + 1].double(), w[:, c:c + 1].double(), padding=1) for c in range(C)]
+        want_T = torch.stack([t.permute(0, 2, 3, 1).reshape(-1) for t in per_channel])   # NHWC
+        oh, ow = Hp, Wp
+    else:
+        S = Hp * Wp
+        w = torch.randn((C1, C * S), generator=gen) / (C * S) ** 0.5
+        wt = w.view(C1, C, S).permute(1, 2, 0).contiguous()
+        want_T = torch.stack([(zp[:, c].reshape(B, S).double() @ w.view(C1, C, S)[:, c].double().t()).reshape(-1)
+                              for c in range(C)])
+        oh, ow = 1, 1
+    M1 = want_T.shape[1]
+    T = torch.empty(C * M1, device=DEV)
+    pixels = _lib.channel_contrib(z.to(DEV), wt.to(DEV), pool_first, mode, T)
+    assert pixels * C1 == M1
+    got_T = T.view(C, M1).cpu().double()
+    assert float((got_T - want_T).abs().max()) <= 1e-6 * float(want_T.abs().max())
+    s_all = torch.empty(M1, dtype=torch.float64, device=DEV)
+    _lib.contrib_sum(T, C, M1, s_all)
+    assert float((s_all.cpu() - got_T.sum(0)).abs().max()) <= 1e-12 * float(want_T.abs().max()) * C
+
+    perm = np.random.RandomState(C).permutation(C)
+    perm_dev = torch.from_numpy(perm.astype(np.int64)).to(DEV)
+    scale = (torch.rand(C1, generator=gen) + 0.5).to(DEV)
+    shift = (torch.randn(C1, generator=gen) * 0.1).to(DEV)
+    base = s_all.clone()
+    skip = 2   # a sharded rank skips a prefix without producing output
+    _lib.prefix_contrib_stack(T, perm_dev, 0, skip, base, scale, shift, pixels, C1, oh, ow, pool_after, True)
+    P = C - skip
+    m_out = (pixels // 4 if pool_after else pixels) * C1
+    hi = torch.empty(P * m_out, device=DEV)
+    lo = torch.empty_like(hi)
+    assert _lib.prefix_contrib_stack(T, perm_dev, skip, P, base, scale, shift, pixels, C1, oh, ow,
+                                     pool_after, True, hi, lo) == m_out
+    got = (hi + lo).view(P, -1).cpu().double()
+    run = got_T.sum(0) - got_T[perm[:skip]].sum(0)
+    for p in range(P):
+        run = run - got_T[perm[skip + p]]
+        y = torch.relu(run.view(-1, C1) * scale.cpu().double() + shift.cpu().double())
+        if pool_after:
+            y = F.max_pool2d(y.view(B, oh, ow, C1).permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+        want = y.reshape(-1)
+        assert float((got[p] - want).abs().max()) <= 1e-6 * max(float(want.abs().max()), 1e-3)
+    # every channel removed: the running sum is back to (numerically) nothing
+    assert float(base.abs().max()) <= 1e-12 * float(want_T.abs().max()) * C
