@@ -372,7 +372,10 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
         y_hi, y_lo = out
     flops = 2 * N * H * W * Cout * taps * Cin
     nbytes = 4 * (2 * x_hi.numel() + 2 * w_hi.numel() + (2 if split else 1) * y_hi.numel())
-    with torch.cuda.device(x_hi.device), _launch("conv_tf32x3", nbytes, x_hi, 1, flops):
+    name = "conv_tf32x3"
+    if _profile is not None and getattr(_profile, "by_shape", False):
+        name = f"conv_tf32x3[{H}x{W} {Cin}->{Cout} t{taps}]"
+    with torch.cuda.device(x_hi.device), _launch(name, nbytes, x_hi, 1, flops):
         _check(load().tp_conv_tf32x3(
             x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
             int(taps), Cout, scale.data_ptr(), shift.data_ptr(), int(bool(relu)), y_hi.data_ptr(),

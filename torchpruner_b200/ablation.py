@@ -97,6 +97,8 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
                 ct = (out.argmax(dim=1).view(P, B) == y.view(1, B)).sum(1).to(torch.int32)
             losses.append(ml)
             counts.append(ct)
+        if native is not None:
+            native.release()
         if not losses:
             return np.zeros(0, np.float32), np.zeros(0, np.float32)
         loss = torch.cat(losses).cpu().numpy()

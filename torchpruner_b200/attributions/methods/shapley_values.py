@@ -261,13 +261,16 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 self.restore_deterministic()
                 row += B
 
+            incremental_used = bool(native is not None and native.incremental)
+            if native is not None:
+                native.release()
             if sv is None:
                 return None
             if world > 1:
                 allreduce_scores(sv, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
-                                  "incremental_first": bool(native is not None and native.incremental),
+                                  "incremental_first": incremental_used,
                                   "native": native_info}
             return sv
 

@@ -225,19 +225,42 @@ class NativeTail:
                     raise _Unsupported("odd spatial size before pooling")
                 pool = True
                 i += 1
+            # A 3x3 / pad 1 convolution on a 2x2 image touches 4 of its 9 taps per output pixel
+            # (the other 5 fall in the padding): as an implicit GEMM 56 % of the MMAs multiply
+            # zeros.  It is exactly a dense map from the 4*Cin inputs of the image to its 4*Cout
+            # outputs, and NHWC [N,2,2,C] already is that [N, 4C] matrix, so the layer runs as a
+            # linear one with the weight re-indexed (no data movement, 16/36 of the MMAs).
+            dense2x2 = taps == 9 and H == 2 and W == 2
+            k_cin, k_cout, k_taps = C, cout, taps
+            if dense2x2:
+                w4 = m.weight.detach().float()
+                wd = torch.zeros((2, 2, cout, 2, 2, C), device=dev)
+                for h in range(2):
+                    for ww in range(2):
+                        for h2 in range(2):
+                            for w2 in range(2):
+                                wd[h, ww, :, h2, w2, :] = w4[:, :, h2 - h + 1, w2 - ww + 1]
+                w = wd.reshape(4 * cout, 4 * C)
+                scale, shift = scale.repeat(4), shift.repeat(4)
+                k_cin, k_cout, k_taps = 4 * C, 4 * cout, 1
             key = (_tensor_key(m.weight, m.bias) + (
                 _tensor_key(bn_used.weight, bn_used.bias, bn_used.running_mean, bn_used.running_var)
-                if bn_used is not None else ()), w.shape[1], H * W if taps == 1 else 0)
+                if bn_used is not None else ()), w.shape[1], H * W if taps == 1 else 0, dense2x2)
             store = _LAYERS.setdefault(model, {})
             prep = store.get(id(m))
             if prep is None or prep[0] != key:
                 w_hi, w_lo = _lib.tf32_split(w.contiguous())
                 prep = (key, w_hi, w_lo, scale.contiguous(), shift.contiguous())
                 store[id(m)] = prep
-            _, w_hi, w_lo, scale, shift = prep
-            steps.append({"taps": taps, "cin": C, "cout": cout, "H": H, "W": W, "relu": relu,
-                          "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale,
-                          "shift": shift, "flops": 2 * H * W * cout * taps * C})
+            _, w_hi, w_lo, scale_k, shift_k = prep
+            steps.append({"taps": k_taps, "cin": k_cin, "cout": k_cout, "H": H, "W": W, "relu": relu,
+                          "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale_k,
+                          "shift": shift_k, "out_view": (H, W, cout) if dense2x2 else None,
+                          "flops": 2 * k_cout * k_taps * k_cin * (1 if dense2x2 else H * W)})
+            if dense2x2:   # per-channel vectors for the incremental form of this layer
+                scale, shift = scale_k[:cout], shift_k[:cout]
+            else:
+                scale, shift = scale_k, shift_k
             if len(steps) == 1 and cout % 4 == 0:
                 if taps == 9:   # [Cout, Cin, 3, 3] -> [Cin, 9, Cout]
                     wt = m.weight.detach().float().permute(1, 2, 3, 0).reshape(C, 9, cout)
@@ -287,6 +310,12 @@ class NativeTail:
         _lib.contrib_sum(self._T, C, M1, self._s_all)
         self._M1, self._pixels = M1, pixels
         self.incremental = True
+
+    def release(self):
+        """Drop the per-batch scratch (contributions can be several GB); the plan itself, which is
+        cached across runs, keeps only the prepared weights."""
+        self._T = self._s_all = self._base = self._perm = None
+        self.incremental = False
 
     def begin(self, perm, k_start):
         """Start (or restart) a run of consecutive prefixes of permutation `perm` at k_start."""
@@ -343,6 +372,9 @@ class NativeTail:
             split = not (idx == last or s["pool"])
             y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w_hi"], s["w_lo"], s["taps"], s["scale"],
                                           s["shift"], s["relu"], split=split)
+            if s["out_view"] is not None:   # dense form of a conv on a 2x2 image: back to NHWC
+                y_hi = y_hi.view((n,) + s["out_view"])
+                y_lo = y_lo.view((n,) + s["out_view"]) if y_lo is not None else None
             if s["pool"]:
                 y_hi, y_lo = _lib.maxpool2_split_nhwc(y_hi)
             x_hi, x_lo = y_hi, y_lo
