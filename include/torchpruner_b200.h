@@ -162,6 +162,11 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
                    const float* scale, const float* shift, int relu, float* y_hi, float* y_lo,
                    tp_stream_t stream);
 
+/* 2 x the multiply-accumulates tp_conv_tf32x3 executes for this shape (per product term; the
+ * tensor pipe does 3x that).  Small images use position-major tiles that skip taps lying wholly in
+ * the zero padding, so this can be less than 2*N*H*W*Cout*taps*Cin.  For roofline accounting. */
+int64_t tp_conv_tf32x3_flops(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int taps);
+
 /* hi[i] = rn_tf32(x[i]), lo[i] = rn_tf32(x[i] - hi[i]); hi + lo == x up to 2^-23 relative. */
 int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t stream);
 

@@ -57,9 +57,12 @@ def main():
             run(*shp, images_for(*shp[:3]), iters=1)
         return
     print("variant promote  H  W  Cin Cout taps      N     ms  useful_TF/s  executed_TF/s")
-    for variant in (0, 1):
-        for promote in (1, 2, 4):
-            _lib.set_tuning("conv_variant", variant)
+    print("# (variant 2 = persistent kernel with position-major tiles disabled; FLOPs are the")
+    print("#  nominal 2*pixels*Cout*9*Cin, so skipped padding taps show up as > peak)")
+    for variant in (0, 2, 1):
+        for promote in ((2,) if variant == 2 else (1, 2, 4)):
+            _lib.set_tuning("conv_variant", 1 if variant == 1 else 0)
+            _lib.set_tuning("conv_pos_major", 1 if variant == 2 else 0)
             _lib.set_tuning("conv_promote", promote)
             tot_ms = tot_fl = 0.0
             for (H, W, Cin, Cout, taps) in LAYERS:

@@ -48,7 +48,9 @@ def test_tf32_split():
     (130, 1, 1, 512, 10, 1, False),    # logits: 10 outputs, unsplit result
     (2, 16, 16, 32, 64, 9, True),      # one k-block per tap
     (40, 32, 32, 64, 64, 9, True),     # 320 tiles: several tiles per persistent CTA
-    (150, 8, 8, 256, 512, 9, False),   # 75 x 4 tiles, ragged M
+    (150, 8, 8, 256, 512, 9, False),   # position-major tiles (N >= 128), ragged image block
+    (300, 4, 4, 512, 512, 9, True),    # position-major: corner / edge / interior tap subsets
+    (131, 2, 2, 64, 64, 9, True),      # position-major at 2x2: 4 of 9 taps per tile
 ])
 @pytest.mark.parametrize("variant", [0, 1], ids=["persistent", "tile-per-cta"])
 @pytest.mark.parametrize("promote", [1, 2, 8])

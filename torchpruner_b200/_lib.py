@@ -58,6 +58,7 @@ _SIGNATURES = {
     "tp_nan_any_dim1_static": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "tp_conv_tf32x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
                                       _vp, _vp, ctypes.c_int, _vp, _vp, _vp]),
+    "tp_conv_tf32x3_flops": (_i64, [_i64, _i64, _i64, _i64, _i64, ctypes.c_int]),
     "tp_tf32_split": (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
                                           _vp, _vp, _vp]),
@@ -370,7 +371,7 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
         y_lo = torch.empty_like(y_hi) if split else None
     else:
         y_hi, y_lo = out
-    flops = 2 * N * H * W * Cout * taps * Cin
+    flops = load().tp_conv_tf32x3_flops(N, H, W, Cin, Cout, int(taps)) if _profile is not None else 0
     nbytes = 4 * (2 * x_hi.numel() + 2 * w_hi.numel() + (2 if split else 1) * y_hi.numel())
     name = "conv_tf32x3"
     if _profile is not None and getattr(_profile, "by_shape", False):

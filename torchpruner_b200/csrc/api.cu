@@ -74,6 +74,12 @@ int tp_set_tuning(const char* key, int64_t value) {
   } else if (!strcmp(key, "reduce_ldg_waves")) {
     TP_REQUIRE(value >= 1 && value <= 64, TP_ERR_INVALID, "reduce_ldg_waves must be in [1,64]");
     t.reduce_ldg_waves = (int)value;
+  } else if (!strcmp(key, "conv_pos_major_max_hw")) {
+    TP_REQUIRE(value >= 1 && value <= 16384, TP_ERR_INVALID, "conv_pos_major_max_hw out of range");
+    t.conv_pos_major_max_hw = (int)value;
+  } else if (!strcmp(key, "conv_pos_major")) {
+    TP_REQUIRE(value == 0 || value == 1, TP_ERR_INVALID, "conv_pos_major must be 0 or 1");
+    t.conv_pos_major = (int)value;
   } else if (!strcmp(key, "conv_variant")) {
     TP_REQUIRE(value == 0 || value == 1, TP_ERR_INVALID, "conv_variant must be 0 or 1");
     t.conv_variant = (int)value;

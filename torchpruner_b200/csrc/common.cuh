@@ -53,6 +53,8 @@ struct Tuning {
   int reduce_ldg_waves = 4;      // grid cap of the direct-load kernel, in waves of 8 CTAs/SM
   int conv_promote = 2;          // k-blocks (of 32 inputs) per TMEM partial sum
   int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
+  int conv_pos_major = 0;        // 0 auto (position-major tiles for small images), 1 never
+  int conv_pos_major_max_hw = 64;  // largest H*W that gets position-major tiles
 };
 Tuning& tuning();
 

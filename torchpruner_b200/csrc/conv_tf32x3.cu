@@ -44,6 +44,7 @@ struct ConvGeom {
   int taps;      // 9: 3x3 stride 1 pad 1;  1: 1x1 / linear
   int bw, bh, bn;  // pixel box of an M tile, bw*bh*bn == 128, bw == W
   int tiles_h;   // M tiles per image (bn == 1) else 1
+  int tiles_w;   // tiles along W (1 unless position-major: bw == bh == 1, bn == 128)
   int num_kb;    // taps * Cin / 32
   int relu;
   int split;     // 1: y_hi/y_lo get the TF32 split of the result; 0: y_hi gets the raw fp32
@@ -408,6 +409,38 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void*
                "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
                : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* smem_src, int c0,
+                                             int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(map)),
+      "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// Tile -> pixel box origin.  Tiles of one image block are consecutive (all positions, then the
+// next image block) so the activations they share stay in L2.
+__device__ __forceinline__ void tile_origin(const ConvGeom& g, int mt, int& n0, int& h0, int& w0) {
+  const int per_block = g.tiles_h * g.tiles_w;
+  const int nb = mt / per_block;
+  const int rem = mt - nb * per_block;
+  const int ht = rem / g.tiles_w;
+  n0 = nb * g.bn;
+  h0 = ht * g.bh;
+  w0 = (rem - ht * g.tiles_w) * g.bw;
+}
+// A tap contributes to a tile only if its shifted pixel box meets the image: position-major
+// tiles (one output pixel x 128 images) skip every tap that falls in the zero padding.
+__device__ __forceinline__ bool tap_meets_image(const ConvGeom& g, int h0, int w0, int r, int s) {
+  const int hs = h0 + r - 1, ws = w0 + s - 1;
+  return hs + g.bh > 0 && hs < g.H && ws + g.bw > 0 && ws < g.W;
+}
+__device__ __forceinline__ int count_kblocks(const ConvGeom& g, int h0, int w0) {
+  if (g.taps != 9) return g.num_kb;
+  int n = 0;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) n += tap_meets_image(g, h0, w0, t / 3, t % 3) ? 1 : 0;
+  return n * (g.Cin / kBlockK);
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
@@ -465,7 +498,6 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int chunks_per_tile = (g.num_kb + g.promote - 1) / g.promote;
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
@@ -474,34 +506,27 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
-        int n0, h0;
-        if (g.bn == 1) {
-          n0 = mt / g.tiles_h;
-          h0 = (mt - n0 * g.tiles_h) * g.bh;
-        } else {
-          n0 = mt * g.bn;
-          h0 = 0;
-        }
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < g.num_kb; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1u);
-          mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-          uint8_t* st = smem + stage * Cfg::kStageBytes;
+        int n0, h0, w0;
+        tile_origin(g, mt, n0, h0, w0);
+        for (int tap = 0; tap < g.taps; ++tap) {
           const int r = (g.taps == 9) ? tap / 3 : 1;
           const int s = (g.taps == 9) ? tap - r * 3 : 1;
-          tma_load_4d(st, &tm_a_hi, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
-          tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, s - 1, h0 + r - 1, n0,
-                      &full[stage]);
-          tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
-          tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK, nt * BLOCK_N,
-                      &full[stage]);
-          if (++cb == kc) {
-            cb = 0;
-            ++tap;
-          }
-          if (++stage == Cfg::kStages) {
-            stage = 0;
-            phase ^= 1u;
+          if (g.taps == 9 && !tap_meets_image(g, h0, w0, r, s)) continue;
+          for (int cb = 0; cb < kc; ++cb) {
+            const int kb = tap * kc + cb;  // k-block of the weight matrix
+            mbar_wait(&empty[stage], phase ^ 1u);
+            mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+            uint8_t* st = smem + stage * Cfg::kStageBytes;
+            tma_load_4d(st, &tm_a_hi, cb * kBlockK, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
+            tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, w0 + s - 1, h0 + r - 1, n0,
+                        &full[stage]);
+            tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
+            tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK,
+                        nt * BLOCK_N, &full[stage]);
+            if (++stage == Cfg::kStages) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
         }
       }
@@ -516,8 +541,11 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       int buf = 0;
       uint32_t acc_phase = 0;  // flips every time buf wraps
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int n0, h0, w0;
+        tile_origin(g, tile / n_tiles, n0, h0, w0);
+        const int nk = count_kblocks(g, h0, w0);
         int in_chunk = 0;
-        for (int kb = 0; kb < g.num_kb; ++kb) {
+        for (int kb = 0; kb < nk; ++kb) {
           if (in_chunk == 0) {
             mbar_wait(&acc_empty[buf], acc_phase ^ 1u);
             tc_fence_after();
@@ -542,7 +570,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             stage = 0;
             phase ^= 1u;
           }
-          if (++in_chunk == g.promote || kb == g.num_kb - 1) {
+          if (++in_chunk == g.promote || kb == nk - 1) {
             umma_commit(&acc_full[buf]);
             in_chunk = 0;
             if (++buf == Cfg::kNumAcc) {
@@ -565,6 +593,10 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     uint32_t stores = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
+      int n0, h0, w0;
+      tile_origin(g, mt, n0, h0, w0);
+      const int nk = count_kblocks(g, h0, w0);
+      const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
       // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
       for (int j = et; j < BLOCK_N; j += 128) {
         const int col = nt * BLOCK_N + j;
@@ -574,7 +606,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       float acc[BLOCK_N];
 #pragma unroll
       for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
-      for (int chunk = 0; chunk < chunks_per_tile; ++chunk) {
+      for (int chunk = 0; chunk < chunks_this_tile; ++chunk) {
         mbar_wait(&acc_full[buf], acc_phase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
@@ -630,7 +662,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           fence_proxy_async();
           epi_barrier();
           if (issuer) {
-            tma_store_2d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, mt * kBlockM);
+            tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
             bulk_commit();
           }
           ++stores;
@@ -799,16 +831,19 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   if (rc != TP_OK) return rc;
   rc = make_map(&b_lo, w_lo, 2, bdims, bbox);
   if (rc != TP_OK) return rc;
-  const cuuint64_t ydims[2] = {(cuuint64_t)g.Cout, (cuuint64_t)g.m_total};
-  const cuuint32_t ybox[2] = {32, kBlockM};
-  rc = make_map(&o_hi, y_hi, 2, ydims, ybox);
+  const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.W, (cuuint64_t)g.H,
+                               (cuuint64_t)g.N};
+  const cuuint32_t ybox[4] = {32, (cuuint32_t)g.bw, (cuuint32_t)g.bh, (cuuint32_t)g.bn};
+  rc = make_map(&o_hi, y_hi, 4, ydims, ybox);
   if (rc != TP_OK) return rc;
-  rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 2, ydims, ybox);
+  rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 4, ydims, ybox);
   if (rc != TP_OK) return rc;
   auto kern = conv_tf32x3_persistent<BLOCK_N>;
   TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  const long long m_tiles = (g.m_total + kBlockM - 1) / kBlockM;
+  const long long img_blocks = (g.N + g.bn - 1) / g.bn;
+  const long long m_tiles = img_blocks * g.tiles_h * g.tiles_w;
   const int n_tiles = (g.Cout + BLOCK_N - 1) / BLOCK_N;
+  TP_REQUIRE(m_tiles * n_tiles < (1ll << 31), TP_ERR_LIMIT, "tp_conv_tf32x3: too many tiles");
   long long grid = m_tiles * n_tiles;
   if (grid > sm_count()) grid = sm_count();
   kern<<<(unsigned)grid, kConvThreads, Cfg::kSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, o_hi, o_lo, g,
@@ -865,6 +900,21 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
     g.bn = rows / (int)H;
     g.tiles_h = 1;
   }
+  g.tiles_w = 1;
+  // Position-major tiles for small images: one output pixel x 128 images per tile, so the taps
+  // that fall entirely in the zero padding are skipped (31 % of the MMAs at 4x4, 16 % at 8x8).
+  // The persistent kernel writes through TMA stores: row pitch must be a multiple of 16 bytes and
+  // the 32-column store box must not straddle the end of a row.
+  const bool persistent = (Cout > 16) && (Cout % 32 == 0) && tuning().conv_variant != 1 &&
+                          ((uintptr_t)y_hi % 16 == 0) && (!y_lo || (uintptr_t)y_lo % 16 == 0);
+  if (persistent && taps == 9 && tuning().conv_pos_major != 1 &&
+      H * W <= tuning().conv_pos_major_max_hw && H * W >= 4 && N >= 128) {
+    g.bw = 1;
+    g.bh = 1;
+    g.bn = 128;
+    g.tiles_h = (int)H;
+    g.tiles_w = (int)W;
+  }
   g.num_kb = taps * (int)(Cin / kBlockK);
   g.relu = relu;
   g.split = (y_lo != nullptr);
@@ -881,10 +931,6 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
   if (rc != TP_OK) return rc;
   if (Cout <= 16)
     return launch_conv<16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
-  // The persistent kernel writes through TMA stores: row pitch must be a multiple of 16 bytes and
-  // the 32-column store box must not straddle the end of a row.
-  const bool persistent = tuning().conv_variant != 1 && (Cout % 32 == 0) &&
-                          ((uintptr_t)y_hi % 16 == 0) && (!y_lo || (uintptr_t)y_lo % 16 == 0);
   if (persistent) {
     if (Cout <= 64)
       return launch_conv_persistent<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
@@ -893,6 +939,18 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
   if (Cout <= 64)
     return launch_conv<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
   return launch_conv<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+}
+
+int64_t tp_conv_tf32x3_flops(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int taps) {
+  // 2 * multiply-accumulates the kernel executes per fp32 product term (x3 on the tensor pipe):
+  // position-major tiles skip the taps that fall entirely in the zero padding.
+  if (N <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return 0;
+  const bool persistent = (Cout > 16) && (Cout % 32 == 0) && tp::tuning().conv_variant != 1;
+  const bool pos_major = persistent && taps == 9 && tp::tuning().conv_pos_major != 1 &&
+                         H * W <= tp::tuning().conv_pos_major_max_hw && H * W >= 4 && N >= 128;
+  if (!pos_major) return 2 * N * H * W * Cout * (int64_t)taps * Cin;
+  const int64_t vr = H >= 2 ? 3 * H - 2 : 1, vs = W >= 2 ? 3 * W - 2 : 1;  // valid (tap, pixel) pairs
+  return 2 * N * Cout * Cin * vr * vs;
 }
 
 int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t stream) {
