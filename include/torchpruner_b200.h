@@ -156,11 +156,13 @@ int tp_nan_any_dim1(const float* x, int64_t B, int64_t C, int64_t inner,
  * linear (taps == 1).  x_hi/x_lo: [N,H,W,Cin]; w_hi/w_lo: [Cout][taps*Cin] with k = tap*Cin + c,
  * tap = r*3 + s; scale/shift: [Cout] (BatchNorm and bias folded by the caller); y_hi/y_lo:
  * [N,H,W,Cout].  y_lo == NULL writes the unsplit fp32 result to y_hi (logits, or the input of a
- * pooling step).  Limits: Cin % 32 == 0; W divides 128 and H*W divides 128 or 128/W divides H. */
+ * pooling step).  act: 0 none, 1 ReLU, 2 LeakyReLU(leaky_slope).  Limits: Cin % 32 == 0 for
+ * taps == 9, Cin % 4 == 0 for taps == 1 (the K tail is zero-filled by the TMA unit); W divides
+ * 128 and H*W divides 128 or 128/W divides H. */
 int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
                    int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
-                   const float* scale, const float* shift, int relu, float* y_hi, float* y_lo,
-                   tp_stream_t stream);
+                   const float* scale, const float* shift, int act, float leaky_slope,
+                   float* y_hi, float* y_lo, tp_stream_t stream);
 
 /* 2 x the multiply-accumulates tp_conv_tf32x3 executes for this shape (per product term; the
  * tensor pipe does 3x that).  Small images use position-major tiles that skip taps lying wholly in
@@ -200,8 +202,8 @@ int tp_channel_contrib(const float* z, const float* wt, int64_t B, int64_t C, in
 int tp_contrib_sum(const float* T, int64_t C, int64_t M1, double* s_all, tp_stream_t stream);
 int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
                             double* base, const float* scale, const float* shift, int64_t pixels,
-                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int relu, float* out_hi,
-                            float* out_lo, tp_stream_t stream);
+                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int act,
+                            float leaky_slope, float* out_hi, float* out_lo, tp_stream_t stream);
 
 /* ---------------------------------------------------------------- no-allocation variant
  * No counterpart in the reference: this entry point exists for callers of THIS library that

@@ -22,9 +22,14 @@ def _ref64(x_nhwc, w, taps, scale, shift, relu):
     else:
         y = F.conv2d(x, w.double().view(Cout, Cin, 1, 1))
     y = y * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)
-    if relu:
-        y = y.relu()
+    y = _act(y, relu)
     return y.permute(0, 2, 3, 1).contiguous()
+
+
+def _act(y, spec):
+    if isinstance(spec, tuple):
+        return F.leaky_relu(y, spec[1])
+    return y.relu() if spec else y
 
 
 def test_tf32_split():
@@ -51,6 +56,8 @@ def test_tf32_split():
     (150, 8, 8, 256, 512, 9, False),   # position-major tiles (N >= 128), ragged image block
     (300, 4, 4, 512, 512, 9, True),    # position-major: corner / edge / interior tap subsets
     (131, 2, 2, 64, 64, 9, True),      # position-major at 2x2: 4 of 9 taps per tile
+    (200, 1, 1, 2024, 2024, 1, ("leaky", 0.01)),   # K tail (2024 = 63*32 + 8) + LeakyReLU
+    (70, 1, 1, 784, 2024, 1, ("leaky", 0.2)),
 ])
 @pytest.mark.parametrize("variant", [0, 1], ids=["persistent", "tile-per-cta"])
 @pytest.mark.parametrize("promote", [1, 2, 8])
@@ -91,9 +98,7 @@ def _conv_case(N, H, W, Cin, Cout, taps, relu, promote):
             y32 = F.conv2d(x32, w.view(Cout, Cin, 1, 1))
     finally:
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
-    y32 = y32 * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
-    if relu:
-        y32 = y32.relu()
+    y32 = _act(y32 * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1), relu)
     err32 = float((y32.permute(0, 2, 3, 1).double() - want).abs().max())
     print(f"K={taps * Cin} promote={promote} max abs err: 3xTF32 {err:.3e}  fp32 library {err32:.3e}  "
           f"(scale {scale_ref:.3f})")
@@ -243,3 +248,37 @@ def test_incremental_first_layer_kernels(B, C, H, W, C1, pool_first, mode, pool_
         assert float((got[p] - want).abs().max()) <= 1e-6 * max(float(want.abs().max()), 1e-3)
     # every channel removed: the running sum is back to (numerically) nothing
     assert float(base.abs().max()) <= 1e-12 * float(want_T.abs().max()) * C
+
+
+def test_native_tail_runs_the_reference_mlp():
+    """The 784-2024-2024-10 LeakyReLU perceptron of the reference's untrained-network notebook:
+    Linear layers whose K is not a multiple of 32, LeakyReLU epilogue, dense incremental first
+    layer — engine on vs engine off."""
+    import numpy as np
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    saved = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        torch.manual_seed(0)
+        model, shape = workloads.build("mlp")
+        model.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=24, batch_size=24, seed=6)
+        layer = model.fc[1]      # Linear(784, 2024): 2024 units to score
+        tables = {}
+        for native in ("auto", False):
+            np.random.seed(5)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                         reduction="none")
+            m.native_tail = native
+            tables[native] = m.run(layer, find_best_evaluation_module=True)
+            assert m.last_run_info["native_tail"] is bool(native), m.last_run_info
+            if native:
+                assert m.last_run_info["incremental_first"] is True
+                print("mlp", m.last_run_info["native"])
+        diff = np.abs(tables["auto"] - tables[False]).max()
+        print("mlp max |native - forward_partial| =", diff, "max |score| =", np.abs(tables[False]).max())
+        assert tables[False].shape == (24, 2024) and diff <= 2e-5
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = saved

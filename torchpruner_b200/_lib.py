@@ -57,7 +57,7 @@ _SIGNATURES = {
     "tp_nan_any_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "tp_nan_any_dim1_static": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "tp_conv_tf32x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
-                                      _vp, _vp, ctypes.c_int, _vp, _vp, _vp]),
+                                      _vp, _vp, ctypes.c_int, ctypes.c_float, _vp, _vp, _vp]),
     "tp_conv_tf32x3_flops": (_i64, [_i64, _i64, _i64, _i64, _i64, ctypes.c_int]),
     "tp_tf32_split": (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
@@ -67,7 +67,8 @@ _SIGNATURES = {
                                           _i64, _vp, _vp]),
     "tp_contrib_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
     "tp_prefix_contrib_stack": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64, _i64,
-                                               _i64, ctypes.c_int, ctypes.c_int, _vp, _vp, _vp]),
+                                               _i64, ctypes.c_int, ctypes.c_int, ctypes.c_float, _vp,
+                                               _vp, _vp]),
 }
 
 _lib = None
@@ -358,6 +359,13 @@ def tf32_split(x):
     return hi, lo
 
 
+def _act_code(act):
+    """(code, slope) of an activation spec: False/None, True/"relu", or ("leaky", slope)."""
+    if isinstance(act, tuple):
+        return 2, float(act[1])
+    return (1 if act else 0), 0.0
+
+
 def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, out=None):
     """y = act(conv(x, w) * scale + shift) on tcgen05 with 3xTF32 products.  x_*: NHWC
     [N,H,W,Cin]; w_*: [Cout, taps*Cin].  Returns (y_hi, y_lo) or (y, None) when split=False."""
@@ -379,7 +387,7 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
     with torch.cuda.device(x_hi.device), _launch(name, nbytes, x_hi, 1, flops):
         _check(load().tp_conv_tf32x3(
             x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
-            int(taps), Cout, scale.data_ptr(), shift.data_ptr(), int(bool(relu)), y_hi.data_ptr(),
+            int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu), y_hi.data_ptr(),
             y_lo.data_ptr() if y_lo is not None else 0, _stream(x_hi)), "tp_conv_tf32x3")
     return y_hi, y_lo
 
@@ -463,6 +471,6 @@ def prefix_contrib_stack(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp,
         _check(load().tp_prefix_contrib_stack(
             T.data_ptr(), perm.data_ptr(), int(k0), int(P), base.data_ptr(), scale.data_ptr(),
             shift.data_ptr(), int(pixels), int(C1), int(Hp), int(Wp), int(bool(pool)),
-            int(bool(relu)), out_hi.data_ptr() if out_hi is not None else 0,
+            *_act_code(relu), out_hi.data_ptr() if out_hi is not None else 0,
             out_lo.data_ptr() if out_lo is not None else 0, _stream(T)), "tp_prefix_contrib_stack")
     return m_out

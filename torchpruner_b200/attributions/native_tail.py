@@ -2,7 +2,8 @@
 
 The reference evaluates every Shapley mask by calling the user's ``forward_partial`` — an opaque
 callback (attributions.py:85).  When the layers it runs form a plain chain of
-Conv2d(3x3, stride 1, pad 1) / BatchNorm2d / ReLU / MaxPool2d(2) / Flatten / Dropout / Linear
+Conv2d(3x3, stride 1, pad 1) / BatchNorm2d / ReLU / LeakyReLU / MaxPool2d(2) / Flatten / Dropout /
+Linear
 modules in eval mode (every VGG-style tail does), the same arithmetic is executed here by
 ``tp_conv_tf32x3`` (tcgen05, 3xTF32, NHWC) instead of by cuDNN/cuBLAS kernels:
 
@@ -197,7 +198,8 @@ class NativeTail:
                 bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
             else:
                 raise _Unsupported(f"unsupported layer {type(m).__name__}")
-            if C % 32 or 128 % W or not ((128 // W) % H == 0 or H % (128 // W) == 0):
+            if (C % 32 if taps == 9 else C % 4) or 128 % W or \
+                    not ((128 // W) % H == 0 or H % (128 // W) == 0):
                 raise _Unsupported("channel / spatial size not tileable")
             scale = torch.ones(cout, device=dev)
             shift = bias.clone()
@@ -215,9 +217,12 @@ class NativeTail:
                     shift = shift + bn.bias.detach().double()
                 scale, shift = a.float(), shift.float()
                 i += 1
-            relu = False
+            relu = False   # activation spec: False, True (ReLU) or ("leaky", slope)
             if i < len(mods) and isinstance(mods[i], nn.ReLU):
                 relu = True
+                i += 1
+            elif i < len(mods) and isinstance(mods[i], nn.LeakyReLU):
+                relu = ("leaky", float(mods[i].negative_slope))
                 i += 1
             pool = False
             if i < len(mods) and _is_pool2(mods[i]) and taps == 9:

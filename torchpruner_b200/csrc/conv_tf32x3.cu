@@ -46,7 +46,8 @@ struct ConvGeom {
   int tiles_h;   // M tiles per image (bn == 1) else 1
   int tiles_w;   // tiles along W (1 unless position-major: bw == bh == 1, bn == 128)
   int num_kb;    // taps * Cin / 32
-  int relu;
+  int relu;      // activation: 0 none, 1 ReLU, 2 LeakyReLU(slope)
+  float slope;
   int split;     // 1: y_hi/y_lo get the TF32 split of the result; 0: y_hi gets the raw fp32
   int promote;   // k-blocks accumulated in TMEM before the partial sum is folded into registers
   long long m_total;
@@ -163,6 +164,12 @@ __device__ __forceinline__ float tf32_hi(float x) {
   return __uint_as_float(r);
 }
 __device__ __forceinline__ float tf32_lo(float x, float hi) { return tf32_hi(x - hi); }
+// 0: identity, 1: ReLU, 2: LeakyReLU (x > 0 ? x : x * slope, as ATen computes it)
+__device__ __forceinline__ float apply_act(float t, int act, float slope) {
+  if (act == 1) return fmaxf(t, 0.f);
+  if (act == 2) return t > 0.f ? t : t * slope;
+  return t;
+}
 
 // ---- the kernel ------------------------------------------------------------------------
 template <int BLOCK_N>
@@ -228,7 +235,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
-      const int kc = g.Cin / kBlockK;
+      const int kc = (g.Cin + kBlockK - 1) / kBlockK;
       int stage = 0;
       uint32_t phase = 0;
       int tap = 0, cb = 0;
@@ -338,7 +345,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
 #pragma unroll
       for (int j = 0; j < kChunk; ++j) {
         float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
-        if (g.relu) t = fmaxf(t, 0.f);
+        t = apply_act(t, g.relu, g.slope);
         y[j] = t;
       }
       if (live) {
@@ -439,7 +446,7 @@ __device__ __forceinline__ int count_kblocks(const ConvGeom& g, int h0, int w0) 
   int n = 0;
 #pragma unroll
   for (int t = 0; t < 9; ++t) n += tap_meets_image(g, h0, w0, t / 3, t % 3) ? 1 : 0;
-  return n * (g.Cin / kBlockK);
+  return n * ((g.Cin + kBlockK - 1) / kBlockK);
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
@@ -501,7 +508,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
-      const int kc = g.Cin / kBlockK;
+      const int kc = (g.Cin + kBlockK - 1) / kBlockK;
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -633,7 +640,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
-          if (g.relu) t = fmaxf(t, 0.f);
+          t = apply_act(t, g.relu, g.slope);
           y[j] = t;
         }
         for (int pass = 0; pass < passes; ++pass) {
@@ -866,13 +873,17 @@ extern "C" {
 
 int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
                    int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
-                   const float* scale, const float* shift, int relu, float* y_hi, float* y_lo,
-                   tp_stream_t stream) {
+                   const float* scale, const float* shift, int act, float leaky_slope,
+                   float* y_hi, float* y_lo, tp_stream_t stream) {
   using namespace tp;
   TP_REQUIRE(N >= 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, TP_ERR_INVALID,
              "tp_conv_tf32x3: bad dimension");
   TP_REQUIRE(taps == 1 || taps == 9, TP_ERR_INVALID, "tp_conv_tf32x3: taps must be 1 or 9");
-  TP_REQUIRE(Cin % kBlockK == 0, TP_ERR_LIMIT, "tp_conv_tf32x3: Cin must be a multiple of 32");
+  TP_REQUIRE(act >= 0 && act <= 2, TP_ERR_INVALID, "tp_conv_tf32x3: act must be 0, 1 or 2");
+  // A linear layer's last k-block may hang over the end of K: the TMA unit zero-fills both
+  // operands there.  A convolution's k index is tap*Cin + c, so its Cin must fill whole blocks.
+  TP_REQUIRE(taps == 1 ? (Cin % 4 == 0) : (Cin % kBlockK == 0), TP_ERR_LIMIT,
+             "tp_conv_tf32x3: Cin must be a multiple of 32 (conv) / 4 (linear)");
   TP_REQUIRE(W <= 128 && (128 % W) == 0, TP_ERR_LIMIT,
              "tp_conv_tf32x3: W must divide 128 (got %lld)", (long long)W);
   if (N == 0) return TP_OK;
@@ -915,8 +926,9 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
     g.tiles_h = (int)H;
     g.tiles_w = (int)W;
   }
-  g.num_kb = taps * (int)(Cin / kBlockK);
-  g.relu = relu;
+  g.num_kb = taps * (int)((Cin + kBlockK - 1) / kBlockK);
+  g.relu = act;
+  g.slope = leaky_slope;
   g.split = (y_lo != nullptr);
   g.promote = tuning().conv_promote;
   g.m_total = N * H * W;

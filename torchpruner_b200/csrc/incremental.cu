@@ -150,13 +150,16 @@ struct PrefixGeom {
   int C1;
   int pool;          // MaxPool2d(2) after the activation: output [B, Hp/2, Wp/2, C1]
   int Hp, Wp;        // spatial size of the layer's output (before that pool)
-  int relu;
+  int relu;          // activation: 0 none, 1 ReLU, 2 LeakyReLU(slope)
+  float slope;
   int emit;          // 0: accumulate only (advance the running sum), 1: write out_hi / out_lo
 };
 
-__device__ __forceinline__ float affine_act(double run, float a, float b, int relu) {
+__device__ __forceinline__ float affine_act(double run, float a, float b, int act, float slope) {
   float t = fmaf((float)run, a, b);
-  return relu ? fmaxf(t, 0.f) : t;
+  if (act == 1) return fmaxf(t, 0.f);
+  if (act == 2) return t > 0.f ? t : t * slope;
+  return t;
 }
 
 // One thread owns 4 consecutive output channels of one output position (after the optional pool)
@@ -215,10 +218,10 @@ prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restri
         run[s][2] -= (double)t.z;
         run[s][3] -= (double)t.w;
         if (g.emit) {
-          y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu));
-          y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu));
-          y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu));
-          y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu));
+          y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
+          y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
+          y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
+          y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
         }
       }
       if (g.emit) {
@@ -301,8 +304,8 @@ int tp_contrib_sum(const float* T, int64_t C, int64_t M1, double* s_all, tp_stre
 
 int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
                             double* base, const float* scale, const float* shift, int64_t pixels,
-                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int relu, float* out_hi,
-                            float* out_lo, tp_stream_t stream) {
+                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int act,
+                            float leaky_slope, float* out_hi, float* out_lo, tp_stream_t stream) {
   using namespace tp;
   TP_REQUIRE(P >= 0 && k0 >= 0 && pixels >= 0 && C1 > 0, TP_ERR_INVALID,
              "tp_prefix_contrib_stack: bad dimension");
@@ -320,7 +323,8 @@ int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int
   g.pool = pool;
   g.Hp = (int)Hp;
   g.Wp = (int)Wp;
-  g.relu = relu;
+  g.relu = act;
+  g.slope = leaky_slope;
   g.emit = out_hi != nullptr;
   const long long items = (pool ? pixels / 4 : pixels) * (C1 / 4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);

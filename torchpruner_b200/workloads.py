@@ -95,6 +95,31 @@ class SmallCNN(_PartialSequential):
         return [(fc1, [fc2]), (conv2, [fc1]), (conv1, [conv2])]
 
 
+class MLP(nn.Module):
+    """784-2024-2024-10 LeakyReLU perceptron of the reference's "Pruning Untrained Networks"
+    notebook (experiments/models/mnist.py:9-35), with its ``forward_partial`` protocol: children
+    of ``fc`` strictly after ``from_module`` up to and including ``to_module``."""
+
+    def __init__(self, in_features=784, width=2024, num_classes=10):
+        super().__init__()
+        self.fc = nn.Sequential(nn.Flatten(1), nn.Linear(in_features, width), nn.LeakyReLU(),
+                                nn.Linear(width, width), nn.LeakyReLU(), nn.Linear(width, num_classes))
+
+    def forward_partial(self, x, from_module=None, to_module=None):
+        active = from_module is None
+        for layer in self.fc.children():
+            if active:
+                x = layer(x)
+                if layer is to_module:
+                    return x
+            elif layer is from_module:
+                active = True
+        return x
+
+    def forward(self, x):
+        return self.forward_partial(x)
+
+
 def _bottleneck(c_in, width, stride):
     c_out = width * 4
     main = nn.Sequential(
@@ -181,6 +206,10 @@ def build(name, seed=1):
         return warm_batchnorm(VGG16Cifar(), (3, 32, 32)), (3, 32, 32)
     if name == "small_cnn":
         model = SmallCNN()
+        model.eval()
+        return model, (1, 28, 28)
+    if name == "mlp":
+        model = MLP()
         model.eval()
         return model, (1, 28, 28)
     if name == "resnet50":
