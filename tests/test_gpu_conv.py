@@ -56,6 +56,9 @@ def test_tf32_split():
     (150, 8, 8, 256, 512, 9, False),   # position-major tiles (N >= 128), ragged image block
     (300, 4, 4, 512, 512, 9, True),    # position-major: corner / edge / interior tap subsets
     (131, 2, 2, 64, 64, 9, True),      # position-major at 2x2: 4 of 9 taps per tile
+    (50, 8, 8, 96, 160, 9, True),      # Cout not a multiple of the 128-wide tile: clipped stores
+    (140, 4, 4, 96, 96, 9, True),      # same with position-major tiles
+    (33, 1, 1, 64, 96, 1, False),
     (200, 1, 1, 2024, 2024, 1, ("leaky", 0.01)),   # K tail (2024 = 63*32 + 8) + LeakyReLU
     (70, 1, 1, 784, 2024, 1, ("leaky", 0.2)),
 ])
