@@ -177,7 +177,8 @@ int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t s
 
 /* K5 for the engine above: z is NCHW [B,C,H,W]; out_hi/out_lo are NHWC [P*B, H', W', C] holding
  * the TF32 split of the (optionally 2x2 max-pooled, pool != 0) activation with channels c such
- * that inv_perm[c] <= k0+p zeroed in copy p.  Replaces shapley_values.py:53-56 like
+ * that inv_perm[c] <= k0+p zeroed in copy p (k0 = -1 makes copy 0 the unmasked activation).
+ * Replaces shapley_values.py:53-56 like
  * tp_prefix_mask_stack does, plus the layout change and a leading MaxPool2d(2). */
 int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
                        int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,

@@ -166,6 +166,15 @@ def test_native_tail_agrees_with_forward_partial(tag):
             assert m.last_run_info["incremental_first"] is bool(native and incremental), m.last_run_info
             if native:
                 print(tag, "incremental" if incremental else "direct", m.last_run_info["native"])
+        # second run on the unchanged model: the cached, verified plan also supplies the unmasked
+        # loss (no library forward of the tail at all) — same table up to 1 ulp of a loss
+        np.random.seed(3)
+        m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                     reduction="none")
+        m.max_stack = 48
+        again = m.run(layer, find_best_evaluation_module=True)
+        assert m.last_run_info["native"].get("cached") is True
+        assert np.abs(again - tables[("auto", True)]).max() <= 5e-7
         ref = tables[(False, False)]
         for key in (("auto", True), ("auto", False)):
             diff = np.abs(tables[key] - ref).max()

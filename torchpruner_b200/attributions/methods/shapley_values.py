@@ -163,8 +163,6 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         with torch.no_grad():
             for x, y in self._batches():
                 original_z, _ = self.run_forward_partial(x, to_module=module)
-                logits0, original_loss = self.run_forward_partial(original_z, y_true=y,
-                                                                  from_module=module)
                 z = original_z.detach().float().contiguous()
                 B, n = z.shape[0], z.shape[1]
                 if perm_dev is None:
@@ -181,37 +179,52 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 if sv is None:
                     sv = torch.zeros((d, n), dtype=torch.float64, device=z.device)
 
+                # --- how the layers after `module` are executed for this batch
+                use_engine = bool(self.native_tail and stack_safe and spans)
+                found, native = False, None
+                if use_engine:
+                    found, native, info = cached_plan(self.model, module, z)
+                    if found:
+                        native_info = dict(info, cached=True)
+
+                def engine_buffers():
+                    native.prepare_batch(z, allow_incremental=self.incremental_first)
+                    per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
+                    p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
+                    hi = torch.empty(native.stack_elems(B, max(p_max, min(2, n))),
+                                     dtype=torch.float32, device=z.device)
+                    return p_max, hi, torch.empty_like(hi)
+
+                if native is not None:
+                    # A plan verified against forward_partial for this very model state: the
+                    # unmasked loss comes from it too, so the whole ladder is self-consistent and
+                    # the library forward of the tail is not needed at all.
+                    P_max, buf_hi, buf_lo = engine_buffers()
+                    logits0 = native.unmasked_logits(z, inv_dev[0], buf_hi, buf_lo)
+                    original_loss = self.criterion(logits0, y, reduction="none")
+                else:
+                    logits0, original_loss = self.run_forward_partial(original_z, y_true=y,
+                                                                      from_module=module)
+                    if use_engine and not found:
+                        native = NativeTail.build(self.model, module, z)
+                        if native is not None:
+                            P_max, buf_hi, buf_lo = engine_buffers()
+                            j0, k0v, _ = spans[0]
+                            ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0],
+                                                     k0v, min(2, n), buf_hi, buf_lo)
+                            native_info = {"verified": ok, "verify_rel_err": verr}
+                            if not ok:
+                                native.release()
+                                native = None
+                                del buf_hi, buf_lo
+                        remember_plan(self.model, module, z, native,
+                                      native_info or {"verified": False})
+
                 loss0 = self._per_example(original_loss, B)
                 fused_ce = self._fused_ce_ok(logits0, y, loss0)
                 prev_a = torch.empty(B, dtype=torch.float32, device=z.device)
                 prev_b = torch.empty_like(prev_a)
                 y_stack = None
-
-                # --- how the layers after `module` are executed for this batch
-                native = None
-                if self.native_tail and stack_safe and spans:
-                    found, native, info = cached_plan(self.model, module, z)
-                    if found:
-                        native_info = dict(info, cached=True)
-                    else:
-                        native = NativeTail.build(self.model, module, z)
-                if native is not None:
-                    native.prepare_batch(z, allow_incremental=self.incremental_first)
-                    per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
-                    P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
-                    buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
-                                         dtype=torch.float32, device=z.device)
-                    buf_lo = torch.empty_like(buf_hi)
-                    if not found:
-                        j0, k0v, _ = spans[0]
-                        ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0], k0v,
-                                                 min(2, n), buf_hi, buf_lo)
-                        native_info = {"verified": ok, "verify_rel_err": verr}
-                        if not ok:
-                            native = None
-                            del buf_hi, buf_lo
-                if self.native_tail and stack_safe and spans and not found:
-                    remember_plan(self.model, module, z, native, native_info or {"verified": False})
                 if native is None:
                     bytes_per_copy = max(1, z.numel() * 4)
                     P_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // bytes_per_copy)))

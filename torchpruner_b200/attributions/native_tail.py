@@ -385,6 +385,16 @@ class NativeTail:
             x_hi, x_lo = y_hi, y_lo
         return x_hi.view(x_hi.shape[0], self.n_out)
 
+    def unmasked_logits(self, z, inv_perm, buf_hi, buf_lo):
+        """[B, n_out] logits with no channel removed (prefix index -1), through the direct form
+        of the first layer."""
+        saved = self.incremental
+        self.incremental = False
+        try:
+            return self.logits(z, inv_perm, -1, 1, buf_hi, buf_lo).clone()
+        finally:
+            self.incremental = saved
+
     def verify(self, model, module, z, perm, inv_perm, k0, P, buf_hi, buf_lo):
         """True iff the plan reproduces ``forward_partial`` on P real masks of this run (both the
         incremental and the direct form of the first layer are checked)."""

@@ -977,7 +977,7 @@ int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t s
 int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
                        int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
                        tp_stream_t stream) {
-  TP_REQUIRE(P >= 0 && B >= 0 && C >= 0 && H >= 0 && W >= 0 && k0 >= 0, TP_ERR_INVALID,
+  TP_REQUIRE(P >= 0 && B >= 0 && C >= 0 && H >= 0 && W >= 0 && k0 >= -1, TP_ERR_INVALID,
              "tp_mask_stack_nhwc: negative dimension");
   TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
              "tp_mask_stack_nhwc: pooling needs even H and W");
