@@ -8,10 +8,11 @@ Workload (config 3 of BASELINE.json, the one the headline metric is quoted on): 
 CIFAR-10 shaped inputs, one batch of 256 synthetic examples, layer-wise Monte-Carlo Shapley
 scoring of all 13 conv layers (evaluated after BN+ReLU, find_best_evaluation_module=True).
 
-One STEP = every GPU evaluates one full permutation (C prefix masks) for each of the 13 layers
-= 4224 channel-evals per GPU, through the product's own sharding path (sv_samples = N
-permutations split over N ranks) including the all-reduce of each layer's score table.  25 such
-steps are the sv_samples=25 job of the config on one GPU.  Scaling is therefore weak.
+One STEP = every GPU evaluates 5 full permutations (the reference's default sv_samples; C prefix
+masks each) for each of the 13 layers = 21120 channel-evals per GPU, through the product's own
+sharding path (sv_samples = 5*N permutations split over N ranks) including the all-reduce of
+each layer's score table.  5 such steps are the sv_samples=25 job of the config on one GPU.
+Scaling is therefore weak.
 
 Printed keys follow the driver's contract; see DESIGN.md "Measurement" for the definitions of
 `roofline`, `cpu_baseline`, `e2e` and `reductions`.
@@ -36,6 +37,7 @@ sys.path.insert(0, ROOT)
 from torchpruner_b200 import workloads  # noqa: E402
 
 BATCH = 256
+PERMS_PER_STEP = 5   # permutations per GPU per layer per step (the reference's default sv_samples)
 METRIC = "shapley_channel_evals_per_s"
 UNIT = "channel-evals/s"
 
@@ -65,11 +67,11 @@ def tensor_peak():
 def workload_description(n_gpus):
     return {
         "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
-                    "BN+ReLU, one permutation per GPU per step = 4224 channel-evals/GPU/step "
-                    "(25 steps = the sv_samples=25 job); layers after the scored module run fp32-accurate "
+                    "BN+ReLU, 5 permutations (the reference's default sv_samples) per GPU per step "
+                    "= 21120 channel-evals/GPU/step (5 steps = the sv_samples=25 job); layers after the scored module run fp32-accurate "
                     "(tcgen05 3xTF32 engine, verified against forward_partial; cuDNN/cuBLAS TF32 off)",
-        "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224,
-        "sv_samples_per_step": n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
+        "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224 * PERMS_PER_STEP,
+        "sv_samples_per_step": PERMS_PER_STEP * n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
         "l2": "working set per step (stacked masked activations, up to 512 MiB per chunk) far "
               "exceeds the 126 MB L2; reduction kernels are timed with an L2 flush between "
               "iterations",
@@ -265,11 +267,11 @@ def run_product(args, rank, world, local_rank):
     convs = model.conv_layers()
     hx, hy = host_batch(shape, pin=True)
     dx, dy = hx.to(device), hy.to(device)
-    evals_per_rank_step = sum(c.out_channels for c in convs)
+    evals_per_rank_step = PERMS_PER_STEP * sum(c.out_channels for c in convs)
 
     def make_metric(loader):
         m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, device,
-                                     sv_samples=world, reduction="none")
+                                     sv_samples=PERMS_PER_STEP * world, reduction="none")
         m.shard = world > 1
         return m
 
@@ -278,7 +280,7 @@ def run_product(args, rank, world, local_rank):
         m = make_metric(OneBatch(dx, dy))
         for conv in convs:
             module = m.find_evaluation_module(conv, find_best_evaluation_module=True)
-            m._scores_on_device(module, world)
+            m._scores_on_device(module, PERMS_PER_STEP * world)
 
     def e2e_step(step):
         np.random.seed(1000 + step)
