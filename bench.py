@@ -339,18 +339,24 @@ def run_product(args, rank, world, local_rank):
         own_ms = {k: v["ms"] for k, v in kernel_summary.items()}
         dominant = max(own_ms, key=own_ms.get)
         dom = kernel_summary[dominant]
-        if dominant == "conv_tf32x3":
-            # fp32-accurate layers on tcgen05: every fp32 product is three TF32 MMAs, so the
-            # tensor pipe executes 3x the layer's nominal FLOPs; TF32 runs at half the bf16 rate.
+        if dominant in ("conv_tf32x3", "conv_f16x3"):
+            # fp32-accurate layers on tcgen05: every fp32 product is three tensor-core MMAs on an
+            # 11-bit split of the operands (hi*hi + hi*lo + lo*hi), so the tensor pipe executes 3x
+            # the layer's FLOPs.  fp16 operands run at the bf16/fp16 rate, TF32 ones at half of it.
             bf16 = tensor_peak()
+            half = dominant == "conv_f16x3"
+            peak = bf16[0] if half else bf16[0] / 2.0
             executed = 3.0 * dom["flops"] / dom["ms"] / 1e9 if dom["ms"] > 0 else 0.0
             roofline = {
-                "kernel": dominant, "bound": "tensor", "achieved": executed, "peak": bf16[0] / 2.0,
-                "unit": "TFLOP/s", "frac": executed / (bf16[0] / 2.0), "traffic": None,
-                "peak_source": bf16[1] + " bf16 sustained / 2 (TF32 dense runs at half the bf16 rate)",
+                "kernel": dominant, "bound": "tensor", "achieved": executed, "peak": peak,
+                "unit": "TFLOP/s", "frac": executed / peak, "traffic": None,
+                "peak_source": bf16[1] + (" bf16 sustained (fp16 and bf16 MMAs run at the same rate)"
+                                         if half else
+                                         " bf16 sustained / 2 (TF32 dense runs at half the bf16 rate)"),
                 "useful_tflops": executed / 3.0,
-                "achieved_definition": "3 TF32 MMAs per fp32 product (hi*hi + hi*lo + lo*hi) x "
-                                       "2*MACs of the layer, summed over launches / summed duration",
+                "achieved_definition": "3 MMAs per fp32 product (hi*hi + hi*lo + lo*hi on an 11-bit "
+                                       "split) x 2*MACs executed by the layer, summed over launches / "
+                                       "summed duration",
                 "launches": dom["launches"], "avg_launch_ms": dom["ms"] / max(1, dom["launches"]),
                 "share_of_step": dom["ms"] / total_ms,
             }

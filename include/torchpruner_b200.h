@@ -188,6 +188,30 @@ int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int6
 int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
                            float* lo, tp_stream_t stream);
 
+/* fp16 flavour of the engine ("fp16x3").  A TF32 number and an fp16 number both carry 11
+ * significant bits, so with a per-tensor power-of-two scale that centres the values in fp16's
+ * exponent range the same split (hi = rn_fp16(x*s), lo = rn_fp16(x*s - hi)) and the same three
+ * products give the same 2^-22 accuracy — on tcgen05.mma.kind::f16, which runs at twice the TF32
+ * rate, from operands that take half the bytes.  x_*, w_* are fp16; `scale` must already contain
+ * 1/(s_x*s_w); split outputs (y_lo != NULL) are fp16 pairs of y*out_scale, unsplit output is
+ * fp32.  Limits: Cin % 64 == 0 (conv) / % 8 (linear); split outputs need Cout % 64 == 0.
+ * The host engine falls back to the TF32 flavour when a tensor leaves fp16's range. */
+int tp_conv_f16x3(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W, int64_t Cin,
+                  const void* w_hi, const void* w_lo, int taps, int64_t Cout, const float* scale,
+                  const float* shift, int act, float leaky_slope, float out_scale, void* y_hi,
+                  void* y_lo, tp_stream_t stream);
+int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_stream_t stream);
+int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
+                           int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
+                           void* out_hi, void* out_lo, tp_stream_t stream);
+int tp_maxpool2_split_nhwc_f16(const float* x, int64_t N, int64_t H, int64_t W, int64_t C,
+                               float scale, void* hi, void* lo, tp_stream_t stream);
+int tp_prefix_contrib_stack_f16(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                                double* base, const float* scale, const float* shift,
+                                int64_t pixels, int64_t C1, int64_t Hp, int64_t Wp, int pool,
+                                int act, float leaky_slope, float out_scale, void* out_hi,
+                                void* out_lo, tp_stream_t stream);
+
 /* ---------------------------------------------------------------- incremental first layer
  * Along one permutation the Shapley masks are nested and the first layer after the evaluation
  * module is linear in the activation, so its pre-activation under mask k is

@@ -294,3 +294,44 @@ def test_native_tail_runs_the_reference_mlp():
         assert tables[False].shape == (24, 2024) and diff <= 2e-5
     finally:
         torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout,taps,relu", [
+    (4, 32, 32, 64, 64, 9, True),
+    (3, 16, 16, 128, 256, 9, True),
+    (150, 8, 8, 256, 512, 9, False),   # position-major tiles
+    (300, 4, 4, 512, 512, 9, True),
+    (300, 1, 1, 2048, 2048, 1, True),  # dense form of a conv on 2x2 images
+    (130, 1, 1, 512, 10, 1, False),    # logits: fp32 unsplit output
+    (70, 1, 1, 520, 128, 1, ("leaky", 0.1)),   # K tail: 520 = 8*64 + 8
+])
+def test_conv_f16x3_matches_float64(N, H, W, Cin, Cout, taps, relu):
+    """fp16x3 flavour: same 11-bit split on fp16 operands with per-tensor power-of-two scales."""
+    gen = torch.Generator(device=DEV).manual_seed(N * 1000 + Cin + 1)
+    x = torch.randn((N, H, W, Cin), device=DEV, generator=gen) * 3.0
+    x = x * (torch.rand((N, H, W, Cin), device=DEV, generator=gen) > 0.3)
+    w = torch.randn((Cout, taps * Cin), device=DEV, generator=gen) / (taps * Cin) ** 0.5
+    scale = torch.rand(Cout, device=DEV, generator=gen) + 0.5
+    shift = torch.randn(Cout, device=DEV, generator=gen) * 0.1
+    s_x = 2.0 ** round(np.log2(64.0 / float(x.abs().max())))
+    s_w = 2.0 ** round(np.log2(64.0 / float(w.abs().max())))
+    x_hi, x_lo = _lib.f16_split(x, s_x)
+    w_hi, w_lo = _lib.f16_split(w, s_w)
+    assert x_hi.dtype == torch.float16
+    rel = ((x_hi.double() + x_lo.double()) / s_x - x.double()).abs().max() / x.abs().max()
+    assert float(rel) <= 2.0 ** -21
+    split = Cout != 10
+    out_scale = 8.0
+    y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, (scale / (s_x * s_w)).contiguous(),
+                                  shift, relu, split=split, out_scale=out_scale)
+    if split:
+        assert y_hi.dtype == torch.float16
+        y = (y_hi.double() + y_lo.double()) / out_scale
+    else:
+        assert y_hi.dtype == torch.float32
+        y = y_hi.double()
+    want = _ref64(x, w, taps, scale, shift, relu)
+    scale_ref = float(want.abs().max())
+    err = float((y - want).abs().max())
+    print(f"fp16x3 K={taps * Cin} max abs err {err:.3e} (scale {scale_ref:.3f})")
+    assert err <= 1e-6 * scale_ref, (err, scale_ref)

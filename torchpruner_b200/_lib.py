@@ -63,6 +63,17 @@ _SIGNATURES = {
     "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
                                           _vp, _vp, _vp]),
     "tp_maxpool2_split_nhwc": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "tp_conv_f16x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
+                                     _vp, _vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, _vp, _vp,
+                                     _vp]),
+    "tp_f16_split": (ctypes.c_int, [_vp, _i64, ctypes.c_float, _vp, _vp, _vp]),
+    "tp_mask_stack_nhwc_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
+                                              ctypes.c_int, ctypes.c_float, _vp, _vp, _vp]),
+    "tp_maxpool2_split_nhwc_f16": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, ctypes.c_float, _vp,
+                                                  _vp, _vp]),
+    "tp_prefix_contrib_stack_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64,
+                                                   _i64, _i64, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.c_float, ctypes.c_float, _vp, _vp, _vp]),
     "tp_channel_contrib": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, ctypes.c_int, ctypes.c_int,
                                           _i64, _vp, _vp]),
     "tp_contrib_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
@@ -185,6 +196,12 @@ def _cuda_f32(t, name):
     if t.device.index not in _checked_devices:
         _check(load().tp_device_check(t.device.index), "tp_device_check")
         _checked_devices.add(t.device.index)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _cuda_half(t, name):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float16:
+        raise TorchPrunerB200Error(f"{name} must be a CUDA float16 tensor")
     return t if t.is_contiguous() else t.contiguous()
 
 
@@ -366,33 +383,62 @@ def _act_code(act):
     return (1 if act else 0), 0.0
 
 
-def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, out=None):
+def f16_split(x, scale):
+    """fp16 pair (hi, lo) of x * scale: hi = rn_fp16(x*scale), lo = rn_fp16(x*scale - hi)."""
+    x = _cuda_f32(x, "x")
+    hi = torch.empty(x.shape, dtype=torch.float16, device=x.device)
+    lo = torch.empty_like(hi)
+    with torch.cuda.device(x.device), _launch("f16_split", 8 * x.numel(), x):
+        _check(load().tp_f16_split(x.data_ptr(), x.numel(), float(scale), hi.data_ptr(),
+                                   lo.data_ptr(), _stream(x)), "tp_f16_split")
+    return hi, lo
+
+
+def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, out=None,
+                out_scale=1.0):
     """y = act(conv(x, w) * scale + shift) on tcgen05 with 3xTF32 products.  x_*: NHWC
     [N,H,W,Cin]; w_*: [Cout, taps*Cin].  Returns (y_hi, y_lo) or (y, None) when split=False."""
-    x_hi, x_lo = _cuda_f32(x_hi, "x_hi"), _cuda_f32(x_lo, "x_lo")
+    half = x_hi.dtype == torch.float16   # fp16x3 flavour: operands are fp16 pairs
+    if half:
+        x_hi, x_lo = _cuda_half(x_hi, "x_hi"), _cuda_half(x_lo, "x_lo")
+        if w_hi.dtype != torch.float16 or w_lo.dtype != torch.float16:
+            raise TorchPrunerB200Error("conv: fp16 activations need fp16 weights")
+    else:
+        x_hi, x_lo = _cuda_f32(x_hi, "x_hi"), _cuda_f32(x_lo, "x_lo")
     N, H, W, Cin = x_hi.shape
     Cout = w_hi.shape[0]
     if w_hi.shape[1] != taps * Cin or w_lo.shape != w_hi.shape or x_lo.shape != x_hi.shape:
         raise TorchPrunerB200Error("conv_tf32x3: operand shapes do not match")
     if out is None:
-        y_hi = torch.empty((N, H, W, Cout), dtype=torch.float32, device=x_hi.device)
+        odt = torch.float16 if (half and split) else torch.float32
+        y_hi = torch.empty((N, H, W, Cout), dtype=odt, device=x_hi.device)
         y_lo = torch.empty_like(y_hi) if split else None
     else:
         y_hi, y_lo = out
     flops = load().tp_conv_tf32x3_flops(N, H, W, Cin, Cout, int(taps)) if _profile is not None else 0
-    nbytes = 4 * (2 * x_hi.numel() + 2 * w_hi.numel() + (2 if split else 1) * y_hi.numel())
-    name = "conv_tf32x3"
+    esz = 2 if half else 4
+    nbytes = esz * (2 * x_hi.numel() + 2 * w_hi.numel()) + \
+        y_hi.element_size() * (2 if split else 1) * y_hi.numel()
+    name = "conv_f16x3" if half else "conv_tf32x3"
     if _profile is not None and getattr(_profile, "by_shape", False):
-        name = f"conv_tf32x3[{H}x{W} {Cin}->{Cout} t{taps}]"
+        name = f"{name}[{H}x{W} {Cin}->{Cout} t{taps}]"
     with torch.cuda.device(x_hi.device), _launch(name, nbytes, x_hi, 1, flops):
-        _check(load().tp_conv_tf32x3(
-            x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
-            int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu), y_hi.data_ptr(),
-            y_lo.data_ptr() if y_lo is not None else 0, _stream(x_hi)), "tp_conv_tf32x3")
+        if half:
+            _check(load().tp_conv_f16x3(
+                x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
+                int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu),
+                float(out_scale), y_hi.data_ptr(), y_lo.data_ptr() if y_lo is not None else 0,
+                _stream(x_hi)), "tp_conv_f16x3")
+        else:
+            _check(load().tp_conv_tf32x3(
+                x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
+                int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu),
+                y_hi.data_ptr(), y_lo.data_ptr() if y_lo is not None else 0, _stream(x_hi)),
+                "tp_conv_tf32x3")
     return y_hi, y_lo
 
 
-def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo):
+def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo, scale=1.0):
     """NHWC TF32-split stack of P prefix-masked copies of the NCHW activation z (optionally
     2x2 max-pooled first).  out_*: preallocated, at least P*B*H'*W'*C floats."""
     z = _cuda_f32(z, "z")
@@ -403,22 +449,36 @@ def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo):
     need = P * B * Ho * Wo * C
     if out_hi.numel() < need or out_lo.numel() < need:
         raise TorchPrunerB200Error("mask_stack_nhwc: output buffers too small")
-    with torch.cuda.device(z.device), _launch("mask_stack_nhwc", 4 * z.numel() + 8 * need, z):
-        _check(load().tp_mask_stack_nhwc(z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H,
-                                         W, int(bool(pool)), out_hi.data_ptr(), out_lo.data_ptr(),
-                                         _stream(z)), "tp_mask_stack_nhwc")
+    esz = out_hi.element_size()
+    with torch.cuda.device(z.device), _launch("mask_stack_nhwc", 4 * z.numel() + 2 * esz * need, z):
+        if out_hi.dtype == torch.float16:
+            _check(load().tp_mask_stack_nhwc_f16(
+                z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H, W, int(bool(pool)),
+                float(scale), out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)),
+                "tp_mask_stack_nhwc_f16")
+        else:
+            _check(load().tp_mask_stack_nhwc(
+                z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H, W, int(bool(pool)),
+                out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)), "tp_mask_stack_nhwc")
     shape = (P * B, Ho, Wo, C)
     return out_hi[:need].view(shape), out_lo[:need].view(shape)
 
 
-def maxpool2_split_nhwc(x):
+def maxpool2_split_nhwc(x, half=False, scale=1.0):
     x = _cuda_f32(x, "x")
     N, H, W, C = x.shape
-    hi = torch.empty((N, H // 2, W // 2, C), dtype=torch.float32, device=x.device)
+    hi = torch.empty((N, H // 2, W // 2, C), dtype=torch.float16 if half else torch.float32,
+                     device=x.device)
     lo = torch.empty_like(hi)
-    with torch.cuda.device(x.device), _launch("maxpool2_split_nhwc", 4 * x.numel() + 8 * hi.numel(), x):
-        _check(load().tp_maxpool2_split_nhwc(x.data_ptr(), N, H, W, C, hi.data_ptr(), lo.data_ptr(),
-                                             _stream(x)), "tp_maxpool2_split_nhwc")
+    nbytes = 4 * x.numel() + 2 * hi.element_size() * hi.numel()
+    with torch.cuda.device(x.device), _launch("maxpool2_split_nhwc", nbytes, x):
+        if half:
+            _check(load().tp_maxpool2_split_nhwc_f16(x.data_ptr(), N, H, W, C, float(scale),
+                                                     hi.data_ptr(), lo.data_ptr(), _stream(x)),
+                   "tp_maxpool2_split_nhwc_f16")
+        else:
+            _check(load().tp_maxpool2_split_nhwc(x.data_ptr(), N, H, W, C, hi.data_ptr(),
+                                                 lo.data_ptr(), _stream(x)), "tp_maxpool2_split_nhwc")
     return hi, lo
 
 
@@ -462,15 +522,24 @@ def contrib_sum(T, C, M1, s_all):
 
 
 def prefix_contrib_stack(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp, pool, relu,
-                         out_hi=None, out_lo=None):
+                         out_hi=None, out_lo=None, out_scale=1.0):
     m_out = (pixels // 4 if pool else pixels) * C1
     if out_hi is not None and (out_hi.numel() < P * m_out or out_lo.numel() < P * m_out):
         raise TorchPrunerB200Error("prefix_contrib_stack: output buffers too small")
-    nbytes = 4 * P * pixels * C1 + (8 * P * m_out if out_hi is not None else 0)
+    half = out_hi is not None and out_hi.dtype == torch.float16
+    nbytes = 4 * P * pixels * C1 + ((4 if half else 8) * P * m_out if out_hi is not None else 0)
     with torch.cuda.device(T.device), _launch("prefix_contrib_stack", nbytes, T):
-        _check(load().tp_prefix_contrib_stack(
-            T.data_ptr(), perm.data_ptr(), int(k0), int(P), base.data_ptr(), scale.data_ptr(),
-            shift.data_ptr(), int(pixels), int(C1), int(Hp), int(Wp), int(bool(pool)),
-            *_act_code(relu), out_hi.data_ptr() if out_hi is not None else 0,
-            out_lo.data_ptr() if out_lo is not None else 0, _stream(T)), "tp_prefix_contrib_stack")
+        if half:
+            _check(load().tp_prefix_contrib_stack_f16(
+                T.data_ptr(), perm.data_ptr(), int(k0), int(P), base.data_ptr(), scale.data_ptr(),
+                shift.data_ptr(), int(pixels), int(C1), int(Hp), int(Wp), int(bool(pool)),
+                *_act_code(relu), float(out_scale), out_hi.data_ptr(), out_lo.data_ptr(),
+                _stream(T)), "tp_prefix_contrib_stack_f16")
+        else:
+            _check(load().tp_prefix_contrib_stack(
+                T.data_ptr(), perm.data_ptr(), int(k0), int(P), base.data_ptr(), scale.data_ptr(),
+                shift.data_ptr(), int(pixels), int(C1), int(Hp), int(Wp), int(bool(pool)),
+                *_act_code(relu), out_hi.data_ptr() if out_hi is not None else 0,
+                out_lo.data_ptr() if out_lo is not None else 0, _stream(T)),
+                "tp_prefix_contrib_stack")
     return m_out

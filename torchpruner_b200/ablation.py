@@ -60,14 +60,21 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
         ranking_dev = torch.from_numpy(ranking).to(z.device)
         if native is not None:
             native.prepare_batch(z, allow_incremental=incremental_first)
-            per_copy = 8 * native.stack_elems(B, 1)
+            per_copy = (4 if native.use_f16 else 8) * native.stack_elems(B, 1)
             P_max = int(max(1, min(max_stack, n, max_stack_bytes // per_copy)))
-            buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))), dtype=torch.float32,
-                                 device=z.device)
+            buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
+                                 dtype=native.stack_dtype, device=z.device)
             buf_lo = torch.empty_like(buf_hi)
             if not found:
                 ok, err = native.verify(model, module_nl, z, ranking_dev, inv_dev, 0, min(2, n),
                                         buf_hi, buf_lo)
+                if not ok and native.use_f16:
+                    native.use_f16 = False
+                    buf_hi = torch.empty(native.stack_elems(B, max(P_max, min(2, n))),
+                                         dtype=torch.float32, device=z.device)
+                    buf_lo = torch.empty_like(buf_hi)
+                    ok, err = native.verify(model, module_nl, z, ranking_dev, inv_dev, 0, min(2, n),
+                                            buf_hi, buf_lo)
                 info = {"verified": ok, "verify_rel_err": err}
                 if not ok:
                     native = None

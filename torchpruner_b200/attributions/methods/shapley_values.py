@@ -149,6 +149,19 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
 
     def _scores_on_device(self, module, sv_samples):
         """The [d, C] float64 score table, left on the GPU (all-reduced when sharded)."""
+        rng_state = np.random.get_state()
+        sv = self._scores_once(module, sv_samples)
+        info = self.last_run_info
+        if sv is not None and info.get("f16") and not bool(torch.isfinite(sv).all()):
+            # An activation left fp16's exponent range under some mask (the per-tensor scales are
+            # calibrated on the unmasked batch, with 2^10 of headroom).  Redo the run on the TF32
+            # flavour, with the numpy RNG rewound so the same permutations are drawn.
+            self._f16_banned = True
+            np.random.set_state(rng_state)
+            sv = self._scores_once(module, sv_samples)
+        return sv
+
+    def _scores_once(self, module, sv_samples):
         d = len(self.data_gen.dataset)
         group, world, rank = self._dist()
         sv = None
@@ -186,13 +199,17 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                     found, native, info = cached_plan(self.model, module, z)
                     if found:
                         native_info = dict(info, cached=True)
+                    if native is not None and getattr(self, "_f16_banned", False):
+                        native.use_f16 = False
 
                 def engine_buffers():
                     native.prepare_batch(z, allow_incremental=self.incremental_first)
                     per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
                     p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
+                    per_copy = per_copy // (2 if native.use_f16 else 1)
+                    p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
                     hi = torch.empty(native.stack_elems(B, max(p_max, min(2, n))),
-                                     dtype=torch.float32, device=z.device)
+                                     dtype=native.stack_dtype, device=z.device)
                     return p_max, hi, torch.empty_like(hi)
 
                 if native is not None:
@@ -212,7 +229,13 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                             j0, k0v, _ = spans[0]
                             ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0],
                                                      k0v, min(2, n), buf_hi, buf_lo)
-                            native_info = {"verified": ok, "verify_rel_err": verr}
+                            if not ok and native.use_f16:   # out of fp16 range? TF32 flavour
+                                native.use_f16 = False
+                                P_max, buf_hi, buf_lo = engine_buffers()
+                                ok, verr = native.verify(self.model, module, z, perm_dev[j0],
+                                                         inv_dev[j0], k0v, min(2, n), buf_hi, buf_lo)
+                            native_info = {"verified": ok, "verify_rel_err": verr,
+                                           "f16": native.use_f16}
                             if not ok:
                                 native.release()
                                 native = None
@@ -284,6 +307,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
                                   "incremental_first": incremental_used,
+                                  "f16": bool(native is not None and native.use_f16),
                                   "native": native_info}
             return sv
 

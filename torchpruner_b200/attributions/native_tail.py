@@ -24,7 +24,18 @@ import torch.nn as nn
 
 from .. import _lib
 
+import math
+import os
+
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+F16_TARGET = 64.0    # per-tensor power-of-two scaling brings max|x| to ~64 (fp16 max is 65504)
+
+
+def _pow2_scale(max_abs):
+    """Power of two s such that max_abs * s is within a factor sqrt(2) of F16_TARGET."""
+    if not (max_abs > 0.0) or not math.isfinite(max_abs):
+        return 1.0
+    return float(2.0 ** round(math.log2(F16_TARGET / max_abs)))
 INCREMENTAL_MAX_BYTES = 12 << 30   # per-channel contributions of the first layer, per batch
 
 
@@ -119,6 +130,10 @@ class NativeTail:
         # the previous one minus the contribution of one channel.
         self.first = first            # dict or None
         self.incremental = False      # decided per batch in prepare_batch()
+        # fp16x3 flavour: every step has fp16 weights and per-tensor scales, and fits the kernel's
+        # limits.  use_f16 may be switched off at run time (verification failure / overflow).
+        self.f16_ok = all(st.get("w16_hi") is not None for st in steps)
+        self.use_f16 = self.f16_ok and os.environ.get("TORCHPRUNER_B200_F16", "1") != "0"
         self._T = self._s_all = self._base = None
         self._perm = None
         self._pos = 0
@@ -177,6 +192,7 @@ class NativeTail:
                 flat = True
                 i += 1
                 continue
+            layer_call = i   # index of this layer's module in the trace (for calibration)
             if isinstance(m, nn.Conv2d):
                 if flat or m.kernel_size != (3, 3) or m.stride != (1, 1) or m.padding != (1, 1) or \
                         m.dilation != (1, 1) or m.groups != 1 or m.padding_mode != "zeros" or \
@@ -257,10 +273,24 @@ class NativeTail:
                 w_hi, w_lo = _lib.tf32_split(w.contiguous())
                 prep = (key, w_hi, w_lo, scale.contiguous(), shift.contiguous())
                 store[id(m)] = prep
-            _, w_hi, w_lo, scale_k, shift_k = prep
+            _, w_hi, w_lo, scale_k, shift_k = prep[:5]
+            # fp16x3 flavour of the same layer: fp16 pair of w * s_w, calibrated input scale s_in
+            f16_fits = (k_cin % 64 == 0) if k_taps == 9 else (k_cin % 8 == 0)
+            w16_hi = w16_lo = None
+            s_w = s_in = 1.0
+            if f16_fits:
+                if len(prep) < 8:
+                    s_w = _pow2_scale(float(w.abs().max()))
+                    w16_hi, w16_lo = _lib.f16_split(w.contiguous(), s_w)
+                    prep = prep[:5] + (w16_hi, w16_lo, s_w)
+                    store[id(m)] = prep
+                w16_hi, w16_lo, s_w = prep[5:8]
+                s_in = _pow2_scale(float(calls[layer_call][1].detach().abs().max()))
             steps.append({"taps": k_taps, "cin": k_cin, "cout": k_cout, "H": H, "W": W, "relu": relu,
                           "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale_k,
                           "shift": shift_k, "out_view": (H, W, cout) if dense2x2 else None,
+                          "w16_hi": w16_hi, "w16_lo": w16_lo, "s_in": s_in, "s_w": s_w,
+                          "scale16": (scale_k / (s_in * s_w)).contiguous() if f16_fits else None,
                           "flops": 2 * k_cout * k_taps * k_cin * (1 if dense2x2 else H * W)})
             if dense2x2:   # per-channel vectors for the incremental form of this layer
                 scale, shift = scale_k[:cout], shift_k[:cout]
@@ -284,6 +314,12 @@ class NativeTail:
                 or H * W != 1:
             raise _Unsupported("tail does not end in a linear read-out")
         in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
+        for idx, st in enumerate(steps):   # fp16 split outputs need Cout % 64 == 0
+            splits = not (idx == len(steps) - 1 or st["pool"])
+            if splits and st["cout"] % 64:
+                for st2 in steps:
+                    st2["w16_hi"] = None
+                break
         if len(steps) < 2:
             first = None   # the only layer produces the logits: nothing to chain after it
         return cls(steps, pool_first, in_shape, logits.shape[1], first)
@@ -334,6 +370,10 @@ class NativeTail:
             _lib.prefix_contrib_stack(self._T, perm, 0, int(k_start), base, f["scale"], f["shift"],
                                       self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"])
 
+    @property
+    def stack_dtype(self):
+        return torch.float16 if self.use_f16 else torch.float32
+
     def stack_elems(self, B, P):
         """Floats (per hi / lo buffer) of the stacked input of the chained layers for P masks."""
         if self.first is not None:
@@ -352,13 +392,17 @@ class NativeTail:
         permutation.  In incremental mode calls must walk the prefixes consecutively from the
         position given to begin()."""
         B = z.shape[0]
+        f16 = self.use_f16
+        if buf_hi.dtype != self.stack_dtype:
+            raise RuntimeError("stack buffers were allocated for the other operand format")
         if self.incremental:
             if k0 != self._pos:
                 raise RuntimeError("incremental tail evaluated out of order")
             f = self.first
             m_out = _lib.prefix_contrib_stack(
                 self._T, self._perm, k0, P, self._base[:self._M1], f["scale"], f["shift"],
-                self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"], buf_hi, buf_lo)
+                self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"], buf_hi, buf_lo,
+                out_scale=self.steps[1]["s_in"] if f16 else 1.0)
             self._pos += P
             Ho, Wo = (f["Hp"] // 2, f["Wp"] // 2) if f["pool"] else (f["Hp"], f["Wp"])
             shape = (P * B, Ho, Wo, f["C1"])
@@ -366,7 +410,8 @@ class NativeTail:
             steps = self.steps[1:]
         else:
             z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
-            x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo)
+            x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo,
+                                              scale=self.steps[0]["s_in"] if f16 else 1.0)
             steps = self.steps
         last = len(steps) - 1
         for idx, s in enumerate(steps):
@@ -375,13 +420,19 @@ class NativeTail:
                 x_hi = x_hi.reshape(n, 1, 1, -1)
                 x_lo = x_lo.reshape(n, 1, 1, -1)
             split = not (idx == last or s["pool"])
-            y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w_hi"], s["w_lo"], s["taps"], s["scale"],
-                                          s["shift"], s["relu"], split=split)
+            next_scale = steps[idx + 1]["s_in"] if (f16 and idx < last) else 1.0
+            if f16:
+                y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w16_hi"], s["w16_lo"], s["taps"],
+                                              s["scale16"], s["shift"], s["relu"], split=split,
+                                              out_scale=next_scale)
+            else:
+                y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w_hi"], s["w_lo"], s["taps"],
+                                              s["scale"], s["shift"], s["relu"], split=split)
             if s["out_view"] is not None:   # dense form of a conv on a 2x2 image: back to NHWC
                 y_hi = y_hi.view((n,) + s["out_view"])
                 y_lo = y_lo.view((n,) + s["out_view"]) if y_lo is not None else None
             if s["pool"]:
-                y_hi, y_lo = _lib.maxpool2_split_nhwc(y_hi)
+                y_hi, y_lo = _lib.maxpool2_split_nhwc(y_hi, half=f16, scale=next_scale)
             x_hi, x_lo = y_hi, y_lo
         return x_hi.view(x_hi.shape[0], self.n_out)
 

@@ -32,6 +32,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 namespace tp {
 
@@ -48,6 +49,7 @@ struct ConvGeom {
   int num_kb;    // taps * Cin / 32
   int relu;      // activation: 0 none, 1 ReLU, 2 LeakyReLU(slope)
   float slope;
+  float out_scale;  // fp16 split outputs hold y * out_scale (a power of two)
   int split;     // 1: y_hi/y_lo get the TF32 split of the result; 0: y_hi gets the raw fp32
   int promote;   // k-blocks accumulated in TMEM before the partial sum is folded into registers
   long long m_total;
@@ -123,6 +125,40 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with fp16 inputs (K = 16 per instruction, twice the TF32 rate).
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+template <bool F16>
+__device__ __forceinline__ void umma_x(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                       uint32_t idesc, uint32_t accumulate) {
+  if (F16) {
+    umma_f16(tmem_d, desc_a, desc_b, idesc, accumulate);
+  } else {
+    umma_tf32(tmem_d, desc_a, desc_b, idesc, accumulate);
+  }
+}
+// Instruction descriptor: D = F32 (bits 4-5 = 1); A = B = TF32 (2) or F16 (0) in bits 7-9 / 10-12;
+// both K-major; N>>3 at bit 17, M>>4 at bit 24.
+template <int BLOCK_N, bool F16>
+__device__ __forceinline__ constexpr uint32_t make_idesc() {
+  return (1u << 4) | ((F16 ? 0u : 2u) << 7) | ((F16 ? 0u : 2u) << 10) |
+         ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+// Elements per 128-byte k-block row.
+template <bool F16>
+struct KBlock {
+  static constexpr int kElems = F16 ? 64 : 32;
+};
+
 // Shared-memory matrix descriptor, K-major, 128-byte swizzle: rows of 128 bytes, 8-row swizzle
 // atoms 1024 bytes apart (SBO), version 1 (Blackwell), layout type 2 (SWIZZLE_128B).
 __device__ __forceinline__ uint64_t umma_desc_sw128(const void* smem_tile) {
@@ -172,7 +208,7 @@ __device__ __forceinline__ float apply_act(float t, int act, float slope) {
 }
 
 // ---- the kernel ------------------------------------------------------------------------
-template <int BLOCK_N>
+template <int BLOCK_N, bool F16>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
                    const __grid_constant__ CUtensorMap tm_a_lo,
@@ -235,7 +271,8 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
-      const int kc = (g.Cin + kBlockK - 1) / kBlockK;
+      constexpr int kKE = KBlock<F16>::kElems;
+      const int kc = (g.Cin + kKE - 1) / kKE;
       int stage = 0;
       uint32_t phase = 0;
       int tap = 0, cb = 0;
@@ -245,10 +282,10 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
         uint8_t* st = smem + stage * Cfg::kStageBytes;
         const int r = (g.taps == 9) ? tap / 3 : 1;
         const int s = (g.taps == 9) ? tap - r * 3 : 1;
-        tma_load_4d(st, &tm_a_hi, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
-        tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, s - 1, h0 + r - 1, n0, &full[stage]);
-        tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
-        tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK, nt * BLOCK_N,
+        tma_load_4d(st, &tm_a_hi, cb * kKE, s - 1, h0 + r - 1, n0, &full[stage]);
+        tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, s - 1, h0 + r - 1, n0, &full[stage]);
+        tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N, &full[stage]);
+        tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE, nt * BLOCK_N,
                     &full[stage]);
         if (++cb == kc) {
           cb = 0;
@@ -263,10 +300,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer =====
-      // Instruction descriptor: D=F32 (bits 4-5 = 1), A=B=TF32 (bits 7-9, 10-12 = 2), both
-      // K-major, N>>3 at bit 17, M>>4 at bit 24.
-      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
-                                 ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+      constexpr uint32_t idesc = make_idesc<BLOCK_N, F16>();
       int stage = 0;
       uint32_t phase = 0;
       int chunk = 0, in_chunk = 0;
@@ -288,9 +322,9 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
         for (int kk = 0; kk < kBlockK / 8; ++kk) {
           const uint64_t off = (uint64_t)(kk * 32 >> 4);  // 8 tf32 = 32 bytes inside the swizzle row
           // small cross terms first, the dominant hi*hi term last
-          umma_tf32(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-          umma_tf32(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-          umma_tf32(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+          umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+          umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+          umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
         }
         umma_commit(&empty[stage]);  // stage reusable once these MMAs have read it
         if (++stage == Cfg::kStages) {
@@ -446,7 +480,7 @@ __device__ __forceinline__ int count_kblocks(const ConvGeom& g, int h0, int w0) 
   int n = 0;
 #pragma unroll
   for (int t = 0; t < 9; ++t) n += tap_meets_image(g, h0, w0, t / 3, t % 3) ? 1 : 0;
-  return n * ((g.Cin + kBlockK - 1) / kBlockK);
+  return n * (g.num_kb / 9);
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
@@ -456,7 +490,7 @@ __device__ __forceinline__ void bulk_wait_read() {
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool F16>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                        const __grid_constant__ CUtensorMap tm_a_lo,
@@ -508,7 +542,8 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
-      const int kc = (g.Cin + kBlockK - 1) / kBlockK;
+      constexpr int kKE = KBlock<F16>::kElems;
+      const int kc = (g.Cin + kKE - 1) / kKE;
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -524,11 +559,11 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             mbar_wait(&empty[stage], phase ^ 1u);
             mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
             uint8_t* st = smem + stage * Cfg::kStageBytes;
-            tma_load_4d(st, &tm_a_hi, cb * kBlockK, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
-            tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kBlockK, w0 + s - 1, h0 + r - 1, n0,
+            tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
+            tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
                         &full[stage]);
-            tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kBlockK, nt * BLOCK_N, &full[stage]);
-            tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kBlockK,
+            tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N, &full[stage]);
+            tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
                         nt * BLOCK_N, &full[stage]);
             if (++stage == Cfg::kStages) {
               stage = 0;
@@ -541,8 +576,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer =====
-      constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) |
-                                 ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+      constexpr uint32_t idesc = make_idesc<BLOCK_N, F16>();
       int stage = 0;
       uint32_t phase = 0;
       int buf = 0;
@@ -568,9 +602,9 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 #pragma unroll
           for (int kk = 0; kk < kBlockK / 8; ++kk) {
             const uint64_t off = (uint64_t)(kk * 32 >> 4);
-            umma_tf32(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-            umma_tf32(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-            umma_tf32(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+            umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+            umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+            umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
           }
           umma_commit(&empty[stage]);
           if (++stage == Cfg::kStages) {
@@ -633,6 +667,48 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
         }
       }
       epi_barrier();  // scale/shift of this tile visible to all epilogue threads
+      if (F16 && g.split) {
+        // fp16 split outputs: staging rows are 64 halves (128 bytes), so 64 columns per store
+#pragma unroll
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 64) {
+          float y[64];
+#pragma unroll
+          for (int j = 0; j < 64; ++j) {
+            float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+            y[j] = apply_act(t, g.relu, g.slope) * g.out_scale;
+          }
+          for (int pass = 0; pass < 2; ++pass) {
+            uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
+            if (issuer) bulk_wait_read<1>();
+            epi_barrier();
+            uint8_t* rowp = sbuf + row * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              uint32_t w[4];
+#pragma unroll
+              for (int h2 = 0; h2 < 4; ++h2) {
+                const float v0 = y[8 * c + 2 * h2], v1 = y[8 * c + 2 * h2 + 1];
+                __half a0 = __float2half_rn(v0), a1 = __float2half_rn(v1);
+                if (pass == 1) {
+                  a0 = __float2half_rn(v0 - __half2float(a0));
+                  a1 = __float2half_rn(v1 - __half2float(a1));
+                }
+                w[h2] = (uint32_t)__half_as_ushort(a0) | ((uint32_t)__half_as_ushort(a1) << 16);
+              }
+              *reinterpret_cast<uint4*>(rowp + ((c ^ (row & 7)) << 4)) =
+                  make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            fence_proxy_async();
+            epi_barrier();
+            if (issuer) {
+              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
+              bulk_commit();
+            }
+            ++stores;
+          }
+        }
+        continue;
+      }
       const int passes = g.split ? 2 : 1;
 #pragma unroll
       for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
@@ -684,25 +760,48 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 }
 
 // ---- small elementwise companions ------------------------------------------------------
-__global__ void __launch_bounds__(256)
-tf32_split_kernel(const float* __restrict__ x, long long n, float* __restrict__ hi,
-                  float* __restrict__ lo) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-       i += gridDim.x * (long long)blockDim.x) {
-    const float v = x[i];
+// Split storage: either the TF32 pair in fp32 containers, or the fp16 pair of v * scale
+// (scale a power of two chosen per tensor so the values sit mid-range of fp16; an fp16 number
+// has the same 11 significant bits as a TF32 one, so hi + lo carries the same 2^-23 precision).
+template <bool HALF>
+struct SplitStore {
+  using T = float;
+  __device__ __forceinline__ static void put(T* hi, T* lo, long long i, float v, float) {
     const float h = tf32_hi(v);
     hi[i] = h;
     lo[i] = tf32_lo(v, h);
   }
+};
+template <>
+struct SplitStore<true> {
+  using T = __half;
+  __device__ __forceinline__ static void put(T* hi, T* lo, long long i, float v, float scale) {
+    const float vs = v * scale;
+    const __half h = __float2half_rn(vs);
+    hi[i] = h;
+    lo[i] = __float2half_rn(vs - __half2float(h));
+  }
+};
+
+template <bool HALF>
+__global__ void __launch_bounds__(256)
+split_kernel(const float* __restrict__ x, long long n, float scale,
+             typename SplitStore<HALF>::T* __restrict__ hi,
+             typename SplitStore<HALF>::T* __restrict__ lo) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += gridDim.x * (long long)blockDim.x)
+    SplitStore<HALF>::put(hi, lo, i, x[i], scale);
 }
 
 // z: NCHW [B, C, H, W].  out: NHWC [P*B, Ho, Wo, C] hi/lo of the (optionally 2x2 max-pooled)
 // activation with the first (k0+p+1) channels of the permutation zeroed.  Pooling commutes with
 // the per-channel mask, so it is applied once, before the P-fold replication.
+template <bool HALF>
 __global__ void __launch_bounds__(256)
 mask_stack_nhwc_kernel(const float* __restrict__ z, const int32_t* __restrict__ inv_perm,
-                       long long k0, int P, int B, int C, int H, int W, int pool,
-                       float* __restrict__ out_hi, float* __restrict__ out_lo) {
+                       long long k0, int P, int B, int C, int H, int W, int pool, float scale,
+                       typename SplitStore<HALF>::T* __restrict__ out_hi,
+                       typename SplitStore<HALF>::T* __restrict__ out_lo) {
   const int Ho = pool ? H / 2 : H, Wo = pool ? W / 2 : W;
   const long long per_copy = (long long)B * Ho * Wo * C;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < per_copy;
@@ -721,21 +820,18 @@ mask_stack_nhwc_kernel(const float* __restrict__ z, const int32_t* __restrict__ 
     } else {
       v = src[ho * W + wo];
     }
-    const float h = tf32_hi(v);
-    const float l = tf32_lo(v, h);
     const long long pos = (long long)inv_perm[c] - k0;  // masked for every p >= pos
-    for (int p = 0; p < P; ++p) {
-      const bool masked = p >= pos;
-      out_hi[p * per_copy + e] = masked ? 0.f : h;
-      out_lo[p * per_copy + e] = masked ? 0.f : l;
-    }
+    for (int p = 0; p < P; ++p)
+      SplitStore<HALF>::put(out_hi, out_lo, p * per_copy + e, p >= pos ? 0.f : v, scale);
   }
 }
 
 // x: NHWC raw fp32 [N, H, W, C] -> 2x2 max pool -> hi/lo [N, H/2, W/2, C].  C % 4 == 0.
+template <bool HALF>
 __global__ void __launch_bounds__(256)
 maxpool2_split_nhwc_kernel(const float* __restrict__ x, long long N, int H, int W, int C,
-                           float* __restrict__ hi, float* __restrict__ lo) {
+                           float scale, typename SplitStore<HALF>::T* __restrict__ hi,
+                           typename SplitStore<HALF>::T* __restrict__ lo) {
   const int Ho = H / 2, Wo = W / 2, C4 = C / 4;
   const long long total = N * Ho * Wo * C4;
   const float4* x4 = reinterpret_cast<const float4*>(x);
@@ -750,15 +846,14 @@ maxpool2_split_nhwc_kernel(const float* __restrict__ x, long long N, int H, int 
     const long long base = ((n * H + 2 * ho) * W + 2 * wo) * C4 + c4;
     const float4 a = x4[base], b = x4[base + C4], c = x4[base + (long long)W * C4],
                  d = x4[base + (long long)W * C4 + C4];
-    float4 m;
-    m.x = fmaxf(fmaxf(a.x, b.x), fmaxf(c.x, d.x));
-    m.y = fmaxf(fmaxf(a.y, b.y), fmaxf(c.y, d.y));
-    m.z = fmaxf(fmaxf(a.z, b.z), fmaxf(c.z, d.z));
-    m.w = fmaxf(fmaxf(a.w, b.w), fmaxf(c.w, d.w));
-    const float4 h = make_float4(tf32_hi(m.x), tf32_hi(m.y), tf32_hi(m.z), tf32_hi(m.w));
-    reinterpret_cast<float4*>(hi)[e] = h;
-    reinterpret_cast<float4*>(lo)[e] = make_float4(tf32_lo(m.x, h.x), tf32_lo(m.y, h.y),
-                                                   tf32_lo(m.z, h.z), tf32_lo(m.w, h.w));
+    const float m0 = fmaxf(fmaxf(a.x, b.x), fmaxf(c.x, d.x));
+    const float m1 = fmaxf(fmaxf(a.y, b.y), fmaxf(c.y, d.y));
+    const float m2 = fmaxf(fmaxf(a.z, b.z), fmaxf(c.z, d.z));
+    const float m3 = fmaxf(fmaxf(a.w, b.w), fmaxf(c.w, d.w));
+    SplitStore<HALF>::put(hi, lo, 4 * e, m0, scale);
+    SplitStore<HALF>::put(hi, lo, 4 * e + 1, m1, scale);
+    SplitStore<HALF>::put(hi, lo, 4 * e + 2, m2, scale);
+    SplitStore<HALF>::put(hi, lo, 4 * e + 3, m3, scale);
   }
 }
 
@@ -781,39 +876,39 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-static int make_map(CUtensorMap* map, const float* base, int rank, const cuuint64_t* dims,
-                    const cuuint32_t* box) {
+static int make_map(CUtensorMap* map, const void* base, int rank, const cuuint64_t* dims,
+                    const cuuint32_t* box, bool half = false) {
   EncodeTiledFn fn = encode_tiled_fn();
   TP_REQUIRE(fn != nullptr, TP_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
   cuuint64_t strides[4];
-  cuuint64_t acc = 4;
+  cuuint64_t acc = half ? 2 : 4;
   for (int i = 0; i < rank - 1; ++i) {
     acc *= dims[i];
     strides[i] = acc;
   }
   const cuuint32_t ones[4] = {1, 1, 1, 1};
   const CUresult rc =
-      fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float*>(base), dims,
-         strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+      fn(map, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+         (cuuint32_t)rank, const_cast<void*>(base), dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   TP_REQUIRE(rc == CUDA_SUCCESS, TP_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d",
              (int)rc);
   return TP_OK;
 }
 
-template <int BLOCK_N>
-static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const float* w_hi,
-                       const float* w_lo, const ConvGeom& g, const float* scale,
+template <int BLOCK_N, bool F16>
+static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const void* w_hi,
+                       const void* w_lo, const ConvGeom& g, const float* scale,
                        const float* shift, float* y_hi, float* y_lo, cudaStream_t st) {
   using Cfg = ConvCfg<BLOCK_N>;
   CUtensorMap b_hi, b_lo;
   const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
-  const cuuint32_t bbox[2] = {kBlockK, BLOCK_N};
-  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox);
+  const cuuint32_t bbox[2] = {(cuuint32_t)KBlock<F16>::kElems, BLOCK_N};
+  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
-  rc = make_map(&b_lo, w_lo, 2, bdims, bbox);
+  rc = make_map(&b_lo, w_lo, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
-  auto kern = conv_tf32x3_kernel<BLOCK_N>;
+  auto kern = conv_tf32x3_kernel<BLOCK_N, F16>;
   TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const long long m_tiles = (g.m_total + kBlockM - 1) / kBlockM;
   const int n_tiles = (g.Cout + BLOCK_N - 1) / BLOCK_N;
@@ -825,27 +920,30 @@ static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const f
 }
 
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool F16>
 static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_lo,
-                                  const float* w_hi, const float* w_lo, const ConvGeom& g,
-                                  const float* scale, const float* shift, float* y_hi, float* y_lo,
+                                  const void* w_hi, const void* w_lo, const ConvGeom& g,
+                                  const float* scale, const float* shift, void* y_hi, void* y_lo,
                                   cudaStream_t st) {
   using Cfg = ConvCfgP<BLOCK_N>;
   CUtensorMap b_hi, b_lo, o_hi, o_lo;
   const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
-  const cuuint32_t bbox[2] = {kBlockK, BLOCK_N};
-  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox);
+  const cuuint32_t bbox[2] = {(cuuint32_t)KBlock<F16>::kElems, BLOCK_N};
+  int rc = make_map(&b_hi, w_hi, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
-  rc = make_map(&b_lo, w_lo, 2, bdims, bbox);
+  rc = make_map(&b_lo, w_lo, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
+  // fp16 split outputs are stored 64 halves (128 bytes) per staging row; everything else is fp32
+  const bool half_out = F16 && g.split;
   const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.W, (cuuint64_t)g.H,
                                (cuuint64_t)g.N};
-  const cuuint32_t ybox[4] = {32, (cuuint32_t)g.bw, (cuuint32_t)g.bh, (cuuint32_t)g.bn};
-  rc = make_map(&o_hi, y_hi, 4, ydims, ybox);
+  const cuuint32_t ybox[4] = {half_out ? 64u : 32u, (cuuint32_t)g.bw, (cuuint32_t)g.bh,
+                              (cuuint32_t)g.bn};
+  rc = make_map(&o_hi, y_hi, 4, ydims, ybox, half_out);
   if (rc != TP_OK) return rc;
-  rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 4, ydims, ybox);
+  rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 4, ydims, ybox, half_out);
   if (rc != TP_OK) return rc;
-  auto kern = conv_tf32x3_persistent<BLOCK_N>;
+  auto kern = conv_tf32x3_persistent<BLOCK_N, F16>;
   TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const long long img_blocks = (g.N + g.bn - 1) / g.bn;
   const long long m_tiles = img_blocks * g.tiles_h * g.tiles_w;
@@ -859,31 +957,21 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   return TP_OK;
 }
 
-static inline unsigned ew_grid(long long items) {
-  long long blocks = (items + 255) / 256;
-  const long long cap = (long long)sm_count() * 16;
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  return (unsigned)blocks;
-}
-
-}  // namespace tp
-
-extern "C" {
-
-int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
-                   int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
-                   const float* scale, const float* shift, int act, float leaky_slope,
-                   float* y_hi, float* y_lo, tp_stream_t stream) {
-  using namespace tp;
+template <bool F16>
+static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W,
+                        int64_t Cin, const void* w_hi, const void* w_lo, int taps, int64_t Cout,
+                        const float* scale, const float* shift, int act, float leaky_slope,
+                        float out_scale, void* y_hi, void* y_lo, tp_stream_t stream) {
+  constexpr int kKE = KBlock<F16>::kElems;
   TP_REQUIRE(N >= 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, TP_ERR_INVALID,
              "tp_conv_tf32x3: bad dimension");
   TP_REQUIRE(taps == 1 || taps == 9, TP_ERR_INVALID, "tp_conv_tf32x3: taps must be 1 or 9");
   TP_REQUIRE(act >= 0 && act <= 2, TP_ERR_INVALID, "tp_conv_tf32x3: act must be 0, 1 or 2");
   // A linear layer's last k-block may hang over the end of K: the TMA unit zero-fills both
   // operands there.  A convolution's k index is tap*Cin + c, so its Cin must fill whole blocks.
-  TP_REQUIRE(taps == 1 ? (Cin % 4 == 0) : (Cin % kBlockK == 0), TP_ERR_LIMIT,
-             "tp_conv_tf32x3: Cin must be a multiple of 32 (conv) / 4 (linear)");
+  TP_REQUIRE(taps == 1 ? (Cin % (F16 ? 8 : 4) == 0) : (Cin % kKE == 0), TP_ERR_LIMIT,
+             "tp_conv_%s: Cin must be a multiple of %d (conv) / %d (linear)",
+             F16 ? "f16x3" : "tf32x3", kKE, F16 ? 8 : 4);
   TP_REQUIRE(W <= 128 && (128 % W) == 0, TP_ERR_LIMIT,
              "tp_conv_tf32x3: W must divide 128 (got %lld)", (long long)W);
   if (N == 0) return TP_OK;
@@ -916,8 +1004,11 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
   // that fall entirely in the zero padding are skipped (31 % of the MMAs at 4x4, 16 % at 8x8).
   // The persistent kernel writes through TMA stores: row pitch must be a multiple of 16 bytes and
   // the 32-column store box must not straddle the end of a row.
-  const bool persistent = (Cout > 16) && (Cout % 32 == 0) && tuning().conv_variant != 1 &&
-                          ((uintptr_t)y_hi % 16 == 0) && (!y_lo || (uintptr_t)y_lo % 16 == 0);
+  const bool persistent = (Cout > 16) && (Cout % (F16 ? 64 : 32) == 0) &&
+                          tuning().conv_variant != 1 && ((uintptr_t)y_hi % 16 == 0) &&
+                          (!y_lo || (uintptr_t)y_lo % 16 == 0);
+  TP_REQUIRE(!F16 || persistent || y_lo == nullptr, TP_ERR_LIMIT,
+             "tp_conv_f16x3: split fp16 outputs need Cout %% 64 == 0");
   if (persistent && taps == 9 && tuning().conv_pos_major != 1 &&
       H * W <= tuning().conv_pos_major_max_hw && H * W >= 4 && N >= 128) {
     g.bw = 1;
@@ -926,9 +1017,10 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
     g.tiles_h = (int)H;
     g.tiles_w = (int)W;
   }
-  g.num_kb = taps * (int)((Cin + kBlockK - 1) / kBlockK);
+  g.num_kb = taps * (int)((Cin + kKE - 1) / kKE);
   g.relu = act;
   g.slope = leaky_slope;
+  g.out_scale = out_scale;
   g.split = (y_lo != nullptr);
   g.promote = tuning().conv_promote;
   g.m_total = N * H * W;
@@ -936,21 +1028,55 @@ int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, i
 
   CUtensorMap a_hi, a_lo;
   const cuuint64_t adims[4] = {(cuuint64_t)Cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  const cuuint32_t abox[4] = {kBlockK, (cuuint32_t)g.bw, (cuuint32_t)g.bh, (cuuint32_t)g.bn};
-  int rc = make_map(&a_hi, x_hi, 4, adims, abox);
+  const cuuint32_t abox[4] = {(cuuint32_t)kKE, (cuuint32_t)g.bw, (cuuint32_t)g.bh,
+                              (cuuint32_t)g.bn};
+  int rc = make_map(&a_hi, x_hi, 4, adims, abox, F16);
   if (rc != TP_OK) return rc;
-  rc = make_map(&a_lo, x_lo, 4, adims, abox);
+  rc = make_map(&a_lo, x_lo, 4, adims, abox, F16);
   if (rc != TP_OK) return rc;
+  float* yf_hi = static_cast<float*>(y_hi);
+  float* yf_lo = static_cast<float*>(y_lo);
   if (Cout <= 16)
-    return launch_conv<16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+    return launch_conv<16, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
   if (persistent) {
     if (Cout <= 64)
-      return launch_conv_persistent<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
-    return launch_conv_persistent<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+      return launch_conv_persistent<64, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo,
+                                             st);
+    return launch_conv_persistent<128, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo,
+                                            st);
   }
   if (Cout <= 64)
-    return launch_conv<64>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
-  return launch_conv<128>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo, st);
+    return launch_conv<64, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
+  return launch_conv<128, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
+}
+
+
+static inline unsigned ew_grid(long long items) {
+  long long blocks = (items + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+}  // namespace tp
+
+extern "C" {
+
+int tp_conv_tf32x3(const float* x_hi, const float* x_lo, int64_t N, int64_t H, int64_t W,
+                   int64_t Cin, const float* w_hi, const float* w_lo, int taps, int64_t Cout,
+                   const float* scale, const float* shift, int act, float leaky_slope,
+                   float* y_hi, float* y_lo, tp_stream_t stream) {
+  return tp::conv_x3_impl<false>(x_hi, x_lo, N, H, W, Cin, w_hi, w_lo, taps, Cout, scale, shift,
+                                 act, leaky_slope, 1.0f, y_hi, y_lo, stream);
+}
+
+int tp_conv_f16x3(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W, int64_t Cin,
+                  const void* w_hi, const void* w_lo, int taps, int64_t Cout, const float* scale,
+                  const float* shift, int act, float leaky_slope, float out_scale, void* y_hi,
+                  void* y_lo, tp_stream_t stream) {
+  return tp::conv_x3_impl<true>(x_hi, x_lo, N, H, W, Cin, w_hi, w_lo, taps, Cout, scale, shift,
+                                act, leaky_slope, out_scale, y_hi, y_lo, stream);
 }
 
 int64_t tp_conv_tf32x3_flops(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int taps) {
@@ -969,14 +1095,25 @@ int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t s
   TP_REQUIRE(n >= 0, TP_ERR_INVALID, "tp_tf32_split: negative size");
   if (n == 0) return TP_OK;
   TP_REQUIRE(x && hi && lo, TP_ERR_INVALID, "tp_tf32_split: NULL pointer");
-  tp::tf32_split_kernel<<<tp::ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, hi, lo);
-  TP_LAUNCH_CHECK("tf32_split_kernel");
+  tp::split_kernel<false><<<tp::ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, n, 1.f,
+                                                                                       hi, lo);
+  TP_LAUNCH_CHECK("split_kernel");
   return TP_OK;
 }
 
-int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
-                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
-                       tp_stream_t stream) {
+int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_stream_t stream) {
+  TP_REQUIRE(n >= 0, TP_ERR_INVALID, "tp_f16_split: negative size");
+  if (n == 0) return TP_OK;
+  TP_REQUIRE(x && hi && lo, TP_ERR_INVALID, "tp_f16_split: NULL pointer");
+  tp::split_kernel<true><<<tp::ew_grid(n), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, n, scale, static_cast<__half*>(hi), static_cast<__half*>(lo));
+  TP_LAUNCH_CHECK("split_kernel");
+  return TP_OK;
+}
+
+static int mask_stack_nhwc_impl(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
+                                int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
+                                void* out_hi, void* out_lo, bool half, tp_stream_t stream) {
   TP_REQUIRE(P >= 0 && B >= 0 && C >= 0 && H >= 0 && W >= 0 && k0 >= -1, TP_ERR_INVALID,
              "tp_mask_stack_nhwc: negative dimension");
   TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
@@ -984,14 +1121,36 @@ int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int6
   const long long per_copy = B * (pool ? H / 2 : H) * (pool ? W / 2 : W) * C;
   if (per_copy == 0 || P == 0) return TP_OK;
   TP_REQUIRE(z && inv_perm && out_hi && out_lo, TP_ERR_INVALID, "tp_mask_stack_nhwc: NULL pointer");
-  tp::mask_stack_nhwc_kernel<<<tp::ew_grid(per_copy), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, out_hi, out_lo);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (half) {
+    tp::mask_stack_nhwc_kernel<true><<<tp::ew_grid(per_copy), 256, 0, st>>>(
+        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, scale,
+        static_cast<__half*>(out_hi), static_cast<__half*>(out_lo));
+  } else {
+    tp::mask_stack_nhwc_kernel<false><<<tp::ew_grid(per_copy), 256, 0, st>>>(
+        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, 1.f,
+        static_cast<float*>(out_hi), static_cast<float*>(out_lo));
+  }
   TP_LAUNCH_CHECK("mask_stack_nhwc_kernel");
   return TP_OK;
 }
 
-int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
-                           float* lo, tp_stream_t stream) {
+int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
+                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
+                       tp_stream_t stream) {
+  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, 1.f, out_hi, out_lo, false,
+                              stream);
+}
+
+int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
+                           int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
+                           void* out_hi, void* out_lo, tp_stream_t stream) {
+  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, scale, out_hi, out_lo, true,
+                              stream);
+}
+
+static int maxpool2_split_impl(const float* x, int64_t N, int64_t H, int64_t W, int64_t C,
+                               float scale, void* hi, void* lo, bool half, tp_stream_t stream) {
   TP_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0, TP_ERR_INVALID,
              "tp_maxpool2_split_nhwc: negative dimension");
   TP_REQUIRE(H % 2 == 0 && W % 2 == 0 && C % 4 == 0, TP_ERR_LIMIT,
@@ -999,10 +1158,26 @@ int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int6
   const long long total = N * (H / 2) * (W / 2) * (C / 4);
   if (total == 0) return TP_OK;
   TP_REQUIRE(x && hi && lo, TP_ERR_INVALID, "tp_maxpool2_split_nhwc: NULL pointer");
-  tp::maxpool2_split_nhwc_kernel<<<tp::ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, N, (int)H, (int)W, (int)C, hi, lo);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (half) {
+    tp::maxpool2_split_nhwc_kernel<true><<<tp::ew_grid(total), 256, 0, st>>>(
+        x, N, (int)H, (int)W, (int)C, scale, static_cast<__half*>(hi), static_cast<__half*>(lo));
+  } else {
+    tp::maxpool2_split_nhwc_kernel<false><<<tp::ew_grid(total), 256, 0, st>>>(
+        x, N, (int)H, (int)W, (int)C, 1.f, static_cast<float*>(hi), static_cast<float*>(lo));
+  }
   TP_LAUNCH_CHECK("maxpool2_split_nhwc_kernel");
   return TP_OK;
+}
+
+int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
+                           float* lo, tp_stream_t stream) {
+  return maxpool2_split_impl(x, N, H, W, C, 1.f, hi, lo, false, stream);
+}
+
+int tp_maxpool2_split_nhwc_f16(const float* x, int64_t N, int64_t H, int64_t W, int64_t C,
+                               float scale, void* hi, void* lo, tp_stream_t stream) {
+  return maxpool2_split_impl(x, N, H, W, C, scale, hi, lo, true, stream);
 }
 
 }  // extern "C"

@@ -18,6 +18,8 @@
 //                             start of its span.
 #include "common.cuh"
 
+#include <cuda_fp16.h>
+
 namespace tp {
 
 __device__ __forceinline__ float inc_tf32_hi(float x) {
@@ -153,6 +155,7 @@ struct PrefixGeom {
   int relu;          // activation: 0 none, 1 ReLU, 2 LeakyReLU(slope)
   float slope;
   int emit;          // 0: accumulate only (advance the running sum), 1: write out_hi / out_lo
+  float out_scale;   // fp16 outputs hold y * out_scale
 };
 
 __device__ __forceinline__ float affine_act(double run, float a, float b, int act, float slope) {
@@ -164,12 +167,12 @@ __device__ __forceinline__ float affine_act(double run, float a, float b, int ac
 
 // One thread owns 4 consecutive output channels of one output position (after the optional pool)
 // and walks the P masks of the chunk with its running sums in float64 registers.
-template <bool POOL>
+template <bool POOL, bool HALF>
 __global__ void __launch_bounds__(256)
 prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restrict__ perm,
                             long long k0, int P, double* __restrict__ base,
                             const float* __restrict__ scale, const float* __restrict__ shift,
-                            PrefixGeom g, float* __restrict__ out_hi, float* __restrict__ out_lo) {
+                            PrefixGeom g, void* __restrict__ out_hi_v, void* __restrict__ out_lo_v) {
   constexpr int NSRC = POOL ? 4 : 1;
   const int opp = g.C1 >> 2;
   const long long out_pos = POOL ? (g.M1 / g.C1) / 4 : (g.M1 / g.C1);  // output positions
@@ -225,13 +228,28 @@ prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restri
         }
       }
       if (g.emit) {
-        const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
-                                      inc_tf32_hi(y.w));
-        const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
-                                      inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
         const long long o = (long long)p * m_out + pos * g.C1 + o4 * 4;
-        *reinterpret_cast<float4*>(out_hi + o) = hi;
-        *reinterpret_cast<float4*>(out_lo + o) = lo;
+        if (HALF) {  // fp16 pair of y * out_scale (same 11 significant bits as a TF32 number)
+          const float v[4] = {y.x * g.out_scale, y.y * g.out_scale, y.z * g.out_scale,
+                              y.w * g.out_scale};
+          __half h[4], l[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            h[q] = __float2half_rn(v[q]);
+            l[q] = __float2half_rn(v[q] - __half2float(h[q]));
+          }
+          *reinterpret_cast<uint2*>(static_cast<__half*>(out_hi_v) + o) =
+              *reinterpret_cast<const uint2*>(h);
+          *reinterpret_cast<uint2*>(static_cast<__half*>(out_lo_v) + o) =
+              *reinterpret_cast<const uint2*>(l);
+        } else {
+          const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
+                                        inc_tf32_hi(y.w));
+          const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
+                                        inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
+          *reinterpret_cast<float4*>(static_cast<float*>(out_hi_v) + o) = hi;
+          *reinterpret_cast<float4*>(static_cast<float*>(out_lo_v) + o) = lo;
+        }
       }
     }
 #pragma unroll
@@ -302,10 +320,11 @@ int tp_contrib_sum(const float* T, int64_t C, int64_t M1, double* s_all, tp_stre
   return TP_OK;
 }
 
-int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
-                            double* base, const float* scale, const float* shift, int64_t pixels,
-                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int act,
-                            float leaky_slope, float* out_hi, float* out_lo, tp_stream_t stream) {
+static int prefix_contrib_stack_impl(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                                     double* base, const float* scale, const float* shift,
+                                     int64_t pixels, int64_t C1, int64_t Hp, int64_t Wp, int pool,
+                                     int act, float leaky_slope, float out_scale, bool half,
+                                     void* out_hi, void* out_lo, tp_stream_t stream) {
   using namespace tp;
   TP_REQUIRE(P >= 0 && k0 >= 0 && pixels >= 0 && C1 > 0, TP_ERR_INVALID,
              "tp_prefix_contrib_stack: bad dimension");
@@ -326,17 +345,42 @@ int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int
   g.relu = act;
   g.slope = leaky_slope;
   g.emit = out_hi != nullptr;
+  g.out_scale = out_scale;
   const long long items = (pool ? pixels / 4 : pixels) * (C1 / 4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (pool) {
-    prefix_contrib_stack_kernel<true><<<inc_grid(items), 256, 0, st>>>(
-        T, perm, k0, (int)P, base, scale, shift, g, out_hi, out_lo);
+  const unsigned grid = inc_grid(items);
+  if (pool && half) {
+    prefix_contrib_stack_kernel<true, true><<<grid, 256, 0, st>>>(T, perm, k0, (int)P, base, scale,
+                                                                  shift, g, out_hi, out_lo);
+  } else if (pool) {
+    prefix_contrib_stack_kernel<true, false><<<grid, 256, 0, st>>>(T, perm, k0, (int)P, base, scale,
+                                                                   shift, g, out_hi, out_lo);
+  } else if (half) {
+    prefix_contrib_stack_kernel<false, true><<<grid, 256, 0, st>>>(T, perm, k0, (int)P, base, scale,
+                                                                   shift, g, out_hi, out_lo);
   } else {
-    prefix_contrib_stack_kernel<false><<<inc_grid(items), 256, 0, st>>>(
-        T, perm, k0, (int)P, base, scale, shift, g, out_hi, out_lo);
+    prefix_contrib_stack_kernel<false, false><<<grid, 256, 0, st>>>(T, perm, k0, (int)P, base,
+                                                                    scale, shift, g, out_hi, out_lo);
   }
   TP_LAUNCH_CHECK("prefix_contrib_stack_kernel");
   return TP_OK;
+}
+
+int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                            double* base, const float* scale, const float* shift, int64_t pixels,
+                            int64_t C1, int64_t Hp, int64_t Wp, int pool, int act,
+                            float leaky_slope, float* out_hi, float* out_lo, tp_stream_t stream) {
+  return prefix_contrib_stack_impl(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp, pool, act,
+                                   leaky_slope, 1.f, false, out_hi, out_lo, stream);
+}
+
+int tp_prefix_contrib_stack_f16(const float* T, const int64_t* perm, int64_t k0, int64_t P,
+                                double* base, const float* scale, const float* shift,
+                                int64_t pixels, int64_t C1, int64_t Hp, int64_t Wp, int pool,
+                                int act, float leaky_slope, float out_scale, void* out_hi,
+                                void* out_lo, tp_stream_t stream) {
+  return prefix_contrib_stack_impl(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp, pool, act,
+                                   leaky_slope, out_scale, true, out_hi, out_lo, stream);
 }
 
 }  // extern "C"
