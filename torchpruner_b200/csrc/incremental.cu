@@ -28,6 +28,18 @@ __device__ __forceinline__ float inc_tf32_hi(float x) {
   return __uint_as_float(r);
 }
 
+// streaming 16-byte load of a contribution (read once per mask, never re-used by this CTA)
+__device__ __forceinline__ float4 ld_nc_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+__device__ __forceinline__ void st_cs_u2(void* p, uint2 v) {
+  asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
 // z: NCHW [B, C, H, W]; pool != 0 => z' = MaxPool2d(2)(z), spatial Hp x Wp.
 __device__ __forceinline__ float zprime(const float* __restrict__ z, int b, int c, int h, int w,
                                         int C, int H, int W, int pool) {
@@ -209,46 +221,59 @@ prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restri
       run[s][2] = bp[2];
       run[s][3] = bp[3];
     }
-    for (int p = 0; p < P; ++p) {
-      const long long c = perm[k0 + p];
-      const float* Tc = T + c * g.M1;
-      float4 y = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    // U masks per trip: all their contribution loads are issued before the first dependent
+    // subtraction, so a thread keeps U x NSRC 16-byte loads in flight instead of NSRC
+    constexpr int U = POOL ? 2 : 8;
+    for (int p0 = 0; p0 < P; p0 += U) {
+      float4 tv[U][NSRC];
 #pragma unroll
-      for (int s = 0; s < NSRC; ++s) {
-        const float4 t = *reinterpret_cast<const float4*>(Tc + src[s] * g.C1 + o4 * 4);
-        run[s][0] -= (double)t.x;
-        run[s][1] -= (double)t.y;
-        run[s][2] -= (double)t.z;
-        run[s][3] -= (double)t.w;
-        if (g.emit) {
-          y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
-          y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
-          y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
-          y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
-        }
+      for (int u = 0; u < U; ++u) {
+        const long long c = perm[k0 + min(p0 + u, P - 1)];
+        const float* Tc = T + c * g.M1;
+#pragma unroll
+        for (int s = 0; s < NSRC; ++s)
+          tv[u][s] = ld_nc_f4(Tc + src[s] * g.C1 + o4 * 4);
       }
-      if (g.emit) {
-        const long long o = (long long)p * m_out + pos * g.C1 + o4 * 4;
-        if (HALF) {  // fp16 pair of y * out_scale (same 11 significant bits as a TF32 number)
-          const float v[4] = {y.x * g.out_scale, y.y * g.out_scale, y.z * g.out_scale,
-                              y.w * g.out_scale};
-          __half h[4], l[4];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            h[q] = __float2half_rn(v[q]);
-            l[q] = __float2half_rn(v[q] - __half2float(h[q]));
+      for (int u = 0; u < U; ++u) {
+        const int p = p0 + u;
+        if (p >= P) break;
+        float4 y = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+        for (int s = 0; s < NSRC; ++s) {
+          const float4 t = tv[u][s];
+          run[s][0] -= (double)t.x;
+          run[s][1] -= (double)t.y;
+          run[s][2] -= (double)t.z;
+          run[s][3] -= (double)t.w;
+          if (g.emit) {
+            y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
+            y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
+            y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
+            y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
           }
-          *reinterpret_cast<uint2*>(static_cast<__half*>(out_hi_v) + o) =
-              *reinterpret_cast<const uint2*>(h);
-          *reinterpret_cast<uint2*>(static_cast<__half*>(out_lo_v) + o) =
-              *reinterpret_cast<const uint2*>(l);
-        } else {
-          const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
-                                        inc_tf32_hi(y.w));
-          const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
-                                        inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
-          *reinterpret_cast<float4*>(static_cast<float*>(out_hi_v) + o) = hi;
-          *reinterpret_cast<float4*>(static_cast<float*>(out_lo_v) + o) = lo;
+        }
+        if (g.emit) {
+          const long long o = (long long)p * m_out + pos * g.C1 + o4 * 4;
+          if (HALF) {  // fp16 pair of y * out_scale (same 11 significant bits as a TF32 number)
+            const float v[4] = {y.x * g.out_scale, y.y * g.out_scale, y.z * g.out_scale,
+                                y.w * g.out_scale};
+            __half h[4], l[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              h[q] = __float2half_rn(v[q]);
+              l[q] = __float2half_rn(v[q] - __half2float(h[q]));
+            }
+            st_cs_u2(static_cast<__half*>(out_hi_v) + o, *reinterpret_cast<const uint2*>(h));
+            st_cs_u2(static_cast<__half*>(out_lo_v) + o, *reinterpret_cast<const uint2*>(l));
+          } else {
+            const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
+                                          inc_tf32_hi(y.w));
+            const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
+                                          inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
+            *reinterpret_cast<float4*>(static_cast<float*>(out_hi_v) + o) = hi;
+            *reinterpret_cast<float4*>(static_cast<float*>(out_lo_v) + o) = lo;
+          }
         }
       }
     }
