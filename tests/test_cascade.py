@@ -1,0 +1,208 @@
+"""Analytic cascade resolution (torchpruner_b200/pruner/cascade.py) against the NaN trick of the
+reference (pruner.py:21-54, 129-185) as restated by the oracle — on CPU, no kernel launched.
+
+For every (module, cascade) of the reference's pruning graphs the analytic answer must equal what
+the probe forward finds: the same ``_activation_len`` and the same ascending int64 positions.
+Where the trace cannot prove the answer it must say so (None) instead of guessing."""
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import tp_oracle as oracle
+from torchpruner_b200 import workloads
+from torchpruner_b200.pruner import cascade
+from torchpruner_b200.utils import get_vgg_pruning_graph
+
+
+def probe(model, module, indices, cascading_modules, input_size, seed=0):
+    """The reference's discovery: poison, forward a random batch of 2, look where NaNs arrive."""
+    found = {}
+
+    def nanify(_, __, output):
+        return output.index_fill_(1, torch.tensor(indices), torch.tensor(np.nan))
+
+    def detect(mod, inp, __):
+        found[id(mod)] = (float(inp[0].shape[1]), oracle.nan_indices(inp[0].detach()))
+
+    handles = [module.register_forward_hook(nanify)]
+    handles += [m.register_forward_hook(detect) for m in cascading_modules]
+    rng = np.random.RandomState(seed)
+    try:
+        with torch.no_grad():
+            model(torch.tensor(rng.random_sample((2,) + tuple(input_size))).float())
+    finally:
+        for h in handles:
+            h.remove()
+    return found
+
+
+def assert_same(analytic, probed):
+    assert analytic is not None
+    assert set(analytic) == set(probed)
+    for key, (length, dead) in probed.items():
+        a_len, a_dead = analytic[key]
+        assert a_len == length and type(a_len) is float
+        assert a_dead.dtype == np.int64
+        np.testing.assert_array_equal(a_dead, dead)
+
+
+def random_units(n, frac, seed):
+    rng = np.random.RandomState(seed)
+    return sorted(rng.choice(n, size=max(1, int(n * frac)), replace=False).tolist())
+
+
+def test_vgg16_graph_matches_nan_trick():
+    model, shape = workloads.build("vgg16_cifar")
+    trace = cascade.trace_chain(model, shape)
+    assert trace is not None and len(trace.calls) == 51
+    graph = get_vgg_pruning_graph(model)
+    assert len(graph) == 15
+    for i, (module, cascading) in enumerate(graph):
+        units = random_units(module.weight.shape[0], 0.25, seed=i)
+        assert_same(cascade.resolve(trace, model, module, units, cascading),
+                    probe(model, module, units, cascading, shape))
+
+
+def test_small_cnn_flatten_expands_channels_to_blocks():
+    model, shape = workloads.build("small_cnn")
+    trace = cascade.trace_chain(model, shape)
+    for i, (module, cascading) in enumerate(model.get_pruning_graph()):
+        units = random_units(module.weight.shape[0], 0.1, seed=10 + i)
+        got = cascade.resolve(trace, model, module, units, cascading)
+        assert_same(got, probe(model, module, units, cascading, shape))
+    conv2, fc1 = model.features[3], model.classifier[0]
+    length, dead = cascade.resolve(trace, model, conv2, [1, 5], [fc1])[id(fc1)]
+    hw = 4096 // 64  # reference test_pruner.py:83-92: channel c -> [c*HW, (c+1)*HW)
+    assert length == 4096.0
+    np.testing.assert_array_equal(dead, np.r_[hw:2 * hw, 5 * hw:6 * hw])
+
+
+def test_mlp_with_flatten_module_and_leaky_relu():
+    model, shape = workloads.build("mlp")
+    trace = cascade.trace_chain(model, shape)
+    fc1, fc2, fc3 = model.fc[1], model.fc[3], model.fc[5]
+    for module, cascading in ((fc1, [fc2]), (fc2, [fc3]), (fc1, [fc3, fc2])):
+        units = random_units(module.weight.shape[0], 0.3, seed=3)
+        assert_same(cascade.resolve(trace, model, module, units, cascading),
+                    probe(model, module, units, cascading, shape))
+
+
+def test_second_consumer_sees_everything_dead():
+    """Behind the first Linear/conv that reads a dead input every unit is NaN in the probe."""
+    model, shape = workloads.build("vgg16_cifar")
+    trace = cascade.trace_chain(model, shape)
+    convs = model.conv_layers()
+    cascading = [convs[1], convs[2], model.features[4], model.features[8]]
+    assert_same(cascade.resolve(trace, model, convs[0], [3], cascading),
+                probe(model, convs[0], [3], cascading, shape))
+    length, dead = cascade.resolve(trace, model, convs[0], [3], cascading)[id(convs[2])]
+    assert dead.size == length == 64.0
+
+
+def test_indices_negative_duplicate_unsorted_and_errors():
+    model, shape = workloads.build("vgg16_cifar")
+    trace = cascade.trace_chain(model, shape)
+    conv, cascading = model.conv_layers()[4], [model.conv_layers()[5], model.features[15]]
+    for units in ([5, 1, 5, -1], np.array([7, 3, 3], dtype=np.int64), torch.tensor([0, 255, -256])):
+        listed = units.tolist() if not isinstance(units, list) else units
+        assert_same(cascade.resolve(trace, model, conv, units, cascading),
+                    probe(model, conv, listed, cascading, shape))
+    with pytest.raises(IndexError):
+        cascade.resolve(trace, model, conv, [256], cascading)
+    with pytest.raises(RuntimeError, match="int64"):
+        cascade.resolve(trace, model, conv, np.array([1, 2], dtype=np.int32), cascading)
+    got = cascade.resolve(trace, model, conv, [2], [])
+    assert got == {}
+
+
+def test_module_before_the_pruned_one_is_reached_but_clean():
+    model, shape = workloads.build("vgg16_cifar")
+    trace = cascade.trace_chain(model, shape)
+    convs = model.conv_layers()
+    cascading = [convs[0], convs[3]]
+    assert_same(cascade.resolve(trace, model, convs[2], [0, 9], cascading),
+                probe(model, convs[2], [0, 9], cascading, shape))
+
+
+class _Residual(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a = nn.Conv2d(3, 8, 3, padding=1)
+        self.r = nn.ReLU()
+        self.b = nn.Conv2d(8, 8, 3, padding=1)
+        self.c = nn.Conv2d(8, 4, 1)
+
+    def forward(self, x):
+        h = self.r(self.a(x))
+        return self.c(self.b(h) + h)
+
+
+class _Hidden(nn.Module):
+    """A functional op between two modules: scaling (new tensor) or an in-place update."""
+
+    def __init__(self, inplace):
+        super().__init__()
+        self.a = nn.Conv2d(3, 8, 3, padding=1)
+        self.b = nn.Conv2d(8, 4, 1)
+        self.inplace = inplace
+
+    def forward(self, x):
+        h = self.a(x)
+        h = h.mul_(2.0) if self.inplace else h * 2.0
+        return self.b(h)
+
+
+class _Twice(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a = nn.Conv2d(3, 8, 3, padding=1)
+        self.r = nn.ReLU()
+        self.b = nn.Conv2d(8, 8, 3, padding=1)
+
+    def forward(self, x):
+        return self.r(self.b(self.r(self.a(x))))
+
+
+def test_unprovable_links_return_none():
+    shape = (3, 8, 8)
+    m = _Residual().eval()
+    trace = cascade.trace_chain(m, shape)
+    assert cascade.resolve(trace, m, m.a, [1], [m.b]) is not None       # a -> relu -> b is a chain
+    assert cascade.resolve(trace, m, m.b, [1], [m.c]) is None           # the add is invisible
+    for inplace in (False, True):
+        m = _Hidden(inplace).eval()
+        assert cascade.resolve(cascade.trace_chain(m, shape), m, m.a, [1], [m.b]) is None
+    m = _Twice().eval()
+    assert cascade.resolve(cascade.trace_chain(m, shape), m, m.a, [1], [m.r, m.b]) is None
+    grouped = nn.Sequential(nn.Conv2d(4, 8, 3, padding=1), nn.Conv2d(8, 8, 3, padding=1, groups=8),
+                            nn.Conv2d(8, 2, 1)).eval()
+    trace = cascade.trace_chain(grouped, (4, 8, 8))
+    assert cascade.resolve(trace, grouped, grouped[0], [1], [grouped[1]]) is not None
+    assert cascade.resolve(trace, grouped, grouped[0], [1], [grouped[1], grouped[2]]) is None
+    soft = nn.Sequential(nn.Linear(6, 5), nn.Softmax(dim=1), nn.Linear(5, 2)).eval()
+    assert cascade.resolve(cascade.trace_chain(soft, (6,)), soft, soft[0], [1], [soft[2]]) is None
+
+
+def test_training_mode_with_side_effects_is_left_to_the_probe():
+    model, shape = workloads.build("vgg16_cifar")
+    trace = cascade.trace_chain(model, shape)
+    conv, cascading = model.conv_layers()[0], [model.conv_layers()[1], model.features[1]]
+    assert cascade.resolve(trace, model, conv, [1], cascading) is not None
+    model.train()
+    assert cascade.resolve(cascade.trace_chain(model, shape), model, conv, [1], cascading) is None
+    assert cascade.structure_signature(model, shape) != trace.signature
+
+
+def test_trace_leaves_the_model_untouched():
+    model, shape = workloads.build("vgg16_cifar")
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    hooks = sum(len(m._forward_hooks) + len(m._forward_pre_hooks) for m in model.modules())
+    state = torch.get_rng_state()
+    np_state = np.random.get_state()[1].copy()
+    cascade.trace_chain(model, shape)
+    assert sum(len(m._forward_hooks) + len(m._forward_pre_hooks) for m in model.modules()) == hooks
+    assert torch.equal(torch.get_rng_state(), state)
+    assert np.array_equal(np.random.get_state()[1], np_state)
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, before[k]), k

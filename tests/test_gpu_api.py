@@ -1,6 +1,7 @@
 """End-to-end parity of the drop-in Python API on a GPU: the reference's own unit tests restated
 against torchpruner_b200 (same fixtures, same expected values), golden vectors produced by the
 unmodified reference on the BASELINE configs, and the CPU oracle run side by side."""
+import copy
 import os
 
 import numpy as np
@@ -352,6 +353,40 @@ def test_prune_model_cascades():
     assert not hasattr(model[2], "_nan_indices")
 
 
+def test_analytic_cascade_falls_back_to_the_probe():
+    """Train-mode BatchNorm (the probe forward moves its running statistics, as in the
+    reference) and links the trace cannot prove are left to the NaN trick."""
+    model = nn.Sequential(nn.Linear(3, 4), nn.BatchNorm1d(4), nn.Linear(4, 1)).to(DEV)
+    twin = copy.deepcopy(model)
+    p, q = Pruner(model, (3,), DEV), Pruner(twin, (3,), DEV, cascade="probe")
+    np.random.seed(5)
+    p.prune_model(model[0], [1], [model[1], model[2]])
+    np.random.seed(5)
+    q.prune_model(twin[0], [1], [twin[1], twin[2]])
+    assert p.last_cascade == q.last_cascade == "probe"
+    for (k, a), b in zip(model.state_dict().items(), twin.state_dict().values()):
+        assert torch.equal(a, b), k
+    model.eval()
+    p.prune_model(model[0], [0], [model[1], model[2]])
+    assert p.last_cascade == "probe"  # the mode changed: the chain is recorded again
+    p.prune_model(model[0], [0], [model[1], model[2]])
+    assert p.last_cascade == "analytic" and list(model[2].weight.shape) == [1, 1]
+
+    class Scaled(nn.Module):  # a functional op between the modules: no hook can see it
+        def __init__(self):
+            super().__init__()
+            self.a, self.b = nn.Linear(3, 4), nn.Linear(4, 2)
+
+        def forward(self, x):
+            return self.b(self.a(x) * 2.0)
+
+    net = Scaled().to(DEV).eval()
+    p = Pruner(net, (3,), DEV)
+    p.prune_model(net.a, [3], [net.b])
+    p.prune_model(net.a, [0], [net.b])
+    assert p.last_cascade == "probe" and list(net.b.weight.shape) == [2, 2]
+
+
 @pytest.mark.parametrize("momentum", [0.0, 0.01])
 def test_training_step_after_pruning(momentum):
     """test_pruner.py:180-228 (the momentum case raises KeyError in the reference on torch>=1.6)."""
@@ -373,21 +408,26 @@ def test_training_step_after_pruning(momentum):
 
 
 # ------------------------------------------------------------------ config 5 / 1: bit-exact cascade
+@pytest.mark.parametrize("mode", ["analytic", "probe"])
 @pytest.mark.parametrize("cfg", ["small_cnn", "vgg16_cifar"])
-def test_cascading_prune_is_bit_exact(cfg, capsys):
+def test_cascading_prune_is_bit_exact(cfg, mode, capsys):
     with open(os.path.join(GOLDEN, "prune.txt")) as f:
         want = [line[len(cfg) + 1:].rstrip("\n") for line in f if line.startswith(cfg + " ")]
     model, shape, opt = cases.prune_setup(cfg, device=DEV)
     cpu_model, _, cpu_opt = cases.prune_setup(cfg, device="cpu")
-    pruner = Pruner(model, shape, DEV, optimizer=opt)
+    pruner = Pruner(model, shape, DEV, optimizer=opt, cascade=mode)
     check = oracle.OraclePruner(cpu_model, shape, optimizer=cpu_opt)
     graph = get_vgg_pruning_graph(model) if cfg == "vgg16_cifar" else model.get_pruning_graph()
     cpu_graph = get_vgg_pruning_graph(cpu_model) if cfg == "vgg16_cifar" else cpu_model.get_pruning_graph()
     # Unit choices and the probe batches both come from the global numpy RNG, interleaved exactly
     # as in the golden run: identical digests therefore also prove identical RNG consumption.
     np.random.seed(21)
+    how = []
     for module, cascade in graph:
         pruner.prune_model(module, cases.prune_choice(module.weight.shape[0]), cascading_modules=cascade)
+        how.append(pruner.last_cascade)
+    # the first probe forward records the chain; every later cascade is resolved without one
+    assert how == ["probe"] + [mode] * (len(graph) - 1)
     rng_after_product = np.random.get_state()[1][:8].copy()
     np.random.seed(21)
     for module, cascade in cpu_graph:

@@ -1,0 +1,242 @@
+"""Analytic cascade resolution: which inputs of each cascading module die when output units of a
+module are removed — without the probe forward of the NaN trick.
+
+The reference answers that question empirically (pruner.py:21-54, 129-185): it overwrites the
+units with NaN in a forward hook, runs a random 2-example batch through the whole model and has
+every cascading module report the dim-1 positions of its input that arrive as NaN — one model
+forward and one device->host synchronisation per cascading module for every ``prune_model``.
+
+For the topologies the reference targets the answer is a matter of bookkeeping:
+
+  * modules that act per channel (BatchNorm, activations, pooling, Dropout, Identity) hand the
+    dead positions on unchanged;
+  * flattening ``[B, C, *S]`` to ``[B, C*prod(S)]`` turns dead channel ``c`` into the contiguous
+    block ``[c*prod(S), (c+1)*prod(S))`` (the mapping the reference tests in
+    test_pruner.py:83-92);
+  * a Linear / ungrouped convolution mixes every input into every output, so behind the first
+    one that sees a dead input everything is dead.
+
+What must be *known* for this to be exact is the order in which the leaf modules run, that each
+one consumes exactly what the previous one produced (no functional op, residual add or in-place
+update hidden between them) and the spatial size at the flatten.  That is established once per
+model structure by a ``Recorder`` riding on the FIRST probe forward the pruner runs anyway: it
+notes every leaf call with the identity and version counter of its input and output.  From the
+second ``prune_model`` on, ``resolve`` walks that record instead of running the model — no
+forward, no kernel launch, no synchronisation; whenever it meets
+something it cannot prove (an unknown module type, a broken link, a version bump between two
+modules, grouped convolutions, a module in training mode that has side effects) it returns
+``None`` and the caller falls back to the NaN trick.  The results are asserted equal to the
+NaN trick's in tests/test_cascade.py (CPU, against the oracle) and tests/test_gpu_api.py.
+"""
+import numpy as np
+import torch
+import torch.nn as nn
+from torch.nn.modules.batchnorm import _BatchNorm
+from torch.nn.modules.conv import _ConvNd
+from torch.nn.modules.dropout import _DropoutNd
+
+# element-wise activations: NaN in, NaN out, nothing crosses channels
+_ELEMENTWISE = (nn.ReLU, nn.ReLU6, nn.LeakyReLU, nn.ELU, nn.SELU, nn.CELU, nn.GELU, nn.SiLU,
+                nn.Mish, nn.Sigmoid, nn.Tanh, nn.Hardtanh, nn.Hardswish, nn.Hardsigmoid,
+                nn.Softplus, nn.PReLU, nn.Identity)
+_POOLING = (nn.MaxPool1d, nn.MaxPool2d, nn.MaxPool3d, nn.AvgPool1d, nn.AvgPool2d, nn.AvgPool3d,
+            nn.AdaptiveAvgPool1d, nn.AdaptiveAvgPool2d, nn.AdaptiveAvgPool3d,
+            nn.AdaptiveMaxPool1d, nn.AdaptiveMaxPool2d, nn.AdaptiveMaxPool3d)
+
+
+class _Call:
+    __slots__ = ("module", "inp", "in_shape", "in_version", "out", "out_shape", "out_version")
+
+
+def _link(a, b):
+    """How call ``b`` receives the output of call ``a``: 'same', 'flatten' or None (unproven)."""
+    if a.out is None or b.inp is None:
+        return None
+    if b.inp is a.out:
+        return "same" if b.in_version == a.out_version else None
+    base = getattr(b.inp, "_base", None)
+    if base is None or not (base is a.out or base is getattr(a.out, "_base", None)):
+        return None
+    if b.in_version != a.out_version:
+        return None
+    if len(a.out_shape) > 2 and len(b.in_shape) == 2 and a.out_shape[0] == b.in_shape[0] \
+            and int(np.prod(a.out_shape[1:])) == b.in_shape[1]:
+        return "flatten"
+    return "same" if tuple(a.out_shape) == tuple(b.in_shape) else None
+
+
+class ChainTrace:
+    """Leaf-module calls of one forward, in order, with what links them.  Only modules, shapes
+    and link kinds are kept; the activations seen while recording are released."""
+
+    def __init__(self, calls, signature):
+        self.signature = signature
+        self.links = [_link(calls[i], calls[i + 1]) for i in range(len(calls) - 1)]
+        self.calls = calls
+        for c in calls:
+            c.inp = c.out = None
+        self.position = {}
+        for i, c in enumerate(calls):
+            # a module called twice has no single position: poison it
+            self.position[id(c.module)] = i if id(c.module) not in self.position else -1
+
+    def link(self, i):
+        return self.links[i]
+
+
+def structure_signature(model, input_size):
+    """Everything the trace depends on that pruning channels does not change."""
+    sig = [tuple(input_size)]
+    for m in model.modules():
+        if next(m.children(), None) is not None:
+            continue
+        sig.append((id(m), type(m).__name__, bool(m.training)))
+    return tuple(sig)
+
+
+class Recorder:
+    """Forward pre-/post-hooks on every leaf module that note the identity, shape and version
+    counter of what goes in and what comes out.  The product installs it around the probe
+    forward of the first ``prune_model`` (after the poisoning hook, so the output it sees is
+    the one the next module receives); every later call on the same structure is bookkeeping."""
+
+    def __init__(self, model):
+        self.model = model
+        self.calls, self._open, self._handles = [], {}, []
+
+    def _pre(self, module, inputs):
+        c = _Call()
+        c.module = module
+        x = inputs[0] if inputs else None
+        if isinstance(x, torch.Tensor):
+            c.inp, c.in_shape, c.in_version = x, tuple(x.shape), x._version
+        else:
+            c.inp, c.in_shape, c.in_version = None, (), -1
+        self._open.setdefault(id(module), []).append(c)
+
+    def _post(self, module, inputs, output):
+        c = self._open[id(module)].pop()
+        if isinstance(output, torch.Tensor):
+            c.out, c.out_shape, c.out_version = output, tuple(output.shape), output._version
+        else:
+            c.out, c.out_shape, c.out_version = None, (), -1
+        self.calls.append(c)
+
+    def __enter__(self):
+        for m in self.model.modules():
+            if next(m.children(), None) is None:
+                self._handles.append(m.register_forward_pre_hook(self._pre))
+                self._handles.append(m.register_forward_hook(self._post))
+        return self
+
+    def __exit__(self, *exc):
+        for h in self._handles:
+            h.remove()
+        self._handles = []
+        return False
+
+    def trace(self, input_size):
+        return ChainTrace(self.calls, structure_signature(self.model, input_size))
+
+
+def trace_chain(model, input_size):
+    """Record one forward of a zero batch of 2 (what the tests use; the product records its own
+    probe forward instead).  Refused (None) when the forward would have side effects."""
+    if _has_side_effects_in_training(model):
+        return None
+    param = next(model.parameters(), None)
+    device = param.device if param is not None else torch.device("cpu")
+    with Recorder(model) as rec, torch.no_grad():
+        model(torch.zeros((2,) + tuple(input_size), dtype=torch.float32, device=device))
+    return rec.trace(input_size)
+
+
+def normalise_indices(indices, n_units):
+    """The units ``index_fill_`` would poison: int64 required, negatives wrap, duplicates and
+    order irrelevant (pruner.py:136-141)."""
+    idx = torch.as_tensor(indices) if not isinstance(indices, torch.Tensor) else indices.detach().cpu()
+    if idx.dtype != torch.int64:
+        raise RuntimeError(f"index_fill_(): Expected dtype int64 for index, got {idx.dtype}")
+    idx = idx.reshape(-1).numpy()
+    if idx.size and (idx.min() < -n_units or idx.max() >= n_units):
+        raise IndexError(f"index out of range in self (dimension of size {n_units})")
+    return np.unique(idx % n_units) if n_units else idx
+
+
+def _has_side_effects_in_training(model):
+    for m in model.modules():
+        if m.training and isinstance(m, (_BatchNorm, _DropoutNd)):
+            return True
+    return False
+
+
+def resolve(trace, model, module, indices, cascading_modules):
+    """Dead input positions of every cascading module, as the NaN trick would report them.
+
+    Returns ``{id(cascading module): (activation_len, sorted int64 ndarray)}`` — modules that the
+    forward reaches get an entry even when nothing dies in them (the reference sets
+    ``_activation_len`` on every hooked module it reaches) — or None when the answer cannot be
+    proven from the trace.
+    """
+    if trace is None or _has_side_effects_in_training(model):
+        # train-mode BatchNorm / Dropout: the reference's probe forward moves running statistics
+        # and draws from the torch RNG; only the real forward reproduces that
+        return None
+    start = trace.position.get(id(module), None)
+    if start is None or start < 0:
+        return None
+    wanted = {}
+    for m in cascading_modules:
+        pos = trace.position.get(id(m), None)
+        if pos is None:
+            continue  # never called: the reference's hook never fires either
+        if pos < 0:
+            return None
+        wanted[pos] = m
+    first = trace.calls[start]
+    if len(first.out_shape) < 2:
+        return None
+    n_units = first.out_shape[1]
+    dead = normalise_indices(indices, n_units)
+    result = {}
+    for pos, m in wanted.items():
+        if pos <= start:  # runs before the poisoned module: reached, nothing dead
+            result[id(m)] = (float(trace.calls[pos].in_shape[1]), np.zeros(0, np.int64))
+    last = max(wanted) if wanted else start
+    width = n_units
+    for i in range(start, last):
+        link = trace.link(i)
+        if link is None:
+            return None
+        nxt = trace.calls[i + 1]
+        if link == "flatten":
+            k = int(np.prod(trace.calls[i].out_shape[2:]))
+            dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
+            width *= k
+        if len(nxt.in_shape) < 2 or nxt.in_shape[1] != width:
+            return None
+        m = nxt.module
+        if (i + 1) in wanted:
+            result[id(m)] = (float(width), dead.astype(np.int64))
+        if i + 1 == last:
+            break
+        # what the module hands on
+        if isinstance(m, (nn.Linear, _ConvNd)):
+            if isinstance(m, _ConvNd) and m.groups != 1:
+                return None
+            if len(nxt.out_shape) < 2:
+                return None
+            width = nxt.out_shape[1]
+            dead = np.arange(width, dtype=np.int64) if dead.size else dead
+        elif isinstance(m, nn.Flatten):
+            if m.start_dim != 1 or m.end_dim not in (-1, len(nxt.in_shape) - 1):
+                return None
+            k = int(np.prod(nxt.in_shape[2:])) if len(nxt.in_shape) > 2 else 1
+            dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
+            width *= k
+        elif isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
+            if len(nxt.out_shape) < 2 or nxt.out_shape[1] != width:
+                return None
+        else:
+            return None
+    return result

@@ -7,6 +7,7 @@ momentum — one launch and one host->device index copy each) is recorded in a p
 a whole, and executed by ONE ``tp_multi_gather`` launch fed by ONE index upload.
 """
 import contextlib
+import os
 
 import numpy as np
 import torch
@@ -16,6 +17,7 @@ from torch.nn.modules.conv import _ConvNd
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import _lib
+from . import cascade as _cascade
 from .opt_pruner import OptimizerPruner, optimizer_state_tensors, sgd_momentum_buffer  # noqa: F401
 
 SUPPORTED_IN_PRUNING_MODULES = [nn.Linear, _ConvNd, nn.Dropout, _BatchNorm]
@@ -117,12 +119,21 @@ def _resolve_detections():
 
 
 class Pruner:
-    def __init__(self, model, input_size, device, optimizer=None):
+    def __init__(self, model, input_size, device, optimizer=None, cascade=None):
+        """Reference signature (pruner.py:15-19) plus ``cascade``: "analytic" records the module
+        chain during the first probe forward and resolves every later cascade from that record
+        whenever it is provably what the NaN trick would find (probe forward otherwise);
+        "probe" always runs the reference's probe forward.  Default: $TORCHPRUNER_B200_CASCADE,
+        else "analytic"."""
         self.model = model
         self.device = device
         self.input_size = input_size
         self.optimizer = optimizer
         self._plan = None
+        self.cascade = cascade or os.environ.get("TORCHPRUNER_B200_CASCADE", "analytic")
+        assert self.cascade in ("analytic", "probe"), "cascade should be 'analytic' or 'probe'"
+        self._trace = None
+        self.last_cascade = None  # "analytic" / "probe": how the last prune_model resolved it
 
     @contextlib.contextmanager
     def _batched(self):
@@ -142,18 +153,27 @@ class Pruner:
         on them (pruner.py:21-57).  Which input positions of each cascading module die is found
         with the reference's NaN trick: poison the units, run a 2-example probe forward, see
         where the NaNs arrive."""
-        module_handle = module.register_forward_hook(self._nanify_hook(indices))
         if cascading_modules is None:
             print("Warning: no cascading modules defined")
             cascading_modules = []
-        handles = [m.register_forward_hook(self._detect_nan_hook()) for m in cascading_modules]
-        try:
-            self._run_forward()
-        finally:
-            module_handle.remove()
-            for handle in handles:
-                handle.remove()
-            _PENDING_DETECTIONS.clear()
+        if not self._resolve_analytically(module, indices, cascading_modules):
+            self.last_cascade = "probe"
+            module_handle = module.register_forward_hook(self._nanify_hook(indices))
+            handles = [m.register_forward_hook(self._detect_nan_hook()) for m in cascading_modules]
+            # the first probe forward doubles as the structure trace later calls resolve from
+            recorder = contextlib.nullcontext()
+            if self.cascade == "analytic" and self._trace is None:
+                recorder = _cascade.Recorder(self.model)
+            try:
+                with recorder as rec:
+                    self._run_forward()
+                if rec is not None:
+                    self._trace = rec.trace(self.input_size)
+            finally:
+                module_handle.remove()
+                for handle in handles:
+                    handle.remove()
+                _PENDING_DETECTIONS.clear()
 
         with self._batched():
             for next_module in cascading_modules:
@@ -163,6 +183,31 @@ class Pruner:
                                       original_len=getattr(next_module, "_activation_len"))
                     delattr(next_module, "_nan_indices")
             self.prune_module(module, indices, direction="out")
+
+    def _resolve_analytically(self, module, indices, cascading_modules):
+        """Leave on the cascading modules what the probe forward would (``_activation_len``,
+        ``_nan_indices``) without running it; False when that cannot be proven (cascade.py)."""
+        if self.cascade != "analytic":
+            return False
+        if self._trace is not None and self._trace.signature != \
+                _cascade.structure_signature(self.model, self.input_size):
+            self._trace = None  # modules were replaced or changed mode: record again
+        if self._trace is None:
+            return False
+        found = _cascade.resolve(self._trace, self.model, module, indices, cascading_modules)
+        if found is None:
+            return False
+        # the probe's random batch comes from the global numpy RNG (pruner.py:178): consume the
+        # same numbers so whatever the caller draws next is what it would have drawn
+        np.random.random((2,) + tuple(self.input_size))
+        for m in cascading_modules:
+            if id(m) in found:
+                length, dead = found[id(m)]
+                setattr(m, "_activation_len", length)
+                if dead.size:
+                    setattr(m, "_nan_indices", dead)
+        self.last_cascade = "analytic"
+        return True
 
     def prune_module(self, module, indices, direction="out", original_len=None):
         """Slice the parameters of one module, knowing which ones its class has
