@@ -349,7 +349,16 @@ def run_product(args, rank, world, local_rank):
             executed = 3.0 * dom["flops"] / dom["ms"] / 1e9 if dom["ms"] > 0 else 0.0
             roofline = {
                 "kernel": dominant, "bound": "tensor", "achieved": executed, "peak": peak,
-                "unit": "TFLOP/s", "frac": executed / peak, "traffic": None,
+                "unit": "TFLOP/s", "frac": executed / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set
+                # full capture under profiles/ (not measured in this run)
+                "traffic": 1.0550e9 if half else 1.0998e9,
+                "traffic_note": "bytes per launch of the 4x4x512->512 layer (the step's largest "
+                                "share) at its Shapley stack size, "
+                                + ("N=16384: algorithmic 1.0737e9 (fp16 hi+lo in, hi+lo out); "
+                                   "profiles/r01_ncu_conv_f16x3_summary.txt" if half else
+                                   "N=8192: algorithmic 1.0737e9 (TF32 hi+lo in fp32 containers); "
+                                   "profiles/r01_ncu_conv_tf32x3_persistent_summary.txt"),
                 "peak_source": bf16[1] + (" bf16 sustained (fp16 and bf16 MMAs run at the same rate)"
                                          if half else
                                          " bf16 sustained / 2 (TF32 dense runs at half the bf16 rate)"),

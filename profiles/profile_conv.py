@@ -1,6 +1,9 @@
-"""Per-layer throughput of tp_conv_tf32x3 on the VGG16-CIFAR tail shapes at Shapley batch sizes.
+"""Per-layer throughput of tp_conv_f16x3 / tp_conv_tf32x3 on the VGG16-CIFAR tail shapes at
+Shapley batch sizes.
 
-    python profiles/profile_conv.py [ncu]
+    python profiles/profile_conv.py [ncu] [tf32]
+
+(fp16x3 flavour unless `tf32` is given.)
 
 Without arguments: CUDA-event timing of every layer shape for both kernel variants and several
 partial-sum intervals.  With `ncu`: launches two representative shapes a few times (to be wrapped
@@ -27,21 +30,39 @@ def images_for(H, W, C):
     return int(min(512 * 256, max(256, (512 << 20) // per_image // 256 * 256)))
 
 
+F16 = "tf32" not in sys.argv
+
+
+def images_for_f16(H, W, C):
+    per_image = H * W * C * 4
+    return int(min(512 * 256, max(256, (512 << 20) // per_image // 256 * 256)))
+
+
 def run(H, W, Cin, Cout, taps, N, iters=5):
     x = torch.randn((N, H, W, Cin), device=DEV)
     w = torch.randn((Cout, taps * Cin), device=DEV) / (taps * Cin) ** 0.5
-    x_hi, x_lo = _lib.tf32_split(x)
-    w_hi, w_lo = _lib.tf32_split(w)
-    scale = torch.ones(Cout, device=DEV)
-    shift = torch.zeros(Cout, device=DEV)
     split = Cout != 10
-    out = (torch.empty((N, H, W, Cout), device=DEV), torch.empty((N, H, W, Cout), device=DEV) if split else None)
+    if F16:
+        x_hi, x_lo = _lib.f16_split(x, 8.0)
+        w_hi, w_lo = _lib.f16_split(w, 64.0)
+        scale = torch.full((Cout,), 1.0 / 512.0, device=DEV)
+        odt = torch.float16 if split else torch.float32
+    else:
+        x_hi, x_lo = _lib.tf32_split(x)
+        w_hi, w_lo = _lib.tf32_split(w)
+        scale = torch.ones(Cout, device=DEV)
+        odt = torch.float32
+    del x, w
+    shift = torch.zeros(Cout, device=DEV)
+    out = (torch.empty((N, H, W, Cout), device=DEV, dtype=odt),
+           torch.empty((N, H, W, Cout), device=DEV, dtype=odt) if split else None)
     stream = torch.cuda.current_stream(DEV)
     ms = []
     for i in range(iters + 2):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, True, split=split, out=out)
+        _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, True, split=split, out=out,
+                         out_scale=8.0 if F16 else 1.0)
         b.record(stream)
         b.synchronize()
         if i >= 2:
@@ -54,19 +75,19 @@ def run(H, W, Cin, Cout, taps, N, iters=5):
 def main():
     if "ncu" in sys.argv:
         for shp in (LAYERS[0], LAYERS[6]):
-            run(*shp, images_for(*shp[:3]), iters=1)
+            run(*shp, (images_for_f16 if F16 else images_for)(*shp[:3]), iters=1)
         return
     print("variant promote  H  W  Cin Cout taps      N     ms  useful_TF/s  executed_TF/s")
     print("# (variant 2 = persistent kernel with position-major tiles disabled; FLOPs are the")
     print("#  nominal 2*pixels*Cout*9*Cin, so skipped padding taps show up as > peak)")
-    for variant in (0, 2, 1):
+    for variant in ((0, 2) if F16 else (0, 2, 1)):
         for promote in ((2,) if variant == 2 else (1, 2, 4)):
             _lib.set_tuning("conv_variant", 1 if variant == 1 else 0)
             _lib.set_tuning("conv_pos_major", 1 if variant == 2 else 0)
             _lib.set_tuning("conv_promote", promote)
             tot_ms = tot_fl = 0.0
             for (H, W, Cin, Cout, taps) in LAYERS:
-                N = images_for(H, W, Cin)
+                N = (images_for_f16 if F16 else images_for)(H, W, Cin)
                 ms, tf = run(H, W, Cin, Cout, taps, N)
                 tot_ms += ms
                 tot_fl += tf * ms
