@@ -200,6 +200,18 @@ int tp_conv_f16x3(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int6
                   const void* w_hi, const void* w_lo, int taps, int64_t Cout, const float* scale,
                   const float* shift, int act, float leaky_slope, float out_scale, void* y_hi,
                   void* y_lo, tp_stream_t stream);
+/* The same 3x3 layer with the MaxPool2d(2) that follows it (cifar10.py:62-77: every VGG block ends
+ * conv-BN-ReLU-MaxPool) fused into the epilogue: y_* are [N, H/2, W/2, Cout] fp16 pairs.  Tiles
+ * are position-major (one output pixel x 128 images); the four pixels of a window are computed
+ * back to back by the same CTA and their running maximum stays in TMEM, so the full-resolution
+ * output never reaches HBM.  Only where tp_conv_pool2_fusable() says 1 (3x3, H*W <= 64, even H
+ * and W, N >= 128, Cin % 64 == 0, Cout % 64 == 0); TP_ERR_LIMIT otherwise — the caller then runs
+ * tp_conv_f16x3 + tp_maxpool2_split_nhwc_f16. */
+int tp_conv_f16x3_pool2(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W,
+                        int64_t Cin, const void* w_hi, const void* w_lo, int64_t Cout,
+                        const float* scale, const float* shift, int act, float leaky_slope,
+                        float out_scale, void* y_hi, void* y_lo, tp_stream_t stream);
+int tp_conv_pool2_fusable(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout);
 int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_stream_t stream);
 int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
                            int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,

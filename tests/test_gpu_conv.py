@@ -335,3 +335,51 @@ def test_conv_f16x3_matches_float64(N, H, W, Cin, Cout, taps, relu):
     err = float((y - want).abs().max())
     print(f"fp16x3 K={taps * Cin} max abs err {err:.3e} (scale {scale_ref:.3f})")
     assert err <= 1e-6 * scale_ref, (err, scale_ref)
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout,relu", [
+    (256, 8, 8, 128, 256, True),
+    (384, 4, 4, 256, 512, True),
+    (200, 4, 4, 64, 128, ("leaky", 0.2)),   # image block cut by the end of the stack
+    (128, 2, 2, 64, 64, True),               # BLOCK_N = 64, one window per image
+    (1300, 8, 8, 64, 192, False),            # more tiles than SMs; negative outputs under the max
+])
+def test_conv_f16x3_fused_pool_is_bit_identical(N, H, W, Cin, Cout, relu):
+    """tp_conv_f16x3_pool2 (window maximum kept in TMEM) against tp_conv_f16x3 followed by
+    tp_maxpool2_split_nhwc_f16: the same partial sums, the same rounding, so the same bits."""
+    assert _lib.conv_pool2_fusable(N, H, W, Cin, Cout)
+    gen = torch.Generator(device=DEV).manual_seed(N + 7 * Cin)
+    x = torch.randn((N, H, W, Cin), device=DEV, generator=gen) * 2.0
+    w = torch.randn((Cout, 9 * Cin), device=DEV, generator=gen) / (9 * Cin) ** 0.5
+    scale = torch.rand(Cout, device=DEV, generator=gen) + 0.5
+    scale[::3] *= -1.0                        # BatchNorm weights may be negative
+    shift = torch.randn(Cout, device=DEV, generator=gen) * 0.3
+    s_x = 2.0 ** round(np.log2(64.0 / float(x.abs().max())))
+    s_w = 2.0 ** round(np.log2(64.0 / float(w.abs().max())))
+    x_hi, x_lo = _lib.f16_split(x, s_x)
+    w_hi, w_lo = _lib.f16_split(w, s_w)
+    sc = (scale / (s_x * s_w)).contiguous()
+    out_scale = 4.0
+    raw, none = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, 9, sc, shift, relu, split=False)
+    assert none is None and raw.dtype == torch.float32
+    want_hi, want_lo = _lib.maxpool2_split_nhwc(raw, half=True, scale=out_scale)
+    got_hi, got_lo = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, 9, sc, shift, relu, split=True,
+                                      out_scale=out_scale, pool=True)
+    assert got_hi.shape == (N, H // 2, W // 2, Cout) and got_hi.dtype == torch.float16
+    assert torch.equal(got_hi, want_hi) and torch.equal(got_lo, want_lo)
+    # and against the float64 reference of conv -> affine -> activation -> max pool
+    ref = _ref64(x, w, 9, scale, shift, relu).view(N, H // 2, 2, W // 2, 2, Cout).amax(dim=(2, 4))
+    y = (got_hi.double() + got_lo.double()) / out_scale
+    assert float((y - ref).abs().max()) <= 1e-6 * float(ref.abs().max())
+
+
+def test_conv_pool2_fusable_limits():
+    assert not _lib.conv_pool2_fusable(64, 4, 4, 64, 64)      # fewer than 128 images
+    assert not _lib.conv_pool2_fusable(256, 16, 16, 64, 64)   # row-major tiles
+    assert not _lib.conv_pool2_fusable(256, 4, 4, 32, 64)     # Cin % 64
+    assert not _lib.conv_pool2_fusable(256, 4, 4, 64, 96)     # Cout % 64
+    x = torch.zeros((256, 16, 16, 64), device=DEV, dtype=torch.float16)
+    w = torch.zeros((64, 576), device=DEV, dtype=torch.float16)
+    one = torch.ones(64, device=DEV)
+    with pytest.raises(_lib.TorchPrunerB200Error, match="position-major"):
+        _lib.conv_tf32x3(x, x, w, w, 9, one, one, True, split=True, pool=True)

@@ -66,6 +66,10 @@ _SIGNATURES = {
     "tp_conv_f16x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
                                      _vp, _vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, _vp, _vp,
                                      _vp]),
+    "tp_conv_f16x3_pool2": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, _i64,
+                                           _vp, _vp, ctypes.c_int, ctypes.c_float, ctypes.c_float,
+                                           _vp, _vp, _vp]),
+    "tp_conv_pool2_fusable": (ctypes.c_int, [_i64, _i64, _i64, _i64, _i64]),
     "tp_f16_split": (ctypes.c_int, [_vp, _i64, ctypes.c_float, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
                                               ctypes.c_int, ctypes.c_float, _vp, _vp, _vp]),
@@ -394,11 +398,20 @@ def f16_split(x, scale):
     return hi, lo
 
 
+def conv_pool2_fusable(N, H, W, Cin, Cout):
+    """True where tp_conv_f16x3_pool2 can run the 3x3 layer and the 2x2 max pool as one kernel."""
+    return bool(load().tp_conv_pool2_fusable(int(N), int(H), int(W), int(Cin), int(Cout)))
+
+
 def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, out=None,
-                out_scale=1.0):
+                out_scale=1.0, pool=False):
     """y = act(conv(x, w) * scale + shift) on tcgen05 with 3xTF32 products.  x_*: NHWC
-    [N,H,W,Cin]; w_*: [Cout, taps*Cin].  Returns (y_hi, y_lo) or (y, None) when split=False."""
+    [N,H,W,Cin]; w_*: [Cout, taps*Cin].  Returns (y_hi, y_lo) or (y, None) when split=False.
+    pool=True (fp16 flavour, where conv_pool2_fusable): MaxPool2d(2) fused, outputs
+    [N,H/2,W/2,Cout]."""
     half = x_hi.dtype == torch.float16   # fp16x3 flavour: operands are fp16 pairs
+    if pool and not (half and split and taps == 9):
+        raise TorchPrunerB200Error("conv: fused pooling needs the fp16 flavour, 3x3 and split outputs")
     if half:
         x_hi, x_lo = _cuda_half(x_hi, "x_hi"), _cuda_half(x_lo, "x_lo")
         if w_hi.dtype != torch.float16 or w_lo.dtype != torch.float16:
@@ -411,19 +424,28 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
         raise TorchPrunerB200Error("conv_tf32x3: operand shapes do not match")
     if out is None:
         odt = torch.float16 if (half and split) else torch.float32
-        y_hi = torch.empty((N, H, W, Cout), dtype=odt, device=x_hi.device)
+        oshape = (N, H // 2, W // 2, Cout) if pool else (N, H, W, Cout)
+        y_hi = torch.empty(oshape, dtype=odt, device=x_hi.device)
         y_lo = torch.empty_like(y_hi) if split else None
     else:
         y_hi, y_lo = out
+        if pool and (y_hi.numel() != N * (H // 2) * (W // 2) * Cout or y_lo is None
+                     or y_lo.numel() != y_hi.numel()):
+            raise TorchPrunerB200Error("conv: pooled outputs must be [N, H/2, W/2, Cout] pairs")
     flops = load().tp_conv_tf32x3_flops(N, H, W, Cin, Cout, int(taps)) if _profile is not None else 0
     esz = 2 if half else 4
     nbytes = esz * (2 * x_hi.numel() + 2 * w_hi.numel()) + \
         y_hi.element_size() * (2 if split else 1) * y_hi.numel()
     name = "conv_f16x3" if half else "conv_tf32x3"
     if _profile is not None and getattr(_profile, "by_shape", False):
-        name = f"{name}[{H}x{W} {Cin}->{Cout} t{taps}]"
+        name = f"{name}[{H}x{W} {Cin}->{Cout} t{taps}{' pool' if pool else ''}]"
     with torch.cuda.device(x_hi.device), _launch(name, nbytes, x_hi, 1, flops):
-        if half:
+        if pool:
+            _check(load().tp_conv_f16x3_pool2(
+                x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
+                Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu), float(out_scale),
+                y_hi.data_ptr(), y_lo.data_ptr(), _stream(x_hi)), "tp_conv_f16x3_pool2")
+        elif half:
             _check(load().tp_conv_f16x3(
                 x_hi.data_ptr(), x_lo.data_ptr(), N, H, W, Cin, w_hi.data_ptr(), w_lo.data_ptr(),
                 int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu),

@@ -28,6 +28,7 @@ import math
 import os
 
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+FUSE_POOL = os.environ.get("TORCHPRUNER_B200_FUSE_POOL", "1") != "0"
 F16_TARGET = 64.0    # per-tensor power-of-two scaling brings max|x| to ~64 (fp16 max is 65504)
 
 
@@ -421,6 +422,14 @@ class NativeTail:
                 x_lo = x_lo.reshape(n, 1, 1, -1)
             split = not (idx == last or s["pool"])
             next_scale = steps[idx + 1]["s_in"] if (f16 and idx < last) else 1.0
+            if f16 and s["pool"] and s["taps"] == 9 and s["out_view"] is None and idx < last \
+                    and FUSE_POOL and _lib.conv_pool2_fusable(n, x_hi.shape[1], x_hi.shape[2],
+                                                              x_hi.shape[3], s["w16_hi"].shape[0]):
+                # conv + BN + ReLU + MaxPool2d(2) as one kernel (window maximum kept in TMEM)
+                x_hi, x_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w16_hi"], s["w16_lo"], 9, s["scale16"],
+                                              s["shift"], s["relu"], split=True,
+                                              out_scale=next_scale, pool=True)
+                continue
             if f16:
                 y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w16_hi"], s["w16_lo"], s["taps"],
                                               s["scale16"], s["shift"], s["relu"], split=split,

@@ -52,6 +52,9 @@ struct ConvGeom {
   float out_scale;  // fp16 split outputs hold y * out_scale (a power of two)
   int split;     // 1: y_hi/y_lo get the TF32 split of the result; 0: y_hi gets the raw fp32
   int promote;   // k-blocks accumulated in TMEM before the partial sum is folded into registers
+  int pool;      // persistent kernel, position-major fp16 split outputs: MaxPool2d(2) fused into
+                 // the epilogue (tiles_h x tiles_w is then the POOLED grid; every tile index
+                 // stands for the four output pixels of one window, computed back to back)
   long long m_total;
 };
 
@@ -178,6 +181,23 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// 32 consecutive fp32 columns of this thread's TMEM lane <- registers (the running maximum of a
+// pooling window lives in TMEM between the four tiles that make it up)
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const float* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, "
+      "%21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]),
+      "f"(v[8]), "f"(v[9]), "f"(v[10]), "f"(v[11]), "f"(v[12]), "f"(v[13]), "f"(v[14]), "f"(v[15]),
+      "f"(v[16]), "f"(v[17]), "f"(v[18]), "f"(v[19]), "f"(v[20]), "f"(v[21]), "f"(v[22]),
+      "f"(v[23]), "f"(v[24]), "f"(v[25]), "f"(v[26]), "f"(v[27]), "f"(v[28]), "f"(v[29]),
+      "f"(v[30]), "f"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -515,6 +535,10 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = m_tiles * n_tiles;
+  // fused pooling: four output pixels per tile index, and the last accumulator's TMEM columns
+  // hold the running maximum instead of a partial sum
+  const int subs = g.pool ? 4 : 1;
+  const int num_acc = g.pool ? Cfg::kNumAcc - 1 : Cfg::kNumAcc;
 
   if (warp == 0 && lane == 0) {
     prefetch_tensormap(&tm_a_hi);
@@ -548,26 +572,30 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
-        int n0, h0, w0;
-        tile_origin(g, mt, n0, h0, w0);
-        for (int tap = 0; tap < g.taps; ++tap) {
-          const int r = (g.taps == 9) ? tap / 3 : 1;
-          const int s = (g.taps == 9) ? tap - r * 3 : 1;
-          if (g.taps == 9 && !tap_meets_image(g, h0, w0, r, s)) continue;
-          for (int cb = 0; cb < kc; ++cb) {
-            const int kb = tap * kc + cb;  // k-block of the weight matrix
-            mbar_wait(&empty[stage], phase ^ 1u);
-            mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-            uint8_t* st = smem + stage * Cfg::kStageBytes;
-            tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
-            tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
-                        &full[stage]);
-            tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N, &full[stage]);
-            tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
-                        nt * BLOCK_N, &full[stage]);
-            if (++stage == Cfg::kStages) {
-              stage = 0;
-              phase ^= 1u;
+        int n0, hb, wb;
+        tile_origin(g, mt, n0, hb, wb);
+        for (int sub = 0; sub < subs; ++sub) {
+          const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
+          const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+          for (int tap = 0; tap < g.taps; ++tap) {
+            const int r = (g.taps == 9) ? tap / 3 : 1;
+            const int s = (g.taps == 9) ? tap - r * 3 : 1;
+            if (g.taps == 9 && !tap_meets_image(g, h0, w0, r, s)) continue;
+            for (int cb = 0; cb < kc; ++cb) {
+              const int kb = tap * kc + cb;  // k-block of the weight matrix
+              mbar_wait(&empty[stage], phase ^ 1u);
+              mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+              uint8_t* st = smem + stage * Cfg::kStageBytes;
+              tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
+              tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
+                          &full[stage]);
+              tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N, &full[stage]);
+              tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
+                          nt * BLOCK_N, &full[stage]);
+              if (++stage == Cfg::kStages) {
+                stage = 0;
+                phase ^= 1u;
+              }
             }
           }
         }
@@ -582,8 +610,11 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       int buf = 0;
       uint32_t acc_phase = 0;  // flips every time buf wraps
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        int n0, h0, w0;
-        tile_origin(g, tile / n_tiles, n0, h0, w0);
+        int n0, hb, wb;
+        tile_origin(g, tile / n_tiles, n0, hb, wb);
+       for (int sub = 0; sub < subs; ++sub) {
+        const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
+        const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
         const int nk = count_kblocks(g, h0, w0);
         int in_chunk = 0;
         for (int kb = 0; kb < nk; ++kb) {
@@ -614,12 +645,13 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           if (++in_chunk == g.promote || kb == nk - 1) {
             umma_commit(&acc_full[buf]);
             in_chunk = 0;
-            if (++buf == Cfg::kNumAcc) {
+            if (++buf == num_acc) {
               buf = 0;
               acc_phase ^= 1u;
             }
           }
         }
+       }
       }
     }
     __syncwarp();
@@ -634,15 +666,20 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     uint32_t stores = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
-      int n0, h0, w0;
-      tile_origin(g, mt, n0, h0, w0);
+      int n0, hb, wb;
+      tile_origin(g, mt, n0, hb, wb);
+     for (int sub = 0; sub < subs; ++sub) {
+      const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
+      const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
       const int nk = count_kblocks(g, h0, w0);
       const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
       // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
-      for (int j = et; j < BLOCK_N; j += 128) {
-        const int col = nt * BLOCK_N + j;
-        s_scale[j] = col < g.Cout ? scale[col] : 0.f;
-        s_shift[j] = col < g.Cout ? shift[col] : 0.f;
+      if (sub == 0) {
+        for (int j = et; j < BLOCK_N; j += 128) {
+          const int col = nt * BLOCK_N + j;
+          s_scale[j] = col < g.Cout ? scale[col] : 0.f;
+          s_shift[j] = col < g.Cout ? shift[col] : 0.f;
+        }
       }
       float acc[BLOCK_N];
 #pragma unroll
@@ -661,7 +698,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&acc_empty[buf]);
-        if (++buf == Cfg::kNumAcc) {
+        if (++buf == num_acc) {
           buf = 0;
           acc_phase ^= 1u;
         }
@@ -676,6 +713,27 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           for (int j = 0; j < 64; ++j) {
             float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
             y[j] = apply_act(t, g.relu, g.slope) * g.out_scale;
+          }
+          if (g.pool) {
+            // running maximum of the 2x2 window in the TMEM columns behind the accumulators
+            // (this thread's lane, so no other thread ever touches it)
+            const uint32_t paddr =
+                tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(num_acc * BLOCK_N + c0);
+            if (sub > 0) {
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                uint32_t v[32];
+                tmem_ld32(paddr + 32 * h, v);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) y[32 * h + j] = fmaxf(y[32 * h + j], __uint_as_float(v[j]));
+              }
+            }
+            if (sub < 3) {
+              tmem_st32(paddr, y);
+              tmem_st32(paddr + 32, y + 32);
+              tmem_wait_st();
+              continue;
+            }
           }
           for (int pass = 0; pass < 2; ++pass) {
             uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
@@ -701,7 +759,8 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             fence_proxy_async();
             epi_barrier();
             if (issuer) {
-              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
+              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0,
+                           g.pool ? wb : w0, g.pool ? hb : h0, n0);
               bulk_commit();
             }
             ++stores;
@@ -751,6 +810,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           ++stores;
         }
       }
+     }
     }
     if (issuer) bulk_wait_all();
   }
@@ -935,8 +995,8 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   if (rc != TP_OK) return rc;
   // fp16 split outputs are stored 64 halves (128 bytes) per staging row; everything else is fp32
   const bool half_out = F16 && g.split;
-  const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)g.W, (cuuint64_t)g.H,
-                               (cuuint64_t)g.N};
+  const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)(g.pool ? g.W / 2 : g.W),
+                               (cuuint64_t)(g.pool ? g.H / 2 : g.H), (cuuint64_t)g.N};
   const cuuint32_t ybox[4] = {half_out ? 64u : 32u, (cuuint32_t)g.bw, (cuuint32_t)g.bh,
                               (cuuint32_t)g.bn};
   rc = make_map(&o_hi, y_hi, 4, ydims, ybox, half_out);
@@ -961,7 +1021,8 @@ template <bool F16>
 static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W,
                         int64_t Cin, const void* w_hi, const void* w_lo, int taps, int64_t Cout,
                         const float* scale, const float* shift, int act, float leaky_slope,
-                        float out_scale, void* y_hi, void* y_lo, tp_stream_t stream) {
+                        float out_scale, void* y_hi, void* y_lo, tp_stream_t stream,
+                        int pool = 0) {
   constexpr int kKE = KBlock<F16>::kElems;
   TP_REQUIRE(N >= 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0, TP_ERR_INVALID,
              "tp_conv_tf32x3: bad dimension");
@@ -1009,13 +1070,24 @@ static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H
                           (!y_lo || (uintptr_t)y_lo % 16 == 0);
   TP_REQUIRE(!F16 || persistent || y_lo == nullptr, TP_ERR_LIMIT,
              "tp_conv_f16x3: split fp16 outputs need Cout %% 64 == 0");
-  if (persistent && taps == 9 && tuning().conv_pos_major != 1 &&
-      H * W <= tuning().conv_pos_major_max_hw && H * W >= 4 && N >= 128) {
+  const bool pos_major = persistent && taps == 9 && tuning().conv_pos_major != 1 &&
+                         H * W <= tuning().conv_pos_major_max_hw && H * W >= 4 && N >= 128;
+  if (pos_major) {
     g.bw = 1;
     g.bh = 1;
     g.bn = 128;
     g.tiles_h = (int)H;
     g.tiles_w = (int)W;
+  }
+  g.pool = 0;
+  if (pool) {
+    TP_REQUIRE(F16 && pos_major && y_lo != nullptr && H % 2 == 0 && W % 2 == 0, TP_ERR_LIMIT,
+               "tp_conv_f16x3_pool2: needs position-major tiles (3x3, H*W <= %d, N >= 128), even "
+               "H and W and split outputs; ask tp_conv_pool2_fusable first",
+               tuning().conv_pos_major_max_hw);
+    g.pool = 1;
+    g.tiles_h = (int)H / 2;
+    g.tiles_w = (int)W / 2;
   }
   g.num_kb = taps * (int)((Cin + kKE - 1) / kKE);
   g.relu = act;
@@ -1077,6 +1149,25 @@ int tp_conv_f16x3(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int6
                   void* y_lo, tp_stream_t stream) {
   return tp::conv_x3_impl<true>(x_hi, x_lo, N, H, W, Cin, w_hi, w_lo, taps, Cout, scale, shift,
                                 act, leaky_slope, out_scale, y_hi, y_lo, stream);
+}
+
+int tp_conv_f16x3_pool2(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W,
+                        int64_t Cin, const void* w_hi, const void* w_lo, int64_t Cout,
+                        const float* scale, const float* shift, int act, float leaky_slope,
+                        float out_scale, void* y_hi, void* y_lo, tp_stream_t stream) {
+  return tp::conv_x3_impl<true>(x_hi, x_lo, N, H, W, Cin, w_hi, w_lo, 9, Cout, scale, shift, act,
+                                leaky_slope, out_scale, y_hi, y_lo, stream, 1);
+}
+
+int tp_conv_pool2_fusable(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout) {
+  if (N < 128 || H <= 0 || W <= 0 || (H % 2) || (W % 2) || Cin <= 0 || Cin % 64 || Cout <= 16 ||
+      Cout % 64 || W > 128 || 128 % W)
+    return 0;
+  const tp::Tuning& t = tp::tuning();
+  return t.conv_variant != 1 && t.conv_pos_major != 1 && H * W <= t.conv_pos_major_max_hw &&
+                 H * W >= 4
+             ? 1
+             : 0;
 }
 
 int64_t tp_conv_tf32x3_flops(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int taps) {
