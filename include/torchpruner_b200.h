@@ -245,6 +245,27 @@ int tp_prefix_contrib_stack(const float* T, const int64_t* perm, int64_t k0, int
                             int64_t C1, int64_t Hp, int64_t Wp, int pool, int act,
                             float leaky_slope, float* out_hi, float* out_lo, tp_stream_t stream);
 
+/* Direct form of the same ladder: the contributions are recomputed where they are consumed
+ * instead of being stored once per batch (C * pixels * C1 floats, several GB on VGG16) and read
+ * back once per permutation — 9 FMAs per output element from L1/L2-resident data against 4 bytes
+ * of HBM read per element per mask.  Same arithmetic, FMA for FMA, so the same bits.
+ *
+ * tp_channel_major: zc[c][b][h][w] = z[b][c][h][w] (pool != 0: MaxPool2d(2) of it), the layout in
+ *   which one removed channel's patch is contiguous.
+ * tp_prefix_contrib_direct: for p in [0,P): c = perm ? perm[k0+p] : k0+p;
+ *   base += sign * T_c (float64, sign = -1 to walk a permutation, +1 with perm == NULL, P == C and
+ *   a zeroed base to form S_all); out[p] = split(act(base*scale + shift) [* out_scale]) as in
+ *   tp_prefix_contrib_stack (out_f16 != 0: fp16 pairs), optionally max-pooled 2x2 (conv mode).
+ *   mode 0: conv3x3 pad 1 over Hp x Wp (wt [C][9][C1]); mode 1: dense over the Hp*Wp positions
+ *   (wt [C][Hp*Wp][C1], one output row per example). */
+int tp_channel_major(const float* z, int64_t B, int64_t C, int64_t H, int64_t W, int pool, float* zc,
+                     tp_stream_t stream);
+int tp_prefix_contrib_direct(const float* zc, const float* wt, const int64_t* perm, int64_t k0,
+                             int64_t P, double* base, const float* scale, const float* shift,
+                             int64_t B, int64_t C, int64_t Hp, int64_t Wp, int mode, int64_t C1,
+                             int pool, int act, float leaky_slope, float sign, float out_scale,
+                             int out_f16, void* out_hi, void* out_lo, tp_stream_t stream);
+
 /* ---------------------------------------------------------------- no-allocation variant
  * No counterpart in the reference: this entry point exists for callers of THIS library that
  * cannot allocate device memory around the call.  Typical cases: a forward hook that runs in the

@@ -262,6 +262,74 @@ def test_incremental_first_layer_kernels(B, C, H, W, C1, pool_first, mode, pool_
     assert float(base.abs().max()) <= 1e-12 * float(want_T.abs().max()) * C
 
 
+@pytest.mark.parametrize("half", [False, True])
+@pytest.mark.parametrize("B,C,H,W,C1,pool_first,mode,pool_after", [
+    (3, 8, 8, 8, 32, False, 0, False),
+    (2, 6, 8, 8, 16, True, 0, True),
+    (4, 5, 4, 4, 64, False, 0, True),
+    (3, 7, 3, 5, 8, False, 0, False),    # odd spatial size: one pixel per thread
+    (2, 4, 2, 2, 128, False, 0, False),  # 2x2 image: every patch entry but the block is padding
+    (5, 12, 4, 4, 24, True, 1, False),
+    (7, 16, 1, 1, 32, False, 1, False),
+    (256, 9, 8, 8, 64, False, 0, True),  # more items than one wave
+])
+def test_direct_prefix_ladder_matches_stored_contributions(B, C, H, W, C1, pool_first, mode,
+                                                           pool_after, half):
+    """tp_channel_major + tp_prefix_contrib_direct (contributions recomputed on the fly) against
+    tp_channel_contrib + tp_contrib_sum + tp_prefix_contrib_stack: same FMAs in the same order,
+    so S_all, the running sums and every output must be identical bit for bit."""
+    gen = torch.Generator().manual_seed(B * 100 + C + 1)
+    z = torch.relu(torch.randn((B, C, H, W), generator=gen)).to(DEV)
+    Hp, Wp = (H // 2, W // 2) if pool_first else (H, W)
+    taps = 9 if mode == 0 else Hp * Wp
+    wt = (torch.randn((C, taps, C1), generator=gen) / 3.0).to(DEV)
+    scale = (torch.rand(C1, generator=gen) - 0.3).to(DEV)
+    shift = (torch.randn(C1, generator=gen) * 0.1).to(DEV)
+    oh, ow = (Hp, Wp) if mode == 0 else (1, 1)
+    pixels = B * oh * ow
+    M1 = pixels * C1
+    # stored form
+    T = torch.empty(C * M1, device=DEV)
+    assert _lib.channel_contrib(z, wt, pool_first, mode, T) == pixels
+    s_all = torch.empty(M1, dtype=torch.float64, device=DEV)
+    _lib.contrib_sum(T, C, M1, s_all)
+    # direct form
+    zc = _lib.channel_major(z, pool_first)
+    want_zc = (F.max_pool2d(z, 2) if pool_first else z).permute(1, 0, 2, 3).contiguous()
+    assert torch.equal(zc.view(want_zc.shape), want_zc)
+    s_dir = torch.zeros(M1, dtype=torch.float64, device=DEV)
+    _lib.prefix_contrib_direct(zc, wt, None, 0, C, s_dir, scale, shift, B, C, Hp, Wp, mode, False,
+                               False, sign=1.0)
+    assert torch.equal(s_dir, s_all)
+
+    perm = torch.from_numpy(np.random.RandomState(C).permutation(C).astype(np.int64)).to(DEV)
+    skip, relu, out_scale = 2, ("leaky", 0.1), 4.0 if half else 1.0
+    P = C - skip
+    m_out = (pixels // 4 if pool_after else pixels) * C1
+    dt = torch.float16 if half else torch.float32
+    outs = []
+    for direct in (False, True):
+        base = s_all.clone()
+        hi = torch.zeros(P * m_out, device=DEV, dtype=dt)
+        lo = torch.zeros_like(hi)
+        if direct:
+            _lib.prefix_contrib_direct(zc, wt, perm, 0, skip, base, scale, shift, B, C, Hp, Wp, mode,
+                                       pool_after, relu)
+            got = _lib.prefix_contrib_direct(zc, wt, perm, skip, P, base, scale, shift, B, C, Hp, Wp,
+                                             mode, pool_after, relu, out_hi=hi, out_lo=lo,
+                                             out_scale=out_scale)
+        else:
+            _lib.prefix_contrib_stack(T, perm, 0, skip, base, scale, shift, pixels, C1, oh, ow,
+                                      pool_after, relu)
+            got = _lib.prefix_contrib_stack(T, perm, skip, P, base, scale, shift, pixels, C1, oh, ow,
+                                            pool_after, relu, hi, lo, out_scale=out_scale)
+        assert got == m_out
+        outs.append((hi, lo, base))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    assert float(outs[1][0].float().abs().max()) > 0
+
+
 def test_native_tail_runs_the_reference_mlp():
     """The 784-2024-2024-10 LeakyReLU perceptron of the reference's untrained-network notebook:
     Linear layers whose K is not a multiple of 32, LeakyReLU epilogue, dense incremental first

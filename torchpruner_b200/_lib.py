@@ -78,6 +78,11 @@ _SIGNATURES = {
     "tp_prefix_contrib_stack_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64,
                                                    _i64, _i64, ctypes.c_int, ctypes.c_int,
                                                    ctypes.c_float, ctypes.c_float, _vp, _vp, _vp]),
+    "tp_channel_major": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, ctypes.c_int, _vp, _vp]),
+    "tp_prefix_contrib_direct": (ctypes.c_int, [_vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64,
+                                                _i64, _i64, ctypes.c_int, _i64, ctypes.c_int,
+                                                ctypes.c_int, ctypes.c_float, ctypes.c_float,
+                                                ctypes.c_float, ctypes.c_int, _vp, _vp, _vp]),
     "tp_channel_contrib": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, ctypes.c_int, ctypes.c_int,
                                           _i64, _vp, _vp]),
     "tp_contrib_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
@@ -535,6 +540,45 @@ def channel_contrib(z4, wt, pool, mode, out):
                                          int(mode), C1, out.data_ptr(), _stream(z4)),
                "tp_channel_contrib")
     return pixels
+
+
+def channel_major(z4, pool, out=None):
+    """[C, B, H', W'] copy of the NCHW activation (2x2 max-pooled first when pool)."""
+    z4 = _cuda_f32(z4, "z")
+    B, C, H, W = z4.shape
+    Hp, Wp = (H // 2, W // 2) if pool else (H, W)
+    if out is None or out.numel() < C * B * Hp * Wp:
+        out = torch.empty(C * B * Hp * Wp, dtype=torch.float32, device=z4.device)
+    with torch.cuda.device(z4.device), _launch("channel_major", 4 * z4.numel() + 4 * C * B * Hp * Wp, z4):
+        _check(load().tp_channel_major(z4.data_ptr(), B, C, H, W, int(bool(pool)), out.data_ptr(),
+                                       _stream(z4)), "tp_channel_major")
+    return out
+
+
+def prefix_contrib_direct(zc, wt, perm, k0, P, base, scale, shift, B, C, Hp, Wp, mode, pool, relu,
+                          sign=-1.0, out_hi=None, out_lo=None, out_scale=1.0):
+    """The prefix ladder with contributions recomputed on the fly (see the header).  Returns the
+    elements of one mask's output."""
+    C1 = wt.shape[2]
+    pixels = B * Hp * Wp if mode == 0 else B
+    m_out = (pixels // 4 if pool else pixels) * C1
+    if out_hi is not None and (out_hi.numel() < P * m_out or out_lo.numel() < P * m_out):
+        raise TorchPrunerB200Error("prefix_contrib_direct: output buffers too small")
+    if base.numel() < pixels * C1 or base.dtype != torch.float64:
+        raise TorchPrunerB200Error("prefix_contrib_direct: base must hold pixels*C1 float64")
+    half = out_hi is not None and out_hi.dtype == torch.float16
+    nbytes = ((4 if half else 8) * P * m_out if out_hi is not None else 0) + 16 * pixels * C1
+    flops = 2 * P * pixels * C1 * wt.shape[1]
+    name = "prefix_contrib_direct" if perm is not None else "contrib_sum_direct"
+    with torch.cuda.device(zc.device), _launch(name, nbytes, zc, 1, flops):
+        _check(load().tp_prefix_contrib_direct(
+            zc.data_ptr(), wt.data_ptr(), perm.data_ptr() if perm is not None else 0, int(k0), int(P),
+            base.data_ptr(), scale.data_ptr(), shift.data_ptr(), int(B), int(C), int(Hp), int(Wp),
+            int(mode), int(C1), int(bool(pool)), *_act_code(relu), float(sign), float(out_scale),
+            int(half), out_hi.data_ptr() if out_hi is not None else 0,
+            out_lo.data_ptr() if out_lo is not None else 0, _stream(zc)),
+            "tp_prefix_contrib_direct")
+    return m_out
 
 
 def contrib_sum(T, C, M1, s_all):

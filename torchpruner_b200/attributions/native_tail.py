@@ -28,6 +28,12 @@ import math
 import os
 
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+# Incremental first layer: "stored" computes the per-channel contributions once per batch into a
+# [C, pixels*C1] scratch (4.3 GB for a VGG16 block at bs 256) and streams them back per mask;
+# "direct" recomputes them where they are consumed (no scratch; measured within 1 % of "stored"
+# on the VGG16 job, profiles/r01_prefix_direct_vs_stored.txt).  "auto": stored while the scratch
+# stays under INCREMENTAL_MAX_BYTES, direct beyond it.
+CONTRIB = os.environ.get("TORCHPRUNER_B200_CONTRIB", "auto")
 FUSE_POOL = os.environ.get("TORCHPRUNER_B200_FUSE_POOL", "1") != "0"
 F16_TARGET = 64.0    # per-tensor power-of-two scaling brings max|x| to ~64 (fp16 max is 65504)
 
@@ -37,7 +43,7 @@ def _pow2_scale(max_abs):
     if not (max_abs > 0.0) or not math.isfinite(max_abs):
         return 1.0
     return float(2.0 ** round(math.log2(F16_TARGET / max_abs)))
-INCREMENTAL_MAX_BYTES = 12 << 30   # per-channel contributions of the first layer, per batch
+INCREMENTAL_MAX_BYTES = 8 << 30   # per-channel contributions of the first layer, per batch
 
 
 class _Unsupported(Exception):
@@ -135,7 +141,7 @@ class NativeTail:
         # limits.  use_f16 may be switched off at run time (verification failure / overflow).
         self.f16_ok = all(st.get("w16_hi") is not None for st in steps)
         self.use_f16 = self.f16_ok and os.environ.get("TORCHPRUNER_B200_F16", "1") != "0"
-        self._T = self._s_all = self._base = None
+        self._T = self._s_all = self._base = self._zc = None
         self._perm = None
         self._pos = 0
 
@@ -342,6 +348,22 @@ class NativeTail:
         B, C = z4.shape[0], z4.shape[1]
         pixels, _ = self._first_out_geometry(B)
         M1 = pixels * f["C1"]
+        if CONTRIB == "direct" or (CONTRIB != "stored" and C * M1 * 4 > INCREMENTAL_MAX_BYTES):
+            if self._s_all is None or self._s_all.numel() < M1 or self._s_all.device != z.device:
+                self._s_all = torch.empty(M1, dtype=torch.float64, device=z.device)
+                self._base = torch.empty(M1, dtype=torch.float64, device=z.device)
+            self._zc = _lib.channel_major(z4, self.pool_first)
+            H, W = z4.shape[2], z4.shape[3]
+            # spatial size of the layer's input: its output grid (conv) or all positions (dense)
+            self._zgeom = (B, C) + ((H // 2, W // 2) if self.pool_first else (H, W))
+            self._s_all[:M1].zero_()
+            _lib.prefix_contrib_direct(self._zc, f["wt"], None, 0, C, self._s_all, f["scale"],
+                                       f["shift"], *self._zgeom, f["mode"], False, False, sign=1.0)
+            self._T = None
+            self._M1, self._pixels = M1, pixels
+            self.incremental = True
+            return
+        self._zc = None
         if C * M1 * 4 > INCREMENTAL_MAX_BYTES:
             return
         if self._T is None or self._T.numel() < C * M1 or self._T.device != z.device:
@@ -356,7 +378,7 @@ class NativeTail:
     def release(self):
         """Drop the per-batch scratch (contributions can be several GB); the plan itself, which is
         cached across runs, keeps only the prepared weights."""
-        self._T = self._s_all = self._base = self._perm = None
+        self._T = self._s_all = self._base = self._perm = self._zc = None
         self.incremental = False
 
     def begin(self, perm, k_start):
@@ -368,8 +390,13 @@ class NativeTail:
         base = self._base[:self._M1]
         base.copy_(self._s_all[:self._M1])
         if k_start > 0:   # a sharded rank starts mid-permutation: skip the prefix without output
-            _lib.prefix_contrib_stack(self._T, perm, 0, int(k_start), base, f["scale"], f["shift"],
-                                      self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"])
+            if self._zc is not None:
+                _lib.prefix_contrib_direct(self._zc, f["wt"], perm, 0, int(k_start), base, f["scale"],
+                                           f["shift"], *self._zgeom, f["mode"], f["pool"], f["relu"])
+            else:
+                _lib.prefix_contrib_stack(self._T, perm, 0, int(k_start), base, f["scale"],
+                                          f["shift"], self._pixels, f["C1"], f["Hp"], f["Wp"],
+                                          f["pool"], f["relu"])
 
     @property
     def stack_dtype(self):
@@ -400,10 +427,16 @@ class NativeTail:
             if k0 != self._pos:
                 raise RuntimeError("incremental tail evaluated out of order")
             f = self.first
-            m_out = _lib.prefix_contrib_stack(
-                self._T, self._perm, k0, P, self._base[:self._M1], f["scale"], f["shift"],
-                self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"], buf_hi, buf_lo,
-                out_scale=self.steps[1]["s_in"] if f16 else 1.0)
+            if self._zc is not None:
+                m_out = _lib.prefix_contrib_direct(
+                    self._zc, f["wt"], self._perm, k0, P, self._base[:self._M1], f["scale"],
+                    f["shift"], *self._zgeom, f["mode"], f["pool"], f["relu"], out_hi=buf_hi,
+                    out_lo=buf_lo, out_scale=self.steps[1]["s_in"] if f16 else 1.0)
+            else:
+                m_out = _lib.prefix_contrib_stack(
+                    self._T, self._perm, k0, P, self._base[:self._M1], f["scale"], f["shift"],
+                    self._pixels, f["C1"], f["Hp"], f["Wp"], f["pool"], f["relu"], buf_hi, buf_lo,
+                    out_scale=self.steps[1]["s_in"] if f16 else 1.0)
             self._pos += P
             Ho, Wo = (f["Hp"] // 2, f["Wp"] // 2) if f["pool"] else (f["Hp"], f["Wp"])
             shape = (P * B, Ho, Wo, f["C1"])

@@ -288,6 +288,231 @@ prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restri
   }
 }
 
+
+// =====================================================================================
+// Direct form: the contributions are never stored.  T_c is 9 FMAs per output element from data
+// that sits in L1/L2 (one channel of the activation and one 9 x C1 weight slab), which is cheaper
+// than writing C*pixels*C1 floats once per batch and reading them back once per permutation (the
+// stored form moves 8 bytes per output element per mask, this one 4 — the output itself — and
+// needs no C-fold scratch).  The arithmetic is the stored form's, FMA for FMA, so both produce
+// the same bits.
+//
+//   zc : channel-major activation [C][B][Hp][Wp] (after the optional pool in front of the layer)
+//   conv mode : a thread owns a BLK x BLK block of output pixels and 4 output channels; per mask
+//               it loads the (BLK+2)^2 activation patch of the removed channel and that channel's
+//               9 float4 weights, forms the BLK^2 contributions and updates its float64 sums.
+//   dense mode: a thread owns one example and 4 output features; taps = Hp*Wp positions.
+//   perm == NULL walks the channels in order (used with sign = +1, emit = 0 to form S_all).
+// =====================================================================================
+__global__ void __launch_bounds__(256)
+channel_major_kernel(const float* __restrict__ z, int B, int C, int H, int W, int pool,
+                     float* __restrict__ zc) {
+  const int Hp = pool ? H / 2 : H, Wp = pool ? W / 2 : W;
+  const long long total = (long long)C * B * Hp * Wp;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += gridDim.x * (long long)blockDim.x) {
+    const int w = (int)(e % Wp);
+    long long t = e / Wp;
+    const int h = (int)(t % Hp);
+    t /= Hp;
+    const int b = (int)(t % B);
+    const int c = (int)(t / B);
+    zc[e] = zprime(z, b, c, h, w, C, H, W, pool);
+  }
+}
+
+struct DirectGeom {
+  int B, C, Hp, Wp, C1;
+  int pool, relu, emit;
+  float slope, out_scale, sign;
+};
+
+template <bool HALF>
+__device__ __forceinline__ void emit_split4(float4 y, float out_scale, void* out_hi_v,
+                                            void* out_lo_v, long long o) {
+  if (HALF) {
+    const float v[4] = {y.x * out_scale, y.y * out_scale, y.z * out_scale, y.w * out_scale};
+    __half h[4], l[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      h[q] = __float2half_rn(v[q]);
+      l[q] = __float2half_rn(v[q] - __half2float(h[q]));
+    }
+    st_cs_u2(static_cast<__half*>(out_hi_v) + o, *reinterpret_cast<const uint2*>(h));
+    st_cs_u2(static_cast<__half*>(out_lo_v) + o, *reinterpret_cast<const uint2*>(l));
+  } else {
+    const float4 hi = make_float4(inc_tf32_hi(y.x), inc_tf32_hi(y.y), inc_tf32_hi(y.z),
+                                  inc_tf32_hi(y.w));
+    const float4 lo = make_float4(inc_tf32_hi(y.x - hi.x), inc_tf32_hi(y.y - hi.y),
+                                  inc_tf32_hi(y.z - hi.z), inc_tf32_hi(y.w - hi.w));
+    *reinterpret_cast<float4*>(static_cast<float*>(out_hi_v) + o) = hi;
+    *reinterpret_cast<float4*>(static_cast<float*>(out_lo_v) + o) = lo;
+  }
+}
+
+template <int BLK, bool HALF>
+__global__ void __launch_bounds__(256, 2)
+prefix_direct_conv_kernel(const float* __restrict__ zc, const float* __restrict__ wt,
+                          const int64_t* __restrict__ perm, long long k0, int P,
+                          double* __restrict__ base, const float* __restrict__ scale,
+                          const float* __restrict__ shift, DirectGeom g,
+                          void* __restrict__ out_hi_v, void* __restrict__ out_lo_v) {
+  constexpr int NSRC = BLK * BLK;
+  constexpr int PW = BLK + 2;
+  const unsigned opp = (unsigned)g.C1 >> 2;
+  const int Hb = g.Hp / BLK, Wb = g.Wp / BLK;
+  const long long blocks = (long long)g.B * Hb * Wb;
+  const long long items = blocks * opp;
+  const long long pixels = (long long)g.B * g.Hp * g.Wp;
+  const long long m_out = (g.pool ? pixels / 4 : pixels) * g.C1;
+  const long long img = (long long)g.Hp * g.Wp;
+  const float4* w4 = reinterpret_cast<const float4*>(wt);
+  for (long long it = blockIdx.x * (long long)blockDim.x + threadIdx.x; it < items;
+       it += gridDim.x * (long long)blockDim.x) {
+    const long long blk = it / opp;
+    const unsigned o4 = (unsigned)(it - blk * opp);
+    const int wb = (int)(blk % Wb);
+    const long long t = blk / Wb;
+    const int hb = (int)(t % Hb);
+    const int b = (int)(t / Hb);
+    const int h0 = hb * BLK, w0 = wb * BLK;
+    const float4 a = reinterpret_cast<const float4*>(scale)[o4];
+    const float4 bsh = reinterpret_cast<const float4*>(shift)[o4];
+    long long pix[NSRC];
+    double run[NSRC][4];
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      pix[s] = ((long long)b * g.Hp + h0 + s / BLK) * g.Wp + w0 + s % BLK;
+      const double* bp = base + pix[s] * g.C1 + o4 * 4;
+      run[s][0] = bp[0];
+      run[s][1] = bp[1];
+      run[s][2] = bp[2];
+      run[s][3] = bp[3];
+    }
+    // which patch entries lie inside the image (the others are the conv's zero padding)
+    bool rin[PW], cin[PW];
+#pragma unroll
+    for (int i = 0; i < PW; ++i) {
+      rin[i] = (h0 + i - 1) >= 0 && (h0 + i - 1) < g.Hp;
+      cin[i] = (w0 + i - 1) >= 0 && (w0 + i - 1) < g.Wp;
+    }
+    for (int p = 0; p < P; ++p) {
+      const long long c = perm ? perm[k0 + p] : (k0 + p);
+      const float* zp = zc + (c * g.B + b) * img + (long long)(h0 - 1) * g.Wp + (w0 - 1);
+      float patch[PW][PW];
+#pragma unroll
+      for (int i = 0; i < PW; ++i)
+#pragma unroll
+        for (int j = 0; j < PW; ++j)
+          patch[i][j] = (rin[i] && cin[j]) ? __ldg(zp + i * g.Wp + j) : 0.f;
+      float4 wv[9];
+#pragma unroll
+      for (int tp = 0; tp < 9; ++tp) wv[tp] = __ldg(w4 + (c * 9 + tp) * opp + o4);
+      float4 y = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+      for (int s = 0; s < NSRC; ++s) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            const float zv = patch[s / BLK + r][s % BLK + q];
+            const float4 w = wv[r * 3 + q];
+            acc.x = fmaf(zv, w.x, acc.x);
+            acc.y = fmaf(zv, w.y, acc.y);
+            acc.z = fmaf(zv, w.z, acc.z);
+            acc.w = fmaf(zv, w.w, acc.w);
+          }
+        run[s][0] += (double)(g.sign * acc.x);
+        run[s][1] += (double)(g.sign * acc.y);
+        run[s][2] += (double)(g.sign * acc.z);
+        run[s][3] += (double)(g.sign * acc.w);
+        if (g.emit) {
+          float4 v;
+          v.x = affine_act(run[s][0], a.x, bsh.x, g.relu, g.slope);
+          v.y = affine_act(run[s][1], a.y, bsh.y, g.relu, g.slope);
+          v.z = affine_act(run[s][2], a.z, bsh.z, g.relu, g.slope);
+          v.w = affine_act(run[s][3], a.w, bsh.w, g.relu, g.slope);
+          if (BLK == 2 && g.pool) {
+            y.x = fmaxf(y.x, v.x);
+            y.y = fmaxf(y.y, v.y);
+            y.z = fmaxf(y.z, v.z);
+            y.w = fmaxf(y.w, v.w);
+          } else {
+            emit_split4<HALF>(v, g.out_scale, out_hi_v, out_lo_v,
+                              (long long)p * m_out + pix[s] * g.C1 + o4 * 4);
+          }
+        }
+      }
+      if (g.emit && BLK == 2 && g.pool)
+        emit_split4<HALF>(y, g.out_scale, out_hi_v, out_lo_v,
+                          (long long)p * m_out + blk * g.C1 + o4 * 4);
+    }
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      double* bp = base + pix[s] * g.C1 + o4 * 4;
+      bp[0] = run[s][0];
+      bp[1] = run[s][1];
+      bp[2] = run[s][2];
+      bp[3] = run[s][3];
+    }
+  }
+}
+
+// dense mode: wt [C][S][C1], zc [C][B][S]; output row = example
+template <bool HALF>
+__global__ void __launch_bounds__(256)
+prefix_direct_dense_kernel(const float* __restrict__ zc, const float* __restrict__ wt,
+                           const int64_t* __restrict__ perm, long long k0, int P,
+                           double* __restrict__ base, const float* __restrict__ scale,
+                           const float* __restrict__ shift, DirectGeom g,
+                           void* __restrict__ out_hi_v, void* __restrict__ out_lo_v) {
+  const unsigned opp = (unsigned)g.C1 >> 2;
+  const int S = g.Hp * g.Wp;
+  const long long items = (long long)g.B * opp;
+  const long long m_out = (long long)g.B * g.C1;
+  const float4* w4 = reinterpret_cast<const float4*>(wt);
+  for (long long it = blockIdx.x * (long long)blockDim.x + threadIdx.x; it < items;
+       it += gridDim.x * (long long)blockDim.x) {
+    const long long b = it / opp;
+    const unsigned o4 = (unsigned)(it - b * opp);
+    const float4 a = reinterpret_cast<const float4*>(scale)[o4];
+    const float4 bsh = reinterpret_cast<const float4*>(shift)[o4];
+    double* bp = base + b * g.C1 + o4 * 4;
+    double run[4] = {bp[0], bp[1], bp[2], bp[3]};
+    for (int p = 0; p < P; ++p) {
+      const long long c = perm ? perm[k0 + p] : (k0 + p);
+      const float* zp = zc + (c * g.B + b) * S;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int tp = 0; tp < S; ++tp) {
+        const float zv = __ldg(zp + tp);
+        const float4 w = __ldg(w4 + (c * S + tp) * opp + o4);
+        acc.x = fmaf(zv, w.x, acc.x);
+        acc.y = fmaf(zv, w.y, acc.y);
+        acc.z = fmaf(zv, w.z, acc.z);
+        acc.w = fmaf(zv, w.w, acc.w);
+      }
+      run[0] += (double)(g.sign * acc.x);
+      run[1] += (double)(g.sign * acc.y);
+      run[2] += (double)(g.sign * acc.z);
+      run[3] += (double)(g.sign * acc.w);
+      if (g.emit) {
+        float4 v;
+        v.x = affine_act(run[0], a.x, bsh.x, g.relu, g.slope);
+        v.y = affine_act(run[1], a.y, bsh.y, g.relu, g.slope);
+        v.z = affine_act(run[2], a.z, bsh.z, g.relu, g.slope);
+        v.w = affine_act(run[3], a.w, bsh.w, g.relu, g.slope);
+        emit_split4<HALF>(v, g.out_scale, out_hi_v, out_lo_v,
+                          (long long)p * m_out + b * g.C1 + o4 * 4);
+      }
+    }
+    bp[0] = run[0];
+    bp[1] = run[1];
+    bp[2] = run[2];
+    bp[3] = run[3];
+  }
+}
+
 static inline unsigned inc_grid(long long items, int waves = 16) {
   long long blocks = (items + 255) / 256;
   const long long cap = (long long)sm_count() * waves;
@@ -406,6 +631,84 @@ int tp_prefix_contrib_stack_f16(const float* T, const int64_t* perm, int64_t k0,
                                 void* out_lo, tp_stream_t stream) {
   return prefix_contrib_stack_impl(T, perm, k0, P, base, scale, shift, pixels, C1, Hp, Wp, pool, act,
                                    leaky_slope, out_scale, true, out_hi, out_lo, stream);
+}
+
+int tp_channel_major(const float* z, int64_t B, int64_t C, int64_t H, int64_t W, int pool, float* zc,
+                     tp_stream_t stream) {
+  TP_REQUIRE(B >= 0 && C >= 0 && H > 0 && W > 0, TP_ERR_INVALID, "tp_channel_major: bad dimension");
+  TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
+             "tp_channel_major: pooling needs even H and W");
+  if (B == 0 || C == 0) return TP_OK;
+  TP_REQUIRE(z && zc, TP_ERR_INVALID, "tp_channel_major: NULL pointer");
+  const long long total = B * C * (pool ? H / 2 : H) * (pool ? W / 2 : W);
+  tp::channel_major_kernel<<<tp::inc_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z, (int)B, (int)C, (int)H, (int)W, pool, zc);
+  TP_LAUNCH_CHECK("channel_major_kernel");
+  return TP_OK;
+}
+
+int tp_prefix_contrib_direct(const float* zc, const float* wt, const int64_t* perm, int64_t k0,
+                             int64_t P, double* base, const float* scale, const float* shift,
+                             int64_t B, int64_t C, int64_t Hp, int64_t Wp, int mode, int64_t C1,
+                             int pool, int act, float leaky_slope, float sign, float out_scale,
+                             int out_f16, void* out_hi, void* out_lo, tp_stream_t stream) {
+  using namespace tp;
+  TP_REQUIRE(P >= 0 && k0 >= 0 && B >= 0 && C >= 0 && Hp > 0 && Wp > 0 && C1 > 0, TP_ERR_INVALID,
+             "tp_prefix_contrib_direct: bad dimension");
+  TP_REQUIRE(mode == 0 || mode == 1, TP_ERR_INVALID, "tp_prefix_contrib_direct: mode must be 0 or 1");
+  TP_REQUIRE(C1 % 4 == 0, TP_ERR_LIMIT, "tp_prefix_contrib_direct: C1 must be a multiple of 4");
+  TP_REQUIRE(k0 + P <= C, TP_ERR_INVALID, "tp_prefix_contrib_direct: k0 + P exceeds the channels");
+  TP_REQUIRE(!pool || (mode == 0 && Hp % 2 == 0 && Wp % 2 == 0), TP_ERR_INVALID,
+             "tp_prefix_contrib_direct: pooling needs the conv mode and even Hp, Wp");
+  TP_REQUIRE((out_hi == nullptr) == (out_lo == nullptr), TP_ERR_INVALID,
+             "tp_prefix_contrib_direct: out_hi and out_lo must both be given or both be NULL");
+  TP_REQUIRE(sign == 1.f || sign == -1.f, TP_ERR_INVALID,
+             "tp_prefix_contrib_direct: sign must be +1 or -1");
+  if (P == 0 || B == 0) return TP_OK;
+  TP_REQUIRE(zc && wt && base && scale && shift, TP_ERR_INVALID,
+             "tp_prefix_contrib_direct: NULL pointer");
+  DirectGeom g;
+  g.B = (int)B;
+  g.C = (int)C;
+  g.Hp = (int)Hp;
+  g.Wp = (int)Wp;
+  g.C1 = (int)C1;
+  g.pool = pool;
+  g.relu = act;
+  g.emit = out_hi != nullptr;
+  g.slope = leaky_slope;
+  g.out_scale = out_scale;
+  g.sign = sign;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool half = out_f16 != 0;
+  if (mode == 1) {
+    const unsigned grid = inc_grid(B * (C1 / 4));
+    if (half)
+      prefix_direct_dense_kernel<true><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                            shift, g, out_hi, out_lo);
+    else
+      prefix_direct_dense_kernel<false><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                             shift, g, out_hi, out_lo);
+    TP_LAUNCH_CHECK("prefix_direct_dense_kernel");
+    return TP_OK;
+  }
+  const bool blk2 = Hp % 2 == 0 && Wp % 2 == 0;
+  const long long items = (blk2 ? B * (Hp / 2) * (Wp / 2) : B * Hp * Wp) * (C1 / 4);
+  const unsigned grid = inc_grid(items);
+  if (blk2 && half)
+    prefix_direct_conv_kernel<2, true><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                            shift, g, out_hi, out_lo);
+  else if (blk2)
+    prefix_direct_conv_kernel<2, false><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                             shift, g, out_hi, out_lo);
+  else if (half)
+    prefix_direct_conv_kernel<1, true><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                            shift, g, out_hi, out_lo);
+  else
+    prefix_direct_conv_kernel<1, false><<<grid, 256, 0, st>>>(zc, wt, perm, k0, (int)P, base, scale,
+                                                             shift, g, out_hi, out_lo);
+  TP_LAUNCH_CHECK("prefix_direct_conv_kernel");
+  return TP_OK;
 }
 
 }  // extern "C"
