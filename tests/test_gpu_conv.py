@@ -200,6 +200,53 @@ def test_native_tail_declines_unsupported_models():
     assert tail is not None and tail.pool_first and len(tail.steps) == 2
 
 
+def test_plan_verification_arbitrates_rounding_with_a_float64_twin(monkeypatch):
+    """The model's own fp32 forward (cuDNN) is itself up to ~2e-5 off: a plan that differs from it
+    by a little more than the tolerance is judged against a float64 copy of the model instead of
+    being thrown away (an 8-GPU run lost 35 % to one rank whose first two masks landed at 2.1e-5).
+    A structurally wrong plan still fails."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import native_tail
+    from torchpruner_b200.attributions.native_tail import NativeTail
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        x = torch.randn((32,) + shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(3))
+        module = model.features[9]
+        with torch.no_grad():
+            z = model.forward_partial(x, to_module=module).float().contiguous()
+        tail = NativeTail.build(model, module, z)
+        assert tail is not None
+        n = z.shape[1]
+        perm = torch.randperm(n, device=DEV)
+        inv = torch.empty(n, dtype=torch.int32, device=DEV)
+        inv[perm] = torch.arange(n, dtype=torch.int32, device=DEV)
+        tail.prepare_batch(z)
+        hi = torch.empty(tail.stack_elems(32, 2), dtype=tail.stack_dtype, device=DEV)
+        lo = torch.empty_like(hi)
+        ok, err = tail.verify(model, module, z, perm, inv, 0, 2, hi, lo)
+        assert ok and err <= native_tail.VERIFY_RTOL
+        # force the second stage: nothing passes the fp32 comparison any more
+        monkeypatch.setattr(native_tail, "VERIFY_RTOL", 1e-9)
+        calls = []
+        real = native_tail._float64_forward
+        monkeypatch.setattr(native_tail, "_float64_forward",
+                            lambda *a: calls.append(1) or real(*a))
+        ok, err64 = tail.verify(model, module, z, perm, inv, 0, 2, hi, lo)
+        assert calls and ok and err64 <= 1e-5, (ok, err64)   # engine vs float64, 10 layers deep
+        # a wrong plan (one layer's shift off by 1 %) fails both stages
+        tail.steps[1]["shift"].mul_(1.01)
+        ok, _ = tail.verify(model, module, z, perm, inv, 0, 2, hi, lo)
+        assert not ok
+        tail.steps[1]["shift"].div_(1.01)
+        tail.release()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 @pytest.mark.parametrize("B,C,H,W,C1,pool_first,mode,pool_after", [
     (3, 8, 8, 8, 32, False, 0, False),
     (2, 6, 8, 8, 16, True, 0, True),     # MaxPool before the layer and after it

@@ -28,6 +28,7 @@ import math
 import os
 
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
+VERIFY_ARBITRATE_BELOW = 1e-3   # above this the difference is structural, not rounding
 # Incremental first layer: "stored" computes the per-channel contributions once per batch into a
 # [C, pixels*C1] scratch (4.3 GB for a VGG16 block at bs 256) and streams them back per mask;
 # "direct" recomputes them where they are consumed (no scratch; measured within 1 % of "stored"
@@ -490,13 +491,21 @@ class NativeTail:
 
     def verify(self, model, module, z, perm, inv_perm, k0, P, buf_hi, buf_lo):
         """True iff the plan reproduces ``forward_partial`` on P real masks of this run (both the
-        incremental and the direct form of the first layer are checked)."""
+        incremental and the direct form of the first layer are checked).
+
+        First against the model's own fp32 forward, to VERIFY_RTOL of the largest logit.  That
+        forward is library code with rounding of its own (cuDNN's fp32 convolution algorithms
+        differ from the exact result by up to ~2e-5 here, forty times the engine's own error),
+        so a difference slightly above the tolerance does not say which side is off: it is then
+        arbitrated by a float64 copy of the model, and the plan is accepted when it is at least as
+        close to that as the fp32 library forward is.  Structural mistakes are O(1) and fail both."""
         stacked = _lib.prefix_mask_stack(z, inv_perm, k0, P)
         with torch.no_grad():
             ref = model.forward_partial(stacked, to_module=None, from_module=module)
         scale = float(ref.abs().max().clamp_min(1e-30))
         worst = 0.0
         was_incremental = self.incremental
+        outs = []
         for mode in ([True, False] if was_incremental else [False]):
             self.incremental = mode
             self.begin(perm, k0)
@@ -504,6 +513,30 @@ class NativeTail:
             if ref.shape != mine.shape:
                 self.incremental = was_incremental
                 return False, float("inf")
+            outs.append(mine.clone())
             worst = max(worst, float((ref - mine).abs().max()) / scale)
         self.incremental = was_incremental
-        return worst <= VERIFY_RTOL, worst
+        if worst <= VERIFY_RTOL:
+            return True, worst
+        if worst > VERIFY_ARBITRATE_BELOW:
+            return False, worst
+        ref64 = _float64_forward(model, module, stacked)
+        if ref64 is None or ref64.shape != ref.shape:
+            return False, worst
+        lib_err = float((ref.double() - ref64).abs().max()) / scale
+        mine_err = max(float((o.double() - ref64).abs().max()) for o in outs) / scale
+        return mine_err <= max(VERIFY_RTOL / 10, lib_err), mine_err
+
+
+def _float64_forward(model, module, stacked):
+    """``forward_partial`` of a float64 deep copy of the model (None when the model cannot be
+    copied or run that way)."""
+    import copy
+    try:
+        name = next(n for n, m in model.named_modules() if m is module)
+        twin = copy.deepcopy(model).double()
+        twin_module = twin.get_submodule(name) if name else twin
+        with torch.no_grad():
+            return twin.forward_partial(stacked.double(), to_module=None, from_module=twin_module)
+    except Exception:
+        return None
