@@ -69,7 +69,8 @@ def workload_description(n_gpus):
         "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
                     "BN+ReLU, 5 permutations (the reference's default sv_samples) per GPU per step "
                     "= 21120 channel-evals/GPU/step (5 steps = the sv_samples=25 job); layers after the scored module run fp32-accurate "
-                    "(tcgen05 3xTF32 engine, verified against forward_partial; cuDNN/cuBLAS TF32 off)",
+                    "(tcgen05 engine: 3 MMAs per fp32 product on an 11-bit fp16 split, TF32 split as fallback; "
+                    "verified against forward_partial; cuDNN/cuBLAS TF32 off)",
         "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224 * PERMS_PER_STEP,
         "sv_samples_per_step": PERMS_PER_STEP * n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
         "l2": "working set per step (stacked masked activations, up to 512 MiB per chunk) far "
