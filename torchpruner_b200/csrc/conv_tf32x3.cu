@@ -612,46 +612,46 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int n0, hb, wb;
         tile_origin(g, tile / n_tiles, n0, hb, wb);
-       for (int sub = 0; sub < subs; ++sub) {
-        const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
-        const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
-        const int nk = count_kblocks(g, h0, w0);
-        int in_chunk = 0;
-        for (int kb = 0; kb < nk; ++kb) {
-          if (in_chunk == 0) {
-            mbar_wait(&acc_empty[buf], acc_phase ^ 1u);
+        for (int sub = 0; sub < subs; ++sub) {
+          const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
+          const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+          const int nk = count_kblocks(g, h0, w0);
+          int in_chunk = 0;
+          for (int kb = 0; kb < nk; ++kb) {
+            if (in_chunk == 0) {
+              mbar_wait(&acc_empty[buf], acc_phase ^ 1u);
+              tc_fence_after();
+            }
+            mbar_wait(&full[stage], phase);
             tc_fence_after();
-          }
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          uint8_t* st = smem + stage * Cfg::kStageBytes;
-          const uint64_t a_hi = umma_desc_sw128(st);
-          const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
-          const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
-          const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
-          const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+            uint8_t* st = smem + stage * Cfg::kStageBytes;
+            const uint64_t a_hi = umma_desc_sw128(st);
+            const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
+            const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
+            const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
+            const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
 #pragma unroll
-          for (int kk = 0; kk < kBlockK / 8; ++kk) {
-            const uint64_t off = (uint64_t)(kk * 32 >> 4);
-            umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-            umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-            umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
-          }
-          umma_commit(&empty[stage]);
-          if (++stage == Cfg::kStages) {
-            stage = 0;
-            phase ^= 1u;
-          }
-          if (++in_chunk == g.promote || kb == nk - 1) {
-            umma_commit(&acc_full[buf]);
-            in_chunk = 0;
-            if (++buf == num_acc) {
-              buf = 0;
-              acc_phase ^= 1u;
+            for (int kk = 0; kk < kBlockK / 8; ++kk) {
+              const uint64_t off = (uint64_t)(kk * 32 >> 4);
+              umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+              umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+              umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+            }
+            umma_commit(&empty[stage]);
+            if (++stage == Cfg::kStages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+            if (++in_chunk == g.promote || kb == nk - 1) {
+              umma_commit(&acc_full[buf]);
+              in_chunk = 0;
+              if (++buf == num_acc) {
+                buf = 0;
+                acc_phase ^= 1u;
+              }
             }
           }
         }
-       }
       }
     }
     __syncwarp();
@@ -668,149 +668,149 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
       int n0, hb, wb;
       tile_origin(g, mt, n0, hb, wb);
-     for (int sub = 0; sub < subs; ++sub) {
-      const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
-      const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
-      const int nk = count_kblocks(g, h0, w0);
-      const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
-      // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
-      if (sub == 0) {
-        for (int j = et; j < BLOCK_N; j += 128) {
-          const int col = nt * BLOCK_N + j;
-          s_scale[j] = col < g.Cout ? scale[col] : 0.f;
-          s_shift[j] = col < g.Cout ? shift[col] : 0.f;
-        }
-      }
-      float acc[BLOCK_N];
-#pragma unroll
-      for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
-      for (int chunk = 0; chunk < chunks_this_tile; ++chunk) {
-        mbar_wait(&acc_full[buf], acc_phase);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
-#pragma unroll
-        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-          uint32_t v[32];
-          tmem_ld32(taddr + c0, v);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) acc[c0 + j] += __uint_as_float(v[j]);
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[buf]);
-        if (++buf == num_acc) {
-          buf = 0;
-          acc_phase ^= 1u;
-        }
-      }
-      epi_barrier();  // scale/shift of this tile visible to all epilogue threads
-      if (F16 && g.split) {
-        // fp16 split outputs: staging rows are 64 halves (128 bytes), so 64 columns per store
-#pragma unroll
-        for (int c0 = 0; c0 < BLOCK_N; c0 += 64) {
-          float y[64];
-#pragma unroll
-          for (int j = 0; j < 64; ++j) {
-            float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
-            y[j] = apply_act(t, g.relu, g.slope) * g.out_scale;
+      for (int sub = 0; sub < subs; ++sub) {
+        const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
+        const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+        const int nk = count_kblocks(g, h0, w0);
+        const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
+        // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
+        if (sub == 0) {
+          for (int j = et; j < BLOCK_N; j += 128) {
+            const int col = nt * BLOCK_N + j;
+            s_scale[j] = col < g.Cout ? scale[col] : 0.f;
+            s_shift[j] = col < g.Cout ? shift[col] : 0.f;
           }
-          if (g.pool) {
-            // running maximum of the 2x2 window in the TMEM columns behind the accumulators
-            // (this thread's lane, so no other thread ever touches it)
-            const uint32_t paddr =
-                tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(num_acc * BLOCK_N + c0);
-            if (sub > 0) {
+        }
+        float acc[BLOCK_N];
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
-                uint32_t v[32];
-                tmem_ld32(paddr + 32 * h, v);
+        for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
+        for (int chunk = 0; chunk < chunks_this_tile; ++chunk) {
+          mbar_wait(&acc_full[buf], acc_phase);
+          tc_fence_after();
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) y[32 * h + j] = fmaxf(y[32 * h + j], __uint_as_float(v[j]));
+          for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c0, v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[c0 + j] += __uint_as_float(v[j]);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[buf]);
+          if (++buf == num_acc) {
+            buf = 0;
+            acc_phase ^= 1u;
+          }
+        }
+        epi_barrier();  // scale/shift of this tile visible to all epilogue threads
+        if (F16 && g.split) {
+          // fp16 split outputs: staging rows are 64 halves (128 bytes), so 64 columns per store
+#pragma unroll
+          for (int c0 = 0; c0 < BLOCK_N; c0 += 64) {
+            float y[64];
+#pragma unroll
+            for (int j = 0; j < 64; ++j) {
+              float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+              y[j] = apply_act(t, g.relu, g.slope) * g.out_scale;
+            }
+            if (g.pool) {
+              // running maximum of the 2x2 window in the TMEM columns behind the accumulators
+              // (this thread's lane, so no other thread ever touches it)
+              const uint32_t paddr =
+                  tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(num_acc * BLOCK_N + c0);
+              if (sub > 0) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                  uint32_t v[32];
+                  tmem_ld32(paddr + 32 * h, v);
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) y[32 * h + j] = fmaxf(y[32 * h + j], __uint_as_float(v[j]));
+                }
+              }
+              if (sub < 3) {
+                tmem_st32(paddr, y);
+                tmem_st32(paddr + 32, y + 32);
+                tmem_wait_st();
+                continue;
               }
             }
-            if (sub < 3) {
-              tmem_st32(paddr, y);
-              tmem_st32(paddr + 32, y + 32);
-              tmem_wait_st();
-              continue;
+            for (int pass = 0; pass < 2; ++pass) {
+              uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
+              if (issuer) bulk_wait_read<1>();
+              epi_barrier();
+              uint8_t* rowp = sbuf + row * 128;
+#pragma unroll
+              for (int c = 0; c < 8; ++c) {
+                uint32_t w[4];
+#pragma unroll
+                for (int h2 = 0; h2 < 4; ++h2) {
+                  const float v0 = y[8 * c + 2 * h2], v1 = y[8 * c + 2 * h2 + 1];
+                  __half a0 = __float2half_rn(v0), a1 = __float2half_rn(v1);
+                  if (pass == 1) {
+                    a0 = __float2half_rn(v0 - __half2float(a0));
+                    a1 = __float2half_rn(v1 - __half2float(a1));
+                  }
+                  w[h2] = (uint32_t)__half_as_ushort(a0) | ((uint32_t)__half_as_ushort(a1) << 16);
+                }
+                *reinterpret_cast<uint4*>(rowp + ((c ^ (row & 7)) << 4)) =
+                    make_uint4(w[0], w[1], w[2], w[3]);
+              }
+              fence_proxy_async();
+              epi_barrier();
+              if (issuer) {
+                tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0,
+                             g.pool ? wb : w0, g.pool ? hb : h0, n0);
+                bulk_commit();
+              }
+              ++stores;
             }
           }
-          for (int pass = 0; pass < 2; ++pass) {
+          continue;
+        }
+        const int passes = g.split ? 2 : 1;
+#pragma unroll
+        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+          float y[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+            t = apply_act(t, g.relu, g.slope);
+            y[j] = t;
+          }
+          for (int pass = 0; pass < passes; ++pass) {
             uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
+            // the TMA store that used this staging tile two stores ago must have read it out
             if (issuer) bulk_wait_read<1>();
             epi_barrier();
             uint8_t* rowp = sbuf + row * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
-              uint32_t w[4];
-#pragma unroll
-              for (int h2 = 0; h2 < 4; ++h2) {
-                const float v0 = y[8 * c + 2 * h2], v1 = y[8 * c + 2 * h2 + 1];
-                __half a0 = __float2half_rn(v0), a1 = __float2half_rn(v1);
-                if (pass == 1) {
-                  a0 = __float2half_rn(v0 - __half2float(a0));
-                  a1 = __float2half_rn(v1 - __half2float(a1));
+              float4 o;
+              if (g.split) {
+                const float h0 = tf32_hi(y[4 * c]), h1 = tf32_hi(y[4 * c + 1]),
+                            h2 = tf32_hi(y[4 * c + 2]), h3 = tf32_hi(y[4 * c + 3]);
+                if (pass == 0) {
+                  o = make_float4(h0, h1, h2, h3);
+                } else {
+                  o = make_float4(tf32_lo(y[4 * c], h0), tf32_lo(y[4 * c + 1], h1),
+                                  tf32_lo(y[4 * c + 2], h2), tf32_lo(y[4 * c + 3], h3));
                 }
-                w[h2] = (uint32_t)__half_as_ushort(a0) | ((uint32_t)__half_as_ushort(a1) << 16);
+              } else {
+                o = make_float4(y[4 * c], y[4 * c + 1], y[4 * c + 2], y[4 * c + 3]);
               }
-              *reinterpret_cast<uint4*>(rowp + ((c ^ (row & 7)) << 4)) =
-                  make_uint4(w[0], w[1], w[2], w[3]);
+              *reinterpret_cast<float4*>(rowp + ((c ^ (row & 7)) << 4)) = o;  // 128B swizzle
             }
             fence_proxy_async();
             epi_barrier();
             if (issuer) {
-              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0,
-                           g.pool ? wb : w0, g.pool ? hb : h0, n0);
+              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
               bulk_commit();
             }
             ++stores;
           }
         }
-        continue;
       }
-      const int passes = g.split ? 2 : 1;
-#pragma unroll
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-        float y[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
-          t = apply_act(t, g.relu, g.slope);
-          y[j] = t;
-        }
-        for (int pass = 0; pass < passes; ++pass) {
-          uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
-          // the TMA store that used this staging tile two stores ago must have read it out
-          if (issuer) bulk_wait_read<1>();
-          epi_barrier();
-          uint8_t* rowp = sbuf + row * 128;
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            float4 o;
-            if (g.split) {
-              const float h0 = tf32_hi(y[4 * c]), h1 = tf32_hi(y[4 * c + 1]),
-                          h2 = tf32_hi(y[4 * c + 2]), h3 = tf32_hi(y[4 * c + 3]);
-              if (pass == 0) {
-                o = make_float4(h0, h1, h2, h3);
-              } else {
-                o = make_float4(tf32_lo(y[4 * c], h0), tf32_lo(y[4 * c + 1], h1),
-                                tf32_lo(y[4 * c + 2], h2), tf32_lo(y[4 * c + 3], h3));
-              }
-            } else {
-              o = make_float4(y[4 * c], y[4 * c + 1], y[4 * c + 2], y[4 * c + 3]);
-            }
-            *reinterpret_cast<float4*>(rowp + ((c ^ (row & 7)) << 4)) = o;  // 128B swizzle
-          }
-          fence_proxy_async();
-          epi_barrier();
-          if (issuer) {
-            tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
-            bulk_commit();
-          }
-          ++stores;
-        }
-      }
-     }
     }
     if (issuer) bulk_wait_all();
   }
