@@ -149,6 +149,64 @@ channel_contrib_conv_kernel(const float* __restrict__ z, const float* __restrict
   }
 }
 
+// Same, a thread owning a 2x2 block of output pixels: the 4x4 activation patch is loaded once
+// (16 values instead of 36 for the four pixels, and with a pool in front of the layer each value
+// is itself four loads and three max), the FMAs per pixel and their order are unchanged.
+// Requires even Hp, Wp.
+__global__ void __launch_bounds__(256)
+channel_contrib_conv2x2_kernel(const float* __restrict__ z, const float* __restrict__ wt,
+                               float* __restrict__ T, int B, int C, int H, int W, int pool,
+                               int C1, unsigned blocks) {
+  const int c = blockIdx.y;
+  const int Hp = pool ? H / 2 : H, Wp = pool ? W / 2 : W;
+  const int Hb = Hp / 2, Wb = Wp / 2;
+  const unsigned opp = (unsigned)C1 >> 2;
+  const unsigned o4 = threadIdx.x % opp;
+  const unsigned bl = threadIdx.x / opp;
+  const unsigned bpb = blockDim.x / opp;
+  const float4* w4 = reinterpret_cast<const float4*>(wt) + (long long)c * 9 * opp;
+  float4 wreg[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wreg[t] = w4[t * opp + o4];
+  float4* out4 = reinterpret_cast<float4*>(T) + (long long)c * ((long long)B * Hp * Wp) * opp;
+  for (unsigned blk = blockIdx.x * bpb + bl; blk < blocks; blk += gridDim.x * bpb) {
+    const int wb = (int)(blk % (unsigned)Wb);
+    const unsigned t = blk / (unsigned)Wb;
+    const int hb = (int)(t % (unsigned)Hb);
+    const int b = (int)(t / (unsigned)Hb);
+    const int h0 = 2 * hb, w0 = 2 * wb;
+    float patch[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int hh = h0 + i - 1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int ww = w0 + j - 1;
+        const bool in = hh >= 0 && hh < Hp && ww >= 0 && ww < Wp;
+        patch[i][j] = in ? zprime(z, b, c, hh, ww, C, H, W, pool) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const float zv = patch[s / 2 + r][s % 2 + q];
+          const float4 wv = wreg[r * 3 + q];
+          acc.x = fmaf(zv, wv.x, acc.x);
+          acc.y = fmaf(zv, wv.y, acc.y);
+          acc.z = fmaf(zv, wv.z, acc.z);
+          acc.w = fmaf(zv, wv.w, acc.w);
+        }
+      const unsigned long long pix =
+          ((unsigned long long)b * Hp + h0 + s / 2) * Wp + w0 + s % 2;
+      out4[pix * opp + o4] = acc;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 contrib_sum_kernel(const float* __restrict__ T, int C, long long M1, double* __restrict__ s_all) {
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < M1;
@@ -542,6 +600,18 @@ int tp_channel_contrib(const float* z, const float* wt, int64_t B, int64_t C, in
   TP_REQUIRE(pixels * (C1 / 4) < (1ll << 31), TP_ERR_LIMIT,
              "tp_channel_contrib: more than 2^31 items per channel");
   const long long opp = C1 / 4;
+  if (mode == 0 && opp <= 256 && (opp & (opp - 1)) == 0 && Hp % 2 == 0 && Wp % 2 == 0) {
+    const long long blocks = pixels / 4;
+    const long long bpb = 256 / opp;
+    long long bx = (blocks + bpb - 1) / bpb;
+    const long long cap = ((long long)sm_count() * 8 + C - 1) / C;  // ~8 CTAs/SM over all channels
+    if (bx > cap) bx = cap < 1 ? 1 : cap;
+    dim3 grid((unsigned)bx, (unsigned)C);
+    channel_contrib_conv2x2_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        z, wt, T, (int)B, (int)C, (int)H, (int)W, pool, (int)C1, (unsigned)blocks);
+    TP_LAUNCH_CHECK("channel_contrib_conv2x2_kernel");
+    return TP_OK;
+  }
   if (mode == 0 && opp <= 256 && (opp & (opp - 1)) == 0) {
     const long long ppb = 256 / opp;
     long long bx = (pixels + ppb - 1) / ppb;
