@@ -180,6 +180,28 @@ def gen_vgg():
     print("vgg16:", len(out), "arrays")
 
 
+def gen_mlp():
+    """The 784-2024-2024-10 LeakyReLU perceptron of the "Pruning Untrained Networks" notebook:
+    Taylor / Sensitivity / APoZ / WeightNorm and Shapley (sv=1) of both hidden layers on 16
+    examples."""
+    out = {}
+    model, shape = workloads.build("mlp")
+    loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=6)
+    for tag, layer in (("fc1", model.fc[1]), ("fc2", model.fc[3])):
+        mk = lambda cls, **kw: cls(model, loader, workloads.cross_entropy, "cpu", **kw)
+        out[f"{tag}/taylor"] = quiet(mk(TaylorAttributionMetric, reduction="none").run, layer, find_best_evaluation_module=True)
+        model.zero_grad()
+        out[f"{tag}/sensitivity"] = quiet(mk(SensitivityAttributionMetric, reduction="none").run, layer, find_best_evaluation_module=True)
+        model.zero_grad()
+        out[f"{tag}/apoz"] = quiet(mk(APoZAttributionMetric, reduction="none").run, layer, find_best_evaluation_module=True)
+        out[f"{tag}/weight_norm"] = quiet(mk(WeightNormAttributionMetric).run, layer)
+        np.random.seed(13)
+        out[f"{tag}/shapley16"] = quiet(mk(ShapleyAttributionMetric, sv_samples=1, reduction="none").run, layer, find_best_evaluation_module=True)
+        print("  mlp", tag, flush=True)
+    np.savez_compressed(os.path.join(HERE, "mlp.npz"), **out)
+    print("mlp:", len(out), "arrays")
+
+
 def gen_graph():
     """Host logic: evaluation-module choice and the VGG cascade graph, as module names."""
     lines = []
@@ -246,7 +268,7 @@ def gen_ablation():
 
 
 GROUPS = {"ablation": gen_ablation, "ops": gen_ops, "max_model": gen_max_model, "small_cnn": gen_small_cnn, "vgg": gen_vgg,
-          "graph": gen_graph, "prune": gen_prune}
+          "mlp": gen_mlp, "graph": gen_graph, "prune": gen_prune}
 
 if __name__ == "__main__":
     torch.set_num_threads(8)

@@ -167,6 +167,36 @@ def test_small_cnn_matches_reference():
                                g["fc1/weight_norm"], rtol=1e-5)
 
 
+# ------------------------------------------------------------------ MLP (mnist.py) vs reference
+@pytest.mark.parametrize("tag,layer_idx", [("fc1", 1), ("fc2", 3)])
+def test_mlp_matches_reference(tag, layer_idx):
+    """784-2024-2024-10 LeakyReLU perceptron: every metric against the unmodified reference's
+    CPU output (tests/golden/mlp.npz); Shapley runs on the engine (Linear + LeakyReLU epilogue,
+    dense incremental first layer)."""
+    g = gold("mlp.npz")
+    torch.manual_seed(0)
+    model, shape = workloads.build("mlp")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=6)
+    layer = model.fc[layer_idx]
+    mk = lambda cls, **kw: cls(model, loader, workloads.cross_entropy, DEV, **kw)
+    t = mk(TaylorAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=True)
+    model.zero_grad()
+    s = mk(SensitivityAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=True)
+    model.zero_grad()
+    a = mk(APoZAttributionMetric, reduction="none").run(layer, find_best_evaluation_module=True)
+    assert norm_err(t, g[f"{tag}/taylor"]) <= 1e-4 and norm_err(s, g[f"{tag}/sensitivity"]) <= 1e-4
+    assert float((a != g[f"{tag}/apoz"]).mean()) <= 1e-3   # sign flips of ~0 pre-activations
+    np.testing.assert_allclose(mk(WeightNormAttributionMetric).run(layer), g[f"{tag}/weight_norm"], rtol=1e-5)
+    np.random.seed(13)
+    m = mk(ShapleyAttributionMetric, sv_samples=1, reduction="none")
+    sv = m.run(layer, find_best_evaluation_module=True)
+    want = g[f"{tag}/shapley16"]
+    assert sv.shape == want.shape == (16, 2024) and sv.dtype == np.float64
+    assert np.abs(sv - want).max() <= 5e-6, np.abs(sv - want).max()   # loss scale, |loss| ~ 2.3
+    assert m.last_run_info["stacked"] is True
+
+
 # ------------------------------------------------------------------ configs 2/3: VGG16 vs reference
 def test_vgg16_scores_match_reference():
     g = gold("vgg16.npz")

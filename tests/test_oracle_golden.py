@@ -121,6 +121,32 @@ def test_shapley_fast_path_matches_reference_small_cnn():
     assert layer is model.features[0]
 
 
+@pytest.mark.parametrize("tag,layer_idx", [("fc1", 1), ("fc2", 3)])
+def test_oracle_matches_reference_on_the_mlp(tag, layer_idx):
+    """Third model family of the reference's experiments (mnist.py:9-35: Linear layers scored
+    after LeakyReLU): the oracle's whole-metric restatements against the unmodified reference."""
+    gold = load("mlp.npz")
+    model, shape = workloads.build("mlp")
+    loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=6)
+    layer, evaluation = model.fc[layer_idx], model.fc[layer_idx + 1]
+    for kind in ("taylor", "sensitivity", "apoz"):
+        model.zero_grad()
+        got = oracle.hook_scores(model, loader, workloads.cross_entropy, evaluation, kind)
+        ref = gold[f"{tag}/{kind}"]
+        assert got.shape == ref.shape == (16, 2024)
+        if kind == "apoz":
+            np.testing.assert_array_equal(got, ref)
+        else:
+            assert np.abs(got - ref).max() <= 1e-6 * np.abs(ref).max()
+    np.testing.assert_allclose(oracle.weight_norm(layer.weight.detach()), gold[f"{tag}/weight_norm"],
+                               rtol=1e-6)
+    np.random.seed(13)
+    sv = oracle.shapley_with_partial(model, loader, workloads.cross_entropy, 1, 16, module=evaluation)
+    ref = gold[f"{tag}/shapley16"]
+    assert sv.shape == ref.shape == (16, 2024) and sv.dtype == np.float64
+    assert np.abs(sv - ref).max() <= 1e-6 * np.abs(ref).max()
+
+
 def test_mask_stack_and_scatter_restate_the_loop():
     """prefix_mask_stack + loss_delta_scatter compose to shapley_with_partial's inner loops."""
     model, shape = workloads.build("small_cnn")
