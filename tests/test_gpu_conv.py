@@ -184,6 +184,73 @@ def test_native_tail_agrees_with_forward_partial(tag):
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 
 
+def test_engine_propagates_nan_like_aten():
+    """ReLU and max pooling keep a NaN (torch.relu / max_pool2d do; fmaxf would not): an fp16
+    overflow upstream (inf in hi, inf - inf = NaN in lo) has to reach the logits to be noticed."""
+    N, H, W, C = 128, 4, 4, 64
+    x = torch.randn((N, H, W, C), device=DEV)
+    w = torch.randn((C, 9 * C), device=DEV) / 24.0
+    one, zero = torch.ones(C, device=DEV), torch.zeros(C, device=DEV)
+    x_hi, x_lo = _lib.f16_split(x, 1.0)
+    w_hi, w_lo = _lib.f16_split(w, 1.0)
+    x_hi[5, 1, 2, 7] = float("inf")
+    x_lo[5, 1, 2, 7] = float("nan")
+    for pool in (False, True):
+        y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, 9, one, zero, True, split=True, pool=pool)
+        bad = ~torch.isfinite(y_hi.float() + y_lo.float())
+        assert bool(bad[5].any()) and not bool(bad[:5].any()) and not bool(bad[6:].any())
+    raw = torch.randn((4, 4, 4, 8), device=DEV)
+    raw[2, 1, 1, 3] = float("nan")
+    hi, lo = _lib.maxpool2_split_nhwc(raw, half=True, scale=1.0)
+    assert bool(torch.isnan(hi[2, 0, 0, 3])) and int(torch.isnan(hi).sum()) == 1
+    want = F.max_pool2d(raw.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+    assert torch.equal(torch.isnan(hi), torch.isnan(want))
+
+
+def test_fp16_range_failure_falls_back_to_tf32_with_the_same_permutations(monkeypatch):
+    """An activation that leaves fp16's range under some mask makes scores non-finite; the run is
+    then repeated on the TF32 flavour with the numpy RNG rewound, so the caller gets the table —
+    and the RNG state — of a run that had used TF32 from the start."""
+    import copy
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric, native_tail
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        twin = copy.deepcopy(model)
+        model.to(DEV)
+        twin.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=2)
+        mk = lambda mdl: ShapleyAttributionMetric(mdl, loader, workloads.cross_entropy, DEV,
+                                                  sv_samples=2, reduction="none")
+        layer = model.features[30]
+        np.random.seed(1)
+        m = mk(model)
+        m.run(layer, find_best_evaluation_module=True)           # builds + caches the fp16 plan
+        assert m.last_run_info["f16"] and m.last_run_info["native_tail"]
+        (plan,) = [e[1] for e in native_tail._PLANS[model].values()]
+        plan.steps[1]["s_in"] *= 2.0 ** 14                       # next layer's input overflows
+        np.random.seed(7)
+        m = mk(model)
+        sv = m.run(layer, find_best_evaluation_module=True)
+        state = np.random.get_state()[1].copy()
+        assert np.isfinite(sv).all() and m.last_run_info["f16"] is False and m._f16_banned
+        # the same job on a model whose plan never had the fp16 flavour
+        monkeypatch.setenv("TORCHPRUNER_B200_F16", "0")
+        np.random.seed(1)
+        mk(twin).run(twin.features[30], find_best_evaluation_module=True)   # caches its plan too
+        np.random.seed(7)
+        m2 = mk(twin)
+        want = m2.run(twin.features[30], find_best_evaluation_module=True)
+        assert m2.last_run_info["f16"] is False
+        np.testing.assert_array_equal(sv, want)
+        assert np.array_equal(np.random.get_state()[1], state)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def test_native_tail_declines_unsupported_models():
     from torchpruner_b200 import workloads
     from torchpruner_b200.attributions.native_tail import NativeTail

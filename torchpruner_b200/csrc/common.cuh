@@ -59,6 +59,12 @@ struct Tuning {
 Tuning& tuning();
 
 // ---- device helpers -----------------------------------------------------------------
+// max and ReLU as ATen defines them: a NaN operand gives NaN (fmaxf would drop it).  The engine
+// relies on this to notice an fp16 overflow: inf - inf = NaN in the lo half, which must reach
+// the logits instead of being flattened to 0 by the next ReLU or pooling window.
+__device__ __forceinline__ float nan_max(float a, float b) { return (a > b || a != a) ? a : b; }
+__device__ __forceinline__ float nan_relu(float t) { return t < 0.f ? 0.f : t; }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

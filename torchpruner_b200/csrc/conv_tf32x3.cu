@@ -222,7 +222,7 @@ __device__ __forceinline__ float tf32_hi(float x) {
 __device__ __forceinline__ float tf32_lo(float x, float hi) { return tf32_hi(x - hi); }
 // 0: identity, 1: ReLU, 2: LeakyReLU (x > 0 ? x : x * slope, as ATen computes it)
 __device__ __forceinline__ float apply_act(float t, int act, float slope) {
-  if (act == 1) return fmaxf(t, 0.f);
+  if (act == 1) return nan_relu(t);
   if (act == 2) return t > 0.f ? t : t * slope;
   return t;
 }
@@ -725,7 +725,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                   uint32_t v[32];
                   tmem_ld32(paddr + 32 * h, v);
 #pragma unroll
-                  for (int j = 0; j < 32; ++j) y[32 * h + j] = fmaxf(y[32 * h + j], __uint_as_float(v[j]));
+                  for (int j = 0; j < 32; ++j) y[32 * h + j] = nan_max(y[32 * h + j], __uint_as_float(v[j]));
                 }
               }
               if (sub < 3) {
@@ -876,7 +876,7 @@ mask_stack_nhwc_kernel(const float* __restrict__ z, const int32_t* __restrict__ 
     float v;
     if (pool) {
       const float* p0 = src + (2 * ho) * W + 2 * wo;
-      v = fmaxf(fmaxf(p0[0], p0[1]), fmaxf(p0[W], p0[W + 1]));
+      v = nan_max(nan_max(p0[0], p0[1]), nan_max(p0[W], p0[W + 1]));
     } else {
       v = src[ho * W + wo];
     }
@@ -906,10 +906,10 @@ maxpool2_split_nhwc_kernel(const float* __restrict__ x, long long N, int H, int 
     const long long base = ((n * H + 2 * ho) * W + 2 * wo) * C4 + c4;
     const float4 a = x4[base], b = x4[base + C4], c = x4[base + (long long)W * C4],
                  d = x4[base + (long long)W * C4 + C4];
-    const float m0 = fmaxf(fmaxf(a.x, b.x), fmaxf(c.x, d.x));
-    const float m1 = fmaxf(fmaxf(a.y, b.y), fmaxf(c.y, d.y));
-    const float m2 = fmaxf(fmaxf(a.z, b.z), fmaxf(c.z, d.z));
-    const float m3 = fmaxf(fmaxf(a.w, b.w), fmaxf(c.w, d.w));
+    const float m0 = nan_max(nan_max(a.x, b.x), nan_max(c.x, d.x));
+    const float m1 = nan_max(nan_max(a.y, b.y), nan_max(c.y, d.y));
+    const float m2 = nan_max(nan_max(a.z, b.z), nan_max(c.z, d.z));
+    const float m3 = nan_max(nan_max(a.w, b.w), nan_max(c.w, d.w));
     SplitStore<HALF>::put(hi, lo, 4 * e, m0, scale);
     SplitStore<HALF>::put(hi, lo, 4 * e + 1, m1, scale);
     SplitStore<HALF>::put(hi, lo, 4 * e + 2, m2, scale);

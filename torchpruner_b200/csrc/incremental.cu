@@ -46,7 +46,7 @@ __device__ __forceinline__ float zprime(const float* __restrict__ z, int b, int 
   const float* src = z + (((long long)b * C + c) * H) * W;
   if (!pool) return src[h * W + w];
   const float* p0 = src + (2 * h) * W + 2 * w;
-  return fmaxf(fmaxf(p0[0], p0[1]), fmaxf(p0[W], p0[W + 1]));
+  return nan_max(nan_max(p0[0], p0[1]), nan_max(p0[W], p0[W + 1]));
 }
 
 // mode 0: conv3x3 pad 1 over the Hp x Wp grid, 9 taps, output pixel = (b, h, w)
@@ -230,7 +230,7 @@ struct PrefixGeom {
 
 __device__ __forceinline__ float affine_act(double run, float a, float b, int act, float slope) {
   float t = fmaf((float)run, a, b);
-  if (act == 1) return fmaxf(t, 0.f);
+  if (act == 1) return nan_relu(t);
   if (act == 2) return t > 0.f ? t : t * slope;
   return t;
 }
@@ -305,10 +305,10 @@ prefix_contrib_stack_kernel(const float* __restrict__ T, const int64_t* __restri
           run[s][2] -= (double)t.z;
           run[s][3] -= (double)t.w;
           if (g.emit) {
-            y.x = fmaxf(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
-            y.y = fmaxf(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
-            y.z = fmaxf(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
-            y.w = fmaxf(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
+            y.x = nan_max(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
+            y.y = nan_max(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
+            y.z = nan_max(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
+            y.w = nan_max(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
           }
         }
         if (g.emit) {
@@ -492,10 +492,10 @@ prefix_direct_conv_kernel(const float* __restrict__ zc, const float* __restrict_
           v.z = affine_act(run[s][2], a.z, bsh.z, g.relu, g.slope);
           v.w = affine_act(run[s][3], a.w, bsh.w, g.relu, g.slope);
           if (BLK == 2 && g.pool) {
-            y.x = fmaxf(y.x, v.x);
-            y.y = fmaxf(y.y, v.y);
-            y.z = fmaxf(y.z, v.z);
-            y.w = fmaxf(y.w, v.w);
+            y.x = nan_max(y.x, v.x);
+            y.y = nan_max(y.y, v.y);
+            y.z = nan_max(y.z, v.z);
+            y.w = nan_max(y.w, v.w);
           } else {
             emit_split4<HALF>(v, g.out_scale, out_hi_v, out_lo_v,
                               (long long)p * m_out + pix[s] * g.C1 + o4 * 4);
