@@ -582,6 +582,25 @@ def test_ablation_curve_matches_reference(cfg, tag, n, native):
     assert int((acc2 != want_acc).sum()) <= 1
 
 
+def test_ablation_curve_redoes_an_fp16_overflow_in_tf32():
+    from torchpruner_b200.ablation import ablation_curve
+    from torchpruner_b200.attributions import native_tail
+
+    g = gold("ablation.npz")
+    model, shape = workloads.build("vgg16_cifar")
+    model.to(DEV)
+    x, y = next(iter(workloads.synthetic_batches(shape, n=32, batch_size=32, seed=8)))
+    module = model.features[34]
+    ranking = np.random.RandomState(4).permutation(module.out_channels)
+    ablation_curve(model, x.to(DEV), y.to(DEV), module, ranking)          # caches the fp16 plan
+    (plan,) = [e[1] for e in native_tail._PLANS[model].values()]
+    assert plan.use_f16
+    plan.steps[1]["s_in"] *= 2.0 ** 14                                     # force the overflow
+    loss, acc = ablation_curve(model, x.to(DEV), y.to(DEV), module, ranking)
+    assert plan.use_f16 is False and np.isfinite(loss).all()
+    np.testing.assert_allclose(loss, g["vgg16_cifar/loss"], rtol=2e-6)
+
+
 def test_adam_state_is_sliced_with_the_parameter():
     """optimizer state beyond SGD / param_groups[0] follows the pruned parameter."""
     (x, y), _ = simple_model()

@@ -104,10 +104,18 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
                 ct = (out.argmax(dim=1).view(P, B) == y.view(1, B)).sum(1).to(torch.int32)
             losses.append(ml)
             counts.append(ct)
+        used_f16 = native is not None and native.use_f16
         if native is not None:
             native.release()
         if not losses:
             return np.zeros(0, np.float32), np.zeros(0, np.float32)
         loss = torch.cat(losses).cpu().numpy()
+        if used_f16 and not np.isfinite(loss).all():
+            # an activation left fp16's range under some mask (NaN reaches the loss, see
+            # common.cuh nan_relu): the cached plan drops to its TF32 flavour and the curve is redone
+            native.use_f16 = False
+            return ablation_curve(model, x, y, module, ranking, criterion,
+                                  find_best_evaluation_module, max_stack_bytes, max_stack,
+                                  native_tail, incremental_first)
         acc = (torch.cat(counts).float() / len(y)).cpu().numpy()  # `.sum().float() / len(y_test)`
         return loss, acc
