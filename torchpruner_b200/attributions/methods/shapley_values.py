@@ -3,7 +3,6 @@ import os
 
 import numpy as np
 import torch
-import torch.nn.functional as F
 from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
@@ -126,8 +125,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         if not (logits.dim() == 2 and y.dim() == 1 and y.dtype == torch.int64
                 and logits.dtype == torch.float32 and y.numel() == logits.shape[0]):
             return False
-        if self.criterion is F.cross_entropy:
-            return True
+        # (also for F.cross_entropy itself: targets equal to its ignore_index have loss 0 there and
+        # are out of range for the kernel, which is exactly what the probe catches)
         B, K = logits.shape
         probe = torch.empty(B, dtype=torch.float32, device=logits.device)
         scratch_prev = torch.zeros(B, dtype=torch.float32, device=logits.device)
