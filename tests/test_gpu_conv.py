@@ -1,5 +1,8 @@
 """The fp32-accurate tensor-core layer engine (tp_conv_tf32x3 and companions) against float64
 convolutions, through the C-ABI."""
+import contextlib
+import io
+
 import numpy as np
 import pytest
 import torch
@@ -180,6 +183,60 @@ def test_native_tail_agrees_with_forward_partial(tag):
             diff = np.abs(tables[key] - ref).max()
             print(tag, key, "max |native - forward_partial| =", diff, "max |score| =", np.abs(ref).max())
             assert diff <= 2e-5   # differences of losses ~2.3: a few fp32 ulps of the loss
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+def test_cached_plan_is_dropped_when_the_model_changes():
+    """A cached plan holds prepared copies of the weights: an in-place update (optimizer step),
+    pruning (``param.data`` replaced) or a BatchNorm mode switch must all invalidate it."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+    from torchpruner_b200.pruner import Pruner
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+        layer = model.features[30]
+
+        def run(native):
+            np.random.seed(3)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                         reduction="none")
+            m.native_tail = native
+            return m.run(layer, find_best_evaluation_module=True), m.last_run_info
+
+        first, info = run("auto")
+        assert info["native_tail"] and not info["native"].get("cached")
+        _, info = run("auto")
+        assert info["native"].get("cached") is True
+        with torch.no_grad():                      # what an optimizer step does
+            model.classifier[6].weight.mul_(3.0)
+            model.features[38].running_mean.add_(0.05)
+        got, info = run("auto")
+        assert info["native_tail"] and not info["native"].get("cached")
+        want, _ = run(False)
+        assert np.abs(got - want).max() <= 2e-5 and np.abs(got - first).max() > 1e-5
+        with contextlib.redirect_stdout(io.StringIO()):
+            pruner = Pruner(model, shape, DEV)
+            pruner.prune_model(model.features[37], list(range(64)),
+                               [model.features[38], model.features[40]])
+        assert model.features[37].out_channels == 512     # stale, as in the reference
+        got, info = run("auto")
+        assert info["native_tail"] and not info["native"].get("cached")   # 448 channels: tileable
+        want, _ = run(False)
+        assert np.abs(got - want).max() <= 2e-5
+        with contextlib.redirect_stdout(io.StringIO()):
+            pruner.prune_model(model.features[37], [0, 5, 9], [model.features[38], model.features[40]])
+        got, info = run("auto")                    # 445 channels: not a multiple of 64 any more
+        assert info["native_tail"] is False and info["stacked"] is True
+        assert np.isfinite(got).all()
+        model.features[38].train()                 # train-mode BatchNorm: no stacking, no engine
+        _, info = run("auto")
+        assert info["native_tail"] is False and info["stacked"] is False
     finally:
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 

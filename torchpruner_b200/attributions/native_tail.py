@@ -17,15 +17,15 @@ BatchNorm (eval) and the conv/linear bias are folded into one per-channel scale/
 the kernel's epilogue; ReLU is fused; a MaxPool that follows is a separate NHWC kernel that also
 re-splits the result into its TF32 hi/lo pair.
 """
+import logging
+import math
+import os
 import weakref
 
 import torch
 import torch.nn as nn
 
 from .. import _lib
-
-import math
-import os
 
 VERIFY_RTOL = 2e-5   # on logits, relative to their largest magnitude
 VERIFY_ARBITRATE_BELOW = 1e-3   # above this the difference is structural, not rounding
@@ -155,6 +155,9 @@ class NativeTail:
             return cls._build(model, module, z)
         except _Unsupported:
             return None
+        except Exception as exc:   # a model this tracer misreads must not break scoring
+            logging.getLogger(__name__).debug("native tail not built: %r", exc)
+            return None
 
     @classmethod
     def _build(cls, model, module, z):
@@ -204,21 +207,24 @@ class NativeTail:
             if isinstance(m, nn.Conv2d):
                 if flat or m.kernel_size != (3, 3) or m.stride != (1, 1) or m.padding != (1, 1) or \
                         m.dilation != (1, 1) or m.groups != 1 or m.padding_mode != "zeros" or \
-                        m.in_channels != C:
+                        m.weight.shape[1] != C:
                     raise _Unsupported("conv geometry")
-                w = m.weight.detach().float().permute(0, 2, 3, 1).reshape(m.out_channels, 9 * C)
-                taps, cout = 9, m.out_channels
+                # sizes from the weight itself: the reference's pruner (and ours, for parity) slices
+                # tensors but leaves out_channels / in_features & co. at their old values
+                cout = m.weight.shape[0]
+                w = m.weight.detach().float().permute(0, 2, 3, 1).reshape(cout, 9 * C)
+                taps = 9
                 bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
             elif isinstance(m, nn.Linear):
                 calls_in = calls[i][1]
-                if calls_in.dim() != 2 or m.in_features != C * H * W:
+                if calls_in.dim() != 2 or m.weight.shape[1] != C * H * W:
                     raise _Unsupported("linear geometry")
                 w = m.weight.detach().float()
                 if H * W > 1:  # NCHW flatten order -> NHWC flatten order
-                    w = w.view(m.out_features, C, H * W).permute(0, 2, 1).reshape(m.out_features, -1)
+                    w = w.view(w.shape[0], C, H * W).permute(0, 2, 1).reshape(w.shape[0], -1)
                 C, H, W = C * H * W, 1, 1
                 flat = True
-                taps, cout = 1, m.out_features
+                taps, cout = 1, m.weight.shape[0]
                 bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
             else:
                 raise _Unsupported(f"unsupported layer {type(m).__name__}")
@@ -310,7 +316,7 @@ class NativeTail:
                     first = {"mode": 0, "Hp": H, "Wp": W}
                 else:           # [Cout, Cz*S] (NCHW flatten order) -> [Cz, S, Cout]
                     cz = z.shape[1]
-                    sp = m.in_features // cz
+                    sp = m.weight.shape[1] // cz
                     wt = m.weight.detach().float().view(cout, cz, sp).permute(1, 2, 0)
                     first = {"mode": 1, "Hp": 1, "Wp": 1}
                 first.update(wt=wt.contiguous(), C1=cout, scale=scale, shift=shift, relu=relu,
