@@ -241,6 +241,47 @@ def test_cached_plan_is_dropped_when_the_model_changes():
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 
 
+def test_score_then_prune_workflow_engine_on_vs_off():
+    """The reference's layerwise loop (notebook "VGG16 - Layerwise robustness"): score a layer,
+    prune its weakest units, move to the next entry of the pruning graph — the later layers are
+    then scored on an already pruned model.  Engine on and engine off must pick the same units
+    and end with the same model."""
+    import copy
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+    from torchpruner_b200.pruner import Pruner
+    from torchpruner_b200.utils import get_vgg_pruning_graph
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        base, shape = workloads.build("vgg16_cifar")
+        models = {True: copy.deepcopy(base).to(DEV), False: copy.deepcopy(base).to(DEV)}
+        loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+        picked = {True: [], False: []}
+        used_engine = 0
+        for native, model in models.items():
+            pruner = Pruner(model, shape, DEV)
+            graph = get_vgg_pruning_graph(model)
+            for step, (module, cascade) in enumerate(graph[:5]):   # fc2, fc1, conv13, conv12, conv11
+                np.random.seed(100 + step)
+                m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1)
+                m.native_tail = "auto" if native else False
+                with contextlib.redirect_stdout(io.StringIO()):
+                    scores = m.run(module, find_best_evaluation_module=True)
+                    used_engine += int(m.last_run_info["native_tail"])
+                    weakest = np.argsort(scores)[:64]
+                    pruner.prune_model(module, weakest.tolist(), cascading_modules=cascade)
+                picked[native].append((scores, np.sort(weakest)))
+        assert used_engine >= 4
+        for (s_on, w_on), (s_off, w_off) in zip(picked[True], picked[False]):
+            assert np.abs(s_on - s_off).max() <= 2e-6          # means of loss differences
+            # the weakest-64 sets agree except where two scores tie within that rounding
+            assert len(set(w_on) ^ set(w_off)) <= 4
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def test_engine_propagates_nan_like_aten():
     """ReLU and max pooling keep a NaN (torch.relu / max_pool2d do; fmaxf would not): an fp16
     overflow upstream (inf in hi, inf - inf = NaN in lo) has to reach the logits to be noticed."""
