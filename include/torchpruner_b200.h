@@ -175,14 +175,16 @@ int64_t tp_conv_tf32x3_flops(int64_t N, int64_t H, int64_t W, int64_t Cin, int64
 /* hi[i] = rn_tf32(x[i]), lo[i] = rn_tf32(x[i] - hi[i]); hi + lo == x up to 2^-23 relative. */
 int tp_tf32_split(const float* x, int64_t n, float* hi, float* lo, tp_stream_t stream);
 
-/* K5 for the engine above: z is NCHW [B,C,H,W]; out_hi/out_lo are NHWC [P*B, H', W', C] holding
- * the TF32 split of the (optionally 2x2 max-pooled, pool != 0) activation with channels c such
- * that inv_perm[c] <= k0+p zeroed in copy p (k0 = -1 makes copy 0 the unmasked activation).
+/* K5 for the engine above: z is NCHW [B,C,H,W]; out_hi/out_lo are NHWC [P*B, H', W', C_pad]
+ * holding the TF32 split of the (optionally 2x2 max-pooled, pool != 0) activation with channels c
+ * such that inv_perm[c] <= k0+p zeroed in copy p (k0 = -1 makes copy 0 the unmasked activation).
+ * C_pad >= C: channels C..C_pad-1 are zeros (the engine pads channel counts to a multiple of 64
+ * so that layers whose width pruning left at, say, 48 or 445 still fit its tiles).
  * Replaces shapley_values.py:53-56 like
  * tp_prefix_mask_stack does, plus the layout change and a leading MaxPool2d(2). */
 int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
-                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
-                       tp_stream_t stream);
+                       int64_t C, int64_t H, int64_t W, int pool, int64_t C_pad, float* out_hi,
+                       float* out_lo, tp_stream_t stream);
 
 /* MaxPool2d(2) over NHWC raw fp32 [N,H,W,C] followed by the TF32 split -> [N,H/2,W/2,C]. */
 int tp_maxpool2_split_nhwc(const float* x, int64_t N, int64_t H, int64_t W, int64_t C, float* hi,
@@ -215,7 +217,7 @@ int tp_conv_pool2_fusable(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t 
 int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_stream_t stream);
 int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
                            int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
-                           void* out_hi, void* out_lo, tp_stream_t stream);
+                           int64_t C_pad, void* out_hi, void* out_lo, tp_stream_t stream);
 int tp_maxpool2_split_nhwc_f16(const float* x, int64_t N, int64_t H, int64_t W, int64_t C,
                                float scale, void* hi, void* lo, tp_stream_t stream);
 int tp_prefix_contrib_stack_f16(const float* T, const int64_t* perm, int64_t k0, int64_t P,

@@ -231,9 +231,10 @@ def test_cached_plan_is_dropped_when_the_model_changes():
         assert np.abs(got - want).max() <= 2e-5
         with contextlib.redirect_stdout(io.StringIO()):
             pruner.prune_model(model.features[37], [0, 5, 9], [model.features[38], model.features[40]])
-        got, info = run("auto")                    # 445 channels: not a multiple of 64 any more
-        assert info["native_tail"] is False and info["stacked"] is True
-        assert np.isfinite(got).all()
+        got, info = run("auto")                    # 445 channels: zero-padded to 448 inside the engine
+        assert info["native_tail"] and info["incremental_first"]
+        want, _ = run(False)
+        assert np.abs(got - want).max() <= 2e-5
         model.features[38].train()                 # train-mode BatchNorm: no stacking, no engine
         _, info = run("auto")
         assert info["native_tail"] is False and info["stacked"] is False
@@ -278,6 +279,50 @@ def test_score_then_prune_workflow_engine_on_vs_off():
             assert np.abs(s_on - s_off).max() <= 2e-6          # means of loss differences
             # the weakest-64 sets agree except where two scores tie within that rounding
             assert len(set(w_on) ^ set(w_off)) <= 4
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+@pytest.mark.parametrize("widths", [(48, 80, 24), (64, 100, 12)])
+def test_native_tail_pads_odd_channel_counts(widths):
+    """Layer widths that are not multiples of the 64-channel k-block (what pruning leaves
+    behind): the engine zero-pads its own copies of activations and weights."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    a, b, c = widths
+
+    class Net(workloads._PartialSequential):
+        def __init__(self):
+            super().__init__()
+            self.features = torch.nn.Sequential(
+                torch.nn.Conv2d(3, a, 3, padding=1), torch.nn.BatchNorm2d(a), torch.nn.ReLU(),
+                torch.nn.Conv2d(a, b, 3, padding=1), torch.nn.BatchNorm2d(b), torch.nn.ReLU(),
+                torch.nn.MaxPool2d(2),
+                torch.nn.Conv2d(b, c, 3, padding=1), torch.nn.LeakyReLU(0.1), torch.nn.MaxPool2d(2))
+            self.classifier = torch.nn.Sequential(torch.nn.Linear(c * 4, 36), torch.nn.ReLU(),
+                                                  torch.nn.Linear(36, 10))
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        torch.manual_seed(a)
+        model = Net()
+        workloads.warm_batchnorm(model, (3, 8, 8), n=32)
+        model.to(DEV)
+        loader = workloads.synthetic_batches((3, 8, 8), n=24, batch_size=24, seed=2)
+        for layer in (model.features[0], model.features[3], model.features[7], model.classifier[0]):
+            tables = {}
+            for native in ("auto", False):
+                np.random.seed(9)
+                m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=2,
+                                             reduction="none")
+                m.native_tail = native
+                with contextlib.redirect_stdout(io.StringIO()):
+                    tables[native] = m.run(layer, find_best_evaluation_module=True)
+                assert m.last_run_info["native_tail"] is bool(native), (layer, m.last_run_info)
+            assert np.abs(tables["auto"] - tables[False]).max() <= 2e-5
+            assert np.abs(tables[False]).max() > 1e-4
     finally:
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 

@@ -61,7 +61,7 @@ _SIGNATURES = {
     "tp_conv_tf32x3_flops": (_i64, [_i64, _i64, _i64, _i64, _i64, ctypes.c_int]),
     "tp_tf32_split": (ctypes.c_int, [_vp, _i64, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, ctypes.c_int,
-                                          _vp, _vp, _vp]),
+                                          _i64, _vp, _vp, _vp]),
     "tp_maxpool2_split_nhwc": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp]),
     "tp_conv_f16x3": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp, ctypes.c_int, _i64,
                                      _vp, _vp, ctypes.c_int, ctypes.c_float, ctypes.c_float, _vp, _vp,
@@ -72,7 +72,7 @@ _SIGNATURES = {
     "tp_conv_pool2_fusable": (ctypes.c_int, [_i64, _i64, _i64, _i64, _i64]),
     "tp_f16_split": (ctypes.c_int, [_vp, _i64, ctypes.c_float, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
-                                              ctypes.c_int, ctypes.c_float, _vp, _vp, _vp]),
+                                              ctypes.c_int, ctypes.c_float, _i64, _vp, _vp, _vp]),
     "tp_maxpool2_split_nhwc_f16": (ctypes.c_int, [_vp, _i64, _i64, _i64, _i64, ctypes.c_float, _vp,
                                                   _vp, _vp]),
     "tp_prefix_contrib_stack_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _i64, _i64,
@@ -465,15 +465,19 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
     return y_hi, y_lo
 
 
-def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo, scale=1.0):
+def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo, scale=1.0, c_pad=None):
     """NHWC TF32-split stack of P prefix-masked copies of the NCHW activation z (optionally
-    2x2 max-pooled first).  out_*: preallocated, at least P*B*H'*W'*C floats."""
+    2x2 max-pooled first), channels zero-padded to c_pad.  out_*: preallocated, at least
+    P*B*H'*W'*c_pad elements."""
     z = _cuda_f32(z, "z")
     if z.dim() != 4:
         raise TorchPrunerB200Error("mask_stack_nhwc expects a [B,C,H,W] activation")
     B, C, H, W = z.shape
+    Cp = C if c_pad is None else int(c_pad)
+    if Cp < C:
+        raise TorchPrunerB200Error("mask_stack_nhwc: c_pad must be at least the channel count")
     Ho, Wo = (H // 2, W // 2) if pool else (H, W)
-    need = P * B * Ho * Wo * C
+    need = P * B * Ho * Wo * Cp
     if out_hi.numel() < need or out_lo.numel() < need:
         raise TorchPrunerB200Error("mask_stack_nhwc: output buffers too small")
     esz = out_hi.element_size()
@@ -481,13 +485,13 @@ def mask_stack_nhwc(z, inv_perm, k0, P, pool, out_hi, out_lo, scale=1.0):
         if out_hi.dtype == torch.float16:
             _check(load().tp_mask_stack_nhwc_f16(
                 z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H, W, int(bool(pool)),
-                float(scale), out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)),
+                float(scale), Cp, out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)),
                 "tp_mask_stack_nhwc_f16")
         else:
             _check(load().tp_mask_stack_nhwc(
                 z.data_ptr(), inv_perm.data_ptr(), int(k0), int(P), B, C, H, W, int(bool(pool)),
-                out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)), "tp_mask_stack_nhwc")
-    shape = (P * B, Ho, Wo, C)
+                Cp, out_hi.data_ptr(), out_lo.data_ptr(), _stream(z)), "tp_mask_stack_nhwc")
+    shape = (P * B, Ho, Wo, Cp)
     return out_hi[:need].view(shape), out_lo[:need].view(shape)
 
 

@@ -51,6 +51,23 @@ class _Unsupported(Exception):
     pass
 
 
+CHANNEL_GRANULE = 64   # one 128-byte k-block of fp16 operands; a multiple of the TF32 one (32)
+
+
+def _pad(n):
+    return -(-int(n) // CHANNEL_GRANULE) * CHANNEL_GRANULE
+
+
+def _pad_to(t, dim, size):
+    """``t`` zero-padded along ``dim`` to ``size`` entries."""
+    extra = size - t.shape[dim]
+    if extra <= 0:
+        return t
+    shape = list(t.shape)
+    shape[dim] = extra
+    return torch.cat([t, t.new_zeros(shape)], dim)
+
+
 # model -> {(id(module), activation shape): (signature, plan or None, info)}.  A plan (traced,
 # weight-prepared and verified against forward_partial) stays valid exactly as long as no
 # parameter or buffer of the model has been written, replaced or resized and no BatchNorm/Dropout
@@ -180,7 +197,12 @@ class NativeTail:
             raise _Unsupported("output is not the last layer's output")
 
         mods = [c[0] for c in calls]
+        # C: channels of the activation as the model sees it; Cp: channels of the engine's NHWC
+        # copy of it, zero-padded to the kernels' granule.  Padded weight rows/columns are zero
+        # and padded outputs get scale 1 / shift 0, so they stay exactly 0 through ReLU and
+        # pooling: any width (48 or 445 channels after pruning) runs on the same tiles.
         C = z.shape[1]
+        Cp = _pad(C)
         H, W = (z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1)
         i = 0
         pool_first = False
@@ -212,25 +234,31 @@ class NativeTail:
                 # sizes from the weight itself: the reference's pruner (and ours, for parity) slices
                 # tensors but leaves out_channels / in_features & co. at their old values
                 cout = m.weight.shape[0]
-                w = m.weight.detach().float().permute(0, 2, 3, 1).reshape(cout, 9 * C)
+                w4 = _pad_to(_pad_to(m.weight.detach().float(), 1, Cp), 0, _pad(cout))
+                w = w4.permute(0, 2, 3, 1).reshape(w4.shape[0], 9 * Cp)
                 taps = 9
                 bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
             elif isinstance(m, nn.Linear):
                 calls_in = calls[i][1]
                 if calls_in.dim() != 2 or m.weight.shape[1] != C * H * W:
                     raise _Unsupported("linear geometry")
-                w = m.weight.detach().float()
-                if H * W > 1:  # NCHW flatten order -> NHWC flatten order
-                    w = w.view(w.shape[0], C, H * W).permute(0, 2, 1).reshape(w.shape[0], -1)
-                C, H, W = C * H * W, 1, 1
+                cout = m.weight.shape[0]
+                # NCHW flatten order -> NHWC flatten order of the padded activation; the layer that
+                # produces the logits keeps its true width (its output is the unsplit fp32 result)
+                produces_logits = all(isinstance(r, (nn.Dropout, nn.Identity)) for r in mods[i + 1:])
+                w = _pad_to(m.weight.detach().float().view(cout, C, H * W), 1, Cp)
+                w = _pad_to(w, 0, cout if produces_logits else _pad(cout))
+                w = w.permute(0, 2, 1).reshape(w.shape[0], -1)
+                w4 = None
+                C, Cp, H, W = C * H * W, Cp * H * W, 1, 1
                 flat = True
-                taps, cout = 1, m.weight.shape[0]
+                taps = 1
                 bias = m.bias.detach().float() if m.bias is not None else torch.zeros(cout, device=dev)
             else:
                 raise _Unsupported(f"unsupported layer {type(m).__name__}")
-            if (C % 32 if taps == 9 else C % 4) or 128 % W or \
-                    not ((128 // W) % H == 0 or H % (128 // W) == 0):
-                raise _Unsupported("channel / spatial size not tileable")
+            if 128 % W or not ((128 // W) % H == 0 or H % (128 // W) == 0):
+                raise _Unsupported("spatial size not tileable")
+            cout_p = w.shape[0]
             scale = torch.ones(cout, device=dev)
             shift = bias.clone()
             bn_used = None
@@ -265,19 +293,20 @@ class NativeTail:
             # zeros.  It is exactly a dense map from the 4*Cin inputs of the image to its 4*Cout
             # outputs, and NHWC [N,2,2,C] already is that [N, 4C] matrix, so the layer runs as a
             # linear one with the weight re-indexed (no data movement, 16/36 of the MMAs).
+            scale = torch.cat([scale, torch.ones(cout_p - cout, device=dev)])
+            shift = torch.cat([shift, torch.zeros(cout_p - cout, device=dev)])
             dense2x2 = taps == 9 and H == 2 and W == 2
-            k_cin, k_cout, k_taps = C, cout, taps
+            k_cin, k_cout, k_taps = Cp, cout_p, taps
             if dense2x2:
-                w4 = m.weight.detach().float()
-                wd = torch.zeros((2, 2, cout, 2, 2, C), device=dev)
+                wd = torch.zeros((2, 2, cout_p, 2, 2, Cp), device=dev)
                 for h in range(2):
                     for ww in range(2):
                         for h2 in range(2):
                             for w2 in range(2):
                                 wd[h, ww, :, h2, w2, :] = w4[:, :, h2 - h + 1, w2 - ww + 1]
-                w = wd.reshape(4 * cout, 4 * C)
+                w = wd.reshape(4 * cout_p, 4 * Cp)
                 scale, shift = scale.repeat(4), shift.repeat(4)
-                k_cin, k_cout, k_taps = 4 * C, 4 * cout, 1
+                k_cin, k_cout, k_taps = 4 * Cp, 4 * cout_p, 1
             key = (_tensor_key(m.weight, m.bias) + (
                 _tensor_key(bn_used.weight, bn_used.bias, bn_used.running_mean, bn_used.running_var)
                 if bn_used is not None else ()), w.shape[1], H * W if taps == 1 else 0, dense2x2)
@@ -302,38 +331,34 @@ class NativeTail:
                 s_in = _pow2_scale(float(calls[layer_call][1].detach().abs().max()))
             steps.append({"taps": k_taps, "cin": k_cin, "cout": k_cout, "H": H, "W": W, "relu": relu,
                           "pool": pool, "w_hi": w_hi, "w_lo": w_lo, "scale": scale_k,
-                          "shift": shift_k, "out_view": (H, W, cout) if dense2x2 else None,
+                          "shift": shift_k, "out_view": (H, W, cout_p) if dense2x2 else None,
                           "w16_hi": w16_hi, "w16_lo": w16_lo, "s_in": s_in, "s_w": s_w,
                           "scale16": (scale_k / (s_in * s_w)).contiguous() if f16_fits else None,
                           "flops": 2 * k_cout * k_taps * k_cin * (1 if dense2x2 else H * W)})
             if dense2x2:   # per-channel vectors for the incremental form of this layer
-                scale, shift = scale_k[:cout], shift_k[:cout]
+                scale, shift = scale_k[:cout_p], shift_k[:cout_p]
             else:
                 scale, shift = scale_k, shift_k
-            if len(steps) == 1 and cout % 4 == 0:
-                if taps == 9:   # [Cout, Cin, 3, 3] -> [Cin, 9, Cout]
-                    wt = m.weight.detach().float().permute(1, 2, 3, 0).reshape(C, 9, cout)
+            if len(steps) == 1 and cout_p % 4 == 0:
+                # contributions of the REAL channels of z (the permutation indexes those) to the
+                # padded outputs of the layer
+                if taps == 9:   # [Cout_p, Cin, 3, 3] -> [Cin, 9, Cout_p]
+                    wt = w4[:, :z.shape[1]].permute(1, 2, 3, 0).reshape(z.shape[1], 9, cout_p)
                     first = {"mode": 0, "Hp": H, "Wp": W}
-                else:           # [Cout, Cz*S] (NCHW flatten order) -> [Cz, S, Cout]
+                else:           # [Cout, Cz*S] (NCHW flatten order) -> [Cz, S, Cout_p]
                     cz = z.shape[1]
                     sp = m.weight.shape[1] // cz
-                    wt = m.weight.detach().float().view(cout, cz, sp).permute(1, 2, 0)
+                    wt = _pad_to(m.weight.detach().float(), 0, cout_p).view(cout_p, cz, sp).permute(1, 2, 0)
                     first = {"mode": 1, "Hp": 1, "Wp": 1}
-                first.update(wt=wt.contiguous(), C1=cout, scale=scale, shift=shift, relu=relu,
+                first.update(wt=wt.contiguous(), C1=cout_p, scale=scale, shift=shift, relu=relu,
                              pool=pool)
-            C = cout
+            C, Cp = cout, cout_p
             if pool:
                 H, W = H // 2, W // 2
         if not steps or steps[-1]["relu"] or steps[-1]["pool"] or steps[-1]["cout"] != logits.shape[1] \
                 or H * W != 1:
             raise _Unsupported("tail does not end in a linear read-out")
         in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
-        for idx, st in enumerate(steps):   # fp16 split outputs need Cout % 64 == 0
-            splits = not (idx == len(steps) - 1 or st["pool"])
-            if splits and st["cout"] % 64:
-                for st2 in steps:
-                    st2["w16_hi"] = None
-                break
         if len(steps) < 2:
             first = None   # the only layer produces the logits: nothing to chain after it
         return cls(steps, pool_first, in_shape, logits.shape[1], first)
@@ -420,7 +445,7 @@ class NativeTail:
         C, H, W = self.in_shape
         if self.pool_first:
             H, W = H // 2, W // 2
-        return P * B * C * H * W
+        return P * B * _pad(C) * H * W
 
     def logits(self, z, inv_perm, k0, P, buf_hi, buf_lo):
         """[P*B, n_out] fp32 logits of the P prefix masks k0 .. k0+P-1 of the current
@@ -452,7 +477,8 @@ class NativeTail:
         else:
             z4 = z if z.dim() == 4 else z.view(z.shape[0], z.shape[1], 1, 1)
             x_hi, x_lo = _lib.mask_stack_nhwc(z4, inv_perm, k0, P, self.pool_first, buf_hi, buf_lo,
-                                              scale=self.steps[0]["s_in"] if f16 else 1.0)
+                                              scale=self.steps[0]["s_in"] if f16 else 1.0,
+                                              c_pad=_pad(z4.shape[1]))
             steps = self.steps
         last = len(steps) - 1
         for idx, s in enumerate(steps):

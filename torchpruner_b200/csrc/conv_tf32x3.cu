@@ -853,34 +853,38 @@ split_kernel(const float* __restrict__ x, long long n, float scale,
     SplitStore<HALF>::put(hi, lo, i, x[i], scale);
 }
 
-// z: NCHW [B, C, H, W].  out: NHWC [P*B, Ho, Wo, C] hi/lo of the (optionally 2x2 max-pooled)
+// z: NCHW [B, C, H, W].  out: NHWC [P*B, Ho, Wo, Cp] hi/lo of the (optionally 2x2 max-pooled)
 // activation with the first (k0+p+1) channels of the permutation zeroed.  Pooling commutes with
-// the per-channel mask, so it is applied once, before the P-fold replication.
+// the per-channel mask, so it is applied once, before the P-fold replication.  Cp >= C: channels
+// C..Cp-1 are written as zeros (the engine pads channel counts to a multiple of 64).
 template <bool HALF>
 __global__ void __launch_bounds__(256)
 mask_stack_nhwc_kernel(const float* __restrict__ z, const int32_t* __restrict__ inv_perm,
-                       long long k0, int P, int B, int C, int H, int W, int pool, float scale,
+                       long long k0, int P, int B, int C, int H, int W, int pool, float scale, int Cp,
                        typename SplitStore<HALF>::T* __restrict__ out_hi,
                        typename SplitStore<HALF>::T* __restrict__ out_lo) {
   const int Ho = pool ? H / 2 : H, Wo = pool ? W / 2 : W;
-  const long long per_copy = (long long)B * Ho * Wo * C;
+  const long long per_copy = (long long)B * Ho * Wo * Cp;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < per_copy;
        e += gridDim.x * (long long)blockDim.x) {
-    const int c = (int)(e % C);
-    long long t = e / C;
+    const int c = (int)(e % Cp);
+    long long t = e / Cp;
     const int wo = (int)(t % Wo);
     t /= Wo;
     const int ho = (int)(t % Ho);
     const int b = (int)(t / Ho);
-    const float* src = z + (((long long)b * C + c) * H) * W;
-    float v;
-    if (pool) {
-      const float* p0 = src + (2 * ho) * W + 2 * wo;
-      v = nan_max(nan_max(p0[0], p0[1]), nan_max(p0[W], p0[W + 1]));
-    } else {
-      v = src[ho * W + wo];
+    float v = 0.f;
+    long long pos = -1;   // padding channels: "masked" in every copy
+    if (c < C) {
+      const float* src = z + (((long long)b * C + c) * H) * W;
+      if (pool) {
+        const float* p0 = src + (2 * ho) * W + 2 * wo;
+        v = nan_max(nan_max(p0[0], p0[1]), nan_max(p0[W], p0[W + 1]));
+      } else {
+        v = src[ho * W + wo];
+      }
+      pos = (long long)inv_perm[c] - k0;  // masked for every p >= pos
     }
-    const long long pos = (long long)inv_perm[c] - k0;  // masked for every p >= pos
     for (int p = 0; p < P; ++p)
       SplitStore<HALF>::put(out_hi, out_lo, p * per_copy + e, p >= pos ? 0.f : v, scale);
   }
@@ -1204,22 +1208,25 @@ int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_
 
 static int mask_stack_nhwc_impl(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
                                 int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
-                                void* out_hi, void* out_lo, bool half, tp_stream_t stream) {
+                                int64_t C_pad, void* out_hi, void* out_lo, bool half,
+                                tp_stream_t stream) {
   TP_REQUIRE(P >= 0 && B >= 0 && C >= 0 && H >= 0 && W >= 0 && k0 >= -1, TP_ERR_INVALID,
              "tp_mask_stack_nhwc: negative dimension");
+  TP_REQUIRE(C_pad >= C && C_pad < (1ll << 31), TP_ERR_INVALID,
+             "tp_mask_stack_nhwc: C_pad must be at least C");
   TP_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), TP_ERR_INVALID,
              "tp_mask_stack_nhwc: pooling needs even H and W");
-  const long long per_copy = B * (pool ? H / 2 : H) * (pool ? W / 2 : W) * C;
+  const long long per_copy = B * (pool ? H / 2 : H) * (pool ? W / 2 : W) * C_pad;
   if (per_copy == 0 || P == 0) return TP_OK;
   TP_REQUIRE(z && inv_perm && out_hi && out_lo, TP_ERR_INVALID, "tp_mask_stack_nhwc: NULL pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (half) {
     tp::mask_stack_nhwc_kernel<true><<<tp::ew_grid(per_copy), 256, 0, st>>>(
-        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, scale,
+        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, scale, (int)C_pad,
         static_cast<__half*>(out_hi), static_cast<__half*>(out_lo));
   } else {
     tp::mask_stack_nhwc_kernel<false><<<tp::ew_grid(per_copy), 256, 0, st>>>(
-        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, 1.f,
+        z, inv_perm, k0, (int)P, (int)B, (int)C, (int)H, (int)W, pool, 1.f, (int)C_pad,
         static_cast<float*>(out_hi), static_cast<float*>(out_lo));
   }
   TP_LAUNCH_CHECK("mask_stack_nhwc_kernel");
@@ -1227,17 +1234,17 @@ static int mask_stack_nhwc_impl(const float* z, const int32_t* inv_perm, int64_t
 }
 
 int tp_mask_stack_nhwc(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P, int64_t B,
-                       int64_t C, int64_t H, int64_t W, int pool, float* out_hi, float* out_lo,
-                       tp_stream_t stream) {
-  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, 1.f, out_hi, out_lo, false,
-                              stream);
+                       int64_t C, int64_t H, int64_t W, int pool, int64_t C_pad, float* out_hi,
+                       float* out_lo, tp_stream_t stream) {
+  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, 1.f, C_pad, out_hi, out_lo,
+                              false, stream);
 }
 
 int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
                            int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,
-                           void* out_hi, void* out_lo, tp_stream_t stream) {
-  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, scale, out_hi, out_lo, true,
-                              stream);
+                           int64_t C_pad, void* out_hi, void* out_lo, tp_stream_t stream) {
+  return mask_stack_nhwc_impl(z, inv_perm, k0, P, B, C, H, W, pool, scale, C_pad, out_hi, out_lo,
+                              true, stream);
 }
 
 static int maxpool2_split_impl(const float* x, int64_t N, int64_t H, int64_t W, int64_t C,
