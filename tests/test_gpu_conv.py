@@ -327,6 +327,37 @@ def test_native_tail_pads_odd_channel_counts(widths):
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 
 
+@pytest.mark.parametrize("tag", ["features.3", "features.27"])
+def test_native_tail_over_several_ragged_batches(tag):
+    """Three batches, the last one smaller (and small enough that the stacked batch of a 64-channel
+    layer drops below one 128-image tile): same permutations for every batch, rows filled batch
+    by batch, per-batch scratch re-sized — engine on vs engine off."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=21, batch_size=10, seed=11)   # 10 + 10 + 1
+        layer = dict(model.named_modules())[tag]
+        tables = {}
+        for native in ("auto", False):
+            np.random.seed(4)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=2,
+                                         reduction="none")
+            m.native_tail = native
+            with contextlib.redirect_stdout(io.StringIO()):
+                tables[native] = m.run(layer, find_best_evaluation_module=True)
+            assert m.last_run_info["native_tail"] is bool(native)
+        assert tables["auto"].shape == (21, layer.out_channels)
+        assert np.abs(tables["auto"] - tables[False]).max() <= 2e-5
+        assert np.abs(tables[False][20]).max() > 0
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def test_engine_propagates_nan_like_aten():
     """ReLU and max pooling keep a NaN (torch.relu / max_pool2d do; fmaxf would not): an fp16
     overflow upstream (inf in hi, inf - inf = NaN in lo) has to reach the logits to be noticed."""
