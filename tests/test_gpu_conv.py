@@ -358,6 +358,49 @@ def test_native_tail_over_several_ragged_batches(tag):
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 
 
+@pytest.mark.parametrize("contrib", ["stored", "direct"])
+def test_sharded_ranks_start_mid_permutation_on_the_engine(contrib, monkeypatch):
+    """3 emulated ranks share ONE permutation of a 512-channel VGG16 layer: ranks 1 and 2 start
+    inside it, so the incremental first layer has to advance its running sum without output
+    (accumulate-only pass) and one halo evaluation supplies the previous loss."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric, native_tail
+    from torchpruner_b200.attributions.methods import shapley_values as sh
+
+    monkeypatch.setattr(native_tail, "CONTRIB", contrib)
+    monkeypatch.setattr(sh, "allreduce_scores", lambda sv, group=None: sv)
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        loader = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+        layer = model.features[24]
+
+        def run(world, rank):
+            np.random.seed(6)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                         reduction="none")
+            m.max_stack = 100
+            if world > 1:
+                m._dist = lambda: (None, world, rank)
+            with contextlib.redirect_stdout(io.StringIO()):
+                sv = m.run(layer, find_best_evaluation_module=True)
+            assert m.last_run_info["native_tail"] and m.last_run_info["incremental_first"]
+            return sv, m.last_run_info["evaluations"]
+
+        base, n_base = run(1, 0)
+        parts = [run(3, r) for r in range(3)]
+        assert n_base == 512 and sum(n for _, n in parts) == 512 + 2
+        total = sum(sv for sv, _ in parts)
+        assert np.abs(total - base).max() <= 5e-7     # the same losses, summed in another order
+        # each rank touched only its own channels of the permutation
+        touched = [(np.abs(sv).sum(0) > 0) for sv, _ in parts]
+        assert not (touched[0] & touched[1]).any() and not (touched[1] & touched[2]).any()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def test_engine_propagates_nan_like_aten():
     """ReLU and max pooling keep a NaN (torch.relu / max_pool2d do; fmaxf would not): an fp16
     overflow upstream (inf in hi, inf - inf = NaN in lo) has to reach the logits to be noticed."""
