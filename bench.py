@@ -562,9 +562,31 @@ def cpu_sample(steps, warmup, evals_per_layer=6):
     }
 
 
+def _host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return None
+    # All the host threads this arm may use.  torchrun exports OMP_NUM_THREADS=1 and the OpenMP /
+    # oneDNN pools are sized when torch is imported (torch.set_num_threads afterwards does not
+    # bring them back), which would make the same CPU arm several times slower at N > 1 than at
+    # N = 1: run it in a fresh interpreter with the variable set to the core count.
+    want = str(_host_threads())
+    if os.environ.get("OMP_NUM_THREADS", want) != want and "TP_BENCH_REF_CHILD" not in os.environ:
+        env = {k: v for k, v in os.environ.items()
+               if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT",
+                            "OMP_NUM_THREADS", "MKL_NUM_THREADS")}
+        env.update(OMP_NUM_THREADS=want, TP_BENCH_REF_CHILD="1", TP_BENCH_REF_WORLD=str(world))
+        out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference",
+                              "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup",
+                              str(args.warmup)], env=env, stdout=subprocess.PIPE, text=True, check=True)
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    world = int(os.environ.get("TP_BENCH_REF_WORLD", world))
     torch.backends.cudnn.allow_tf32 = False
     cpu = cpu_sample(steps=args.steps, warmup=args.warmup)
     value = cpu["value"]
