@@ -49,7 +49,7 @@ def run(C, Hp, Wp, C1, pool, what, iters=3):
 
 if "ncu" in sys.argv:
     for gm in (GEOMS[2], GEOMS[4]):
-        run(*gm, "direct", iters=1)
+        run(*gm, "stored" if "stored" in sys.argv else "direct", iters=1)
 else:
     print("C Hp Wp C1 pool | P | stored ms (GB/s out) | direct ms (GB/s out)")
     for gm in GEOMS:
