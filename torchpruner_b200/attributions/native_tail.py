@@ -5,7 +5,8 @@ callback (attributions.py:85).  When the layers it runs form a plain chain of
 Conv2d(3x3, stride 1, pad 1) / BatchNorm2d / ReLU / LeakyReLU / MaxPool2d(2) / Flatten / Dropout /
 Linear
 modules in eval mode (every VGG-style tail does), the same arithmetic is executed here by
-``tp_conv_tf32x3`` (tcgen05, 3xTF32, NHWC) instead of by cuDNN/cuBLAS kernels:
+``tp_conv_f16x3`` / ``tp_conv_tf32x3`` (tcgen05, three MMAs per fp32 product on an 11-bit split of
+the operands, NHWC) instead of by cuDNN/cuBLAS kernels:
 
 * the chain is *discovered*, not assumed: one ``forward_partial`` call on the unmasked
   activation is traced with forward hooks; anything that is not a supported leaf module applied
@@ -14,8 +15,12 @@ modules in eval mode (every VGG-style tail does), the same arithmetic is execute
   compared with the user's ``forward_partial`` on the same masked activations.
 
 BatchNorm (eval) and the conv/linear bias are folded into one per-channel scale/shift applied in
-the kernel's epilogue; ReLU is fused; a MaxPool that follows is a separate NHWC kernel that also
-re-splits the result into its TF32 hi/lo pair.
+the kernel's epilogue; ReLU / LeakyReLU are fused; a MaxPool that follows is fused into the
+epilogue too where the layer runs on position-major tiles (``tp_conv_f16x3_pool2``) and is a
+separate NHWC kernel otherwise.  Channel counts are zero-padded to the kernels' 64-channel
+k-block inside the engine's own copies, so any layer width runs.  The first layer of the tail is
+evaluated incrementally along each permutation (csrc/incremental.cu).  The fp16 flavour is the
+default; it falls back to the TF32 one when verification fails or a score comes out non-finite.
 """
 import logging
 import math
