@@ -1,13 +1,15 @@
-from .methods.apoz import APoZAttributionMetric
-from .methods.sensitivity import SensitivityAttributionMetric
-from .methods.random import RandomAttributionMetric
-from .methods.taylor import TaylorAttributionMetric
-from .methods.weight_norm import WeightNormAttributionMetric
-from .methods.shapley_values import ShapleyAttributionMetric
-from .attributions import find_best_module_for_attributions
+"""Attribution metrics under the reference's import path (torchpruner/attributions/__init__.py
+exports the same seven names)."""
+from . import attributions as _base
+from .methods import apoz, random, sensitivity, shapley_values, taylor, weight_norm
 
-__all__ = [
-    "APoZAttributionMetric", "SensitivityAttributionMetric", "RandomAttributionMetric",
-    "TaylorAttributionMetric", "WeightNormAttributionMetric", "ShapleyAttributionMetric",
-    "find_best_module_for_attributions",
-]
+APoZAttributionMetric = apoz.APoZAttributionMetric
+SensitivityAttributionMetric = sensitivity.SensitivityAttributionMetric
+RandomAttributionMetric = random.RandomAttributionMetric
+TaylorAttributionMetric = taylor.TaylorAttributionMetric
+WeightNormAttributionMetric = weight_norm.WeightNormAttributionMetric
+ShapleyAttributionMetric = shapley_values.ShapleyAttributionMetric
+find_best_module_for_attributions = _base.find_best_module_for_attributions
+
+__all__ = [name for name in dir() if name.endswith("AttributionMetric")] + \
+    ["find_best_module_for_attributions"]

@@ -1,4 +1,7 @@
-from .pruner import Pruner
-from .opt_pruner import OptimizerPruner
+"""Structured pruning under the reference's import path (torchpruner/pruner)."""
+from . import opt_pruner, pruner
+
+Pruner = pruner.Pruner
+OptimizerPruner = opt_pruner.OptimizerPruner
 
 __all__ = ["Pruner", "OptimizerPruner"]

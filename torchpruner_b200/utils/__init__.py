@@ -1,4 +1,7 @@
-from .graph import find_best_module_for_attributions
-from .graph import get_vgg_pruning_graph
+"""Graph helpers under the reference's import path (torchpruner/utils)."""
+from . import graph
+
+find_best_module_for_attributions = graph.find_best_module_for_attributions
+get_vgg_pruning_graph = graph.get_vgg_pruning_graph
 
 __all__ = ["find_best_module_for_attributions", "get_vgg_pruning_graph"]
