@@ -206,3 +206,52 @@ def test_trace_leaves_the_model_untouched():
     assert np.array_equal(np.random.get_state()[1], np_state)
     for k, v in model.state_dict().items():
         assert torch.equal(v, before[k]), k
+
+
+def _random_net(rng):
+    """A random feature extractor + classifier in the reference's vocabulary."""
+    layers, c, hw = [], int(rng.choice([1, 3])), int(rng.choice([8, 12]))
+    in_shape = (c, hw, hw)
+    for _ in range(int(rng.randint(1, 4))):
+        out = int(rng.choice([4, 6, 9]))
+        layers.append(nn.Conv2d(c, out, 3, padding=1))
+        c = out
+        if rng.rand() < 0.6:
+            layers.append(nn.BatchNorm2d(c))
+        layers.append([nn.ReLU(), nn.LeakyReLU(0.1), nn.ReLU(inplace=True), nn.Tanh()][int(rng.randint(4))])
+        if rng.rand() < 0.5 and hw % 2 == 0:
+            layers.append([nn.MaxPool2d(2), nn.AvgPool2d(2)][int(rng.randint(2))])
+            hw //= 2
+        if rng.rand() < 0.3:
+            layers.append(nn.Dropout2d(0.2))
+    if rng.rand() < 0.3:
+        layers.append(nn.AdaptiveAvgPool2d(1))
+        hw = 1
+    layers.append(nn.Flatten())
+    f = c * hw * hw
+    for _ in range(int(rng.randint(1, 3))):
+        out = int(rng.choice([5, 7]))
+        layers += [nn.Linear(f, out), nn.ReLU()]
+        if rng.rand() < 0.4:
+            layers.append(nn.Dropout(0.3))
+        f = out
+    layers.append(nn.Linear(f, 3))
+    return nn.Sequential(*layers).eval(), in_shape
+
+
+@pytest.mark.parametrize("seed", range(25))
+def test_random_sequential_models_resolve_like_the_nan_trick(seed):
+    rng = np.random.RandomState(1000 + seed)
+    torch.manual_seed(seed)
+    model, shape = _random_net(rng)
+    trace = cascade.trace_chain(model, shape)
+    assert trace is not None
+    prunable = [m for m in model if isinstance(m, (nn.Conv2d, nn.Linear))][:-1]
+    listeners = [m for m in model if isinstance(m, (nn.Conv2d, nn.Linear, nn.BatchNorm2d,
+                                                    nn.Dropout, nn.Dropout2d))]
+    for module in prunable:
+        n = module.weight.shape[0]
+        units = sorted(rng.choice(n, size=int(rng.randint(1, n)), replace=False).tolist())
+        chosen = [m for m in listeners if rng.rand() < 0.7]
+        got = cascade.resolve(trace, model, module, units, chosen)
+        assert_same(got, probe(model, module, units, chosen, shape, seed=seed))
