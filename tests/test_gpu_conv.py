@@ -401,6 +401,81 @@ def test_sharded_ranks_start_mid_permutation_on_the_engine(contrib, monkeypatch)
         torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
 
 
+def _random_vgg_like(rng):
+    from torchpruner_b200 import workloads
+
+    feats, c, hw = [], 3, int(rng.choice([4, 8, 16]))
+    in_hw = hw
+    for _ in range(int(rng.randint(2, 5))):
+        out = int(rng.choice([8, 20, 48, 64, 72]))
+        feats.append(torch.nn.Conv2d(c, out, 3, padding=1, bias=bool(rng.rand() < 0.7)))
+        c = out
+        if rng.rand() < 0.7:
+            feats.append(torch.nn.BatchNorm2d(c))
+        feats.append(torch.nn.ReLU(inplace=bool(rng.rand() < 0.5)) if rng.rand() < 0.7
+                     else torch.nn.LeakyReLU(0.05))
+        if hw > 1 and rng.rand() < 0.5:
+            feats.append(torch.nn.MaxPool2d(2))
+            hw //= 2
+        if rng.rand() < 0.2:
+            feats.append(torch.nn.Dropout2d(0.1))
+    cls, f = [], c * hw * hw
+    for _ in range(int(rng.randint(0, 3))):
+        out = int(rng.choice([12, 40, 100]))
+        if rng.rand() < 0.3:
+            cls.append(torch.nn.Dropout(0.2))
+        cls += [torch.nn.Linear(f, out), torch.nn.ReLU() if rng.rand() < 0.6 else torch.nn.LeakyReLU()]
+        f = out
+    cls.append(torch.nn.Linear(f, int(rng.choice([3, 10, 17]))))
+
+    class Net(workloads._PartialSequential):
+        def __init__(self):
+            super().__init__()
+            self.features = torch.nn.Sequential(*feats)
+            self.classifier = torch.nn.Sequential(*cls)
+
+    return Net(), (3, in_hw, in_hw)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_chains_engine_on_vs_off(seed):
+    """Randomly drawn conv/BN/ReLU/LeakyReLU/MaxPool/Dropout/Linear chains (odd widths, bias-free
+    convs, in-place activations, 3/10/17 classes): every conv and hidden Linear scored with the
+    engine and with the model's own forward_partial."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        rng = np.random.RandomState(500 + seed)
+        torch.manual_seed(seed)
+        model, shape = _random_vgg_like(rng)
+        workloads.warm_batchnorm(model, shape, n=32)
+        model.to(DEV)
+        n_cls = model.classifier[-1].out_features
+        loader = workloads.synthetic_batches(shape, n=12, batch_size=12, num_classes=n_cls, seed=seed)
+        layers = [m for m in list(model.features) + list(model.classifier)[:-1]
+                  if isinstance(m, (torch.nn.Conv2d, torch.nn.Linear))]
+        engine_runs = 0
+        for layer in layers:
+            tables = {}
+            for native in ("auto", False):
+                np.random.seed(seed)
+                m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                             reduction="none")
+                m.native_tail = native
+                with contextlib.redirect_stdout(io.StringIO()):
+                    tables[native] = m.run(layer, find_best_evaluation_module=True)
+                if native:
+                    engine_runs += int(m.last_run_info["native_tail"])
+            scale = max(np.abs(tables[False]).max(), 1e-3)
+            assert np.abs(tables["auto"] - tables[False]).max() <= 2e-5 * max(1.0, scale), (seed, layer)
+        assert engine_runs >= len(layers) - 1, (engine_runs, len(layers))
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
 def test_engine_propagates_nan_like_aten():
     """ReLU and max pooling keep a NaN (torch.relu / max_pool2d do; fmaxf would not): an fp16
     overflow upstream (inf in hi, inf - inf = NaN in lo) has to reach the logits to be noticed."""
