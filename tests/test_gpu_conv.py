@@ -2,6 +2,7 @@
 convolutions, through the C-ABI."""
 import contextlib
 import io
+import os
 
 import numpy as np
 import pytest
@@ -437,7 +438,7 @@ def _random_vgg_like(rng):
     return Net(), (3, in_hw, in_hw)
 
 
-@pytest.mark.parametrize("seed", range(8))
+@pytest.mark.parametrize("seed", range(int(os.environ.get("TP_FUZZ_SEEDS", "8"))))
 def test_random_chains_engine_on_vs_off(seed):
     """Randomly drawn conv/BN/ReLU/LeakyReLU/MaxPool/Dropout/Linear chains (odd widths, bias-free
     convs, in-place activations, 3/10/17 classes): every conv and hidden Linear scored with the
