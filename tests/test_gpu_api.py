@@ -601,6 +601,44 @@ def test_ablation_curve_redoes_an_fp16_overflow_in_tf32():
     np.testing.assert_allclose(loss, g["vgg16_cifar/loss"], rtol=2e-6)
 
 
+@pytest.mark.parametrize("seed", range(int(os.environ.get("TP_FUZZ_SEEDS", "6"))))
+def test_random_models_prune_bit_exact(seed, capsys):
+    """Cascading prune of randomly drawn sequential models (conv/BN/activations/pools/Dropout/
+    flatten/linear) with SGD momentum and gradients: every tensor equal to the CPU oracle's, the
+    numpy RNG left in the same state, in both cascade modes."""
+    from tests.test_cascade import _random_net
+
+    for mode in ("analytic", "probe"):
+        rng = np.random.RandomState(2000 + seed)
+        torch.manual_seed(seed)
+        cpu_model, shape = _random_net(rng)
+        model = copy.deepcopy(cpu_model).to(DEV)
+        opts = []
+        for mdl in (cpu_model, model):
+            opt = torch.optim.SGD(mdl.parameters(), lr=0.1, momentum=0.9)
+            gen = torch.Generator().manual_seed(seed)
+            for p in mdl.parameters():
+                p.grad = torch.randn(p.shape, generator=gen).to(p.device)
+                opt.state[p]["momentum_buffer"] = torch.randn(p.shape, generator=gen).to(p.device)
+            opts.append(opt)
+        check = oracle.OraclePruner(cpu_model, shape, optimizer=opts[0])
+        pruner = Pruner(model, shape, DEV, optimizer=opts[1], cascade=mode)
+        np.random.seed(seed)
+        for module, casc in get_vgg_pruning_graph(model):
+            n = module.weight.shape[0]
+            if n > 2:
+                pruner.prune_model(module, sorted(np.random.choice(n, size=n // 3, replace=False).tolist()), casc)
+        state = np.random.get_state()[1].copy()
+        np.random.seed(seed)
+        for module, casc in get_vgg_pruning_graph(cpu_model):
+            n = module.weight.shape[0]
+            if n > 2:
+                check.prune_model(module, sorted(np.random.choice(n, size=n // 3, replace=False).tolist()), casc)
+        assert np.array_equal(np.random.get_state()[1], state)
+        assert cases.model_digest(model, opts[1]) == cases.model_digest(cpu_model, opts[0]), (seed, mode)
+    capsys.readouterr()
+
+
 def test_adam_state_is_sliced_with_the_parameter():
     """optimizer state beyond SGD / param_groups[0] follows the pruned parameter."""
     (x, y), _ = simple_model()
