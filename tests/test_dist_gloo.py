@@ -75,3 +75,26 @@ def test_sharded_scores_sum_to_the_unsharded_result(tmp_path):
     assert scale > 0
     # identical per-evaluation losses; only the fp64 summation order differs across ranks
     assert np.abs(sharded - full).max() <= 1e-12 * max(scale, 1.0)
+
+
+def _flag_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from torchpruner_b200.attributions.methods.shapley_values import any_rank
+
+        got = [any_rank(rank == 1, "cpu"), any_rank(False, "cpu"), any_rank(True, "cpu")]
+        with open(os.path.join(out_dir, f"flags{rank}.txt"), "w") as f:
+            f.write(repr(got))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ranks_agree_on_repeating_a_run(tmp_path):
+    """The fp16 -> TF32 rerun contains collectives: a flag raised on ONE rank (its plan ran the
+    fp16 flavour) must be seen by all, or the ranks would disagree on whether to run again."""
+    world = 2
+    mp.spawn(_flag_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for rank in range(world):
+        assert open(tmp_path / f"flags{rank}.txt").read() == "[True, False, True]"

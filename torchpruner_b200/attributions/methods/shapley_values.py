@@ -40,6 +40,18 @@ def allreduce_scores(sv, group=None):
     return sv
 
 
+def any_rank(flag, device, group=None):
+    """True on every rank iff ``flag`` is true on at least one (one tiny MAX all-reduce).  Ranks
+    must take collective decisions — such as repeating a run — together."""
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return bool(flag)   # single process (or ranks emulated in one process by the tests)
+    t = torch.tensor([1.0 if flag else 0.0], device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return bool(t.item())
+
+
 class ShapleyAttributionMetric(_base._AttributionMetric):
     """Monte-Carlo permutation-sampling Shapley values (reference:
     attributions/methods/shapley_values.py).
@@ -151,7 +163,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         rng_state = np.random.get_state()
         sv = self._scores_once(module, sv_samples)
         info = self.last_run_info
-        if sv is not None and info.get("f16") and not bool(torch.isfinite(sv).all()):
+        if sv is not None and info.get("f16_any_rank") and not bool(torch.isfinite(sv).all()):
             # An activation left fp16's exponent range under some mask (the per-tensor scales are
             # calibrated on the unmasked batch, with 2^10 of headroom).  Redo the run on the TF32
             # flavour, with the numpy RNG rewound so the same permutations are drawn.
@@ -301,13 +313,17 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 native.release()
             if sv is None:
                 return None
+            used_f16 = bool(native is not None and native.use_f16)
+            f16_somewhere = used_f16
             if world > 1:
                 allreduce_scores(sv, group)
+                # a NaN from one rank's fp16 overflow is in everybody's table now; whether the
+                # run is repeated must not depend on this rank's own flavour
+                f16_somewhere = any_rank(used_f16, sv.device, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
-                                  "incremental_first": incremental_used,
-                                  "f16": bool(native is not None and native.use_f16),
-                                  "native": native_info}
+                                  "incremental_first": incremental_used, "f16": used_f16,
+                                  "f16_any_rank": f16_somewhere, "native": native_info}
             return sv
 
     # ------------------------------------------------------------------ slow path
