@@ -8,11 +8,11 @@ Workload (config 3 of BASELINE.json, the one the headline metric is quoted on): 
 CIFAR-10 shaped inputs, one batch of 256 synthetic examples, layer-wise Monte-Carlo Shapley
 scoring of all 13 conv layers (evaluated after BN+ReLU, find_best_evaluation_module=True).
 
-One STEP = every GPU evaluates 5 full permutations (the reference's default sv_samples; C prefix
-masks each) for each of the 13 layers = 21120 channel-evals per GPU, through the product's own
-sharding path (sv_samples = 5*N permutations split over N ranks) including the all-reduce of
-each layer's score table.  5 such steps are the sv_samples=25 job of the config on one GPU.
-Scaling is therefore weak.
+One STEP = the whole job of the config: sv_samples=25 permutations (C prefix masks each) for each
+of the 13 layers = 105600 channel-evals, sharded over the N ranks by the product's own
+`shard_spans` (three whole permutations per rank at N=8, the 25th cut in eight, one halo
+evaluation per cut) and ended by the all-reduce of each layer's score table.  The job is fixed
+as N grows: scaling is STRONG.
 
 Printed keys follow the driver's contract; see DESIGN.md "Measurement" for the definitions of
 `roofline`, `cpu_baseline`, `e2e` and `reductions`.
@@ -37,7 +37,8 @@ sys.path.insert(0, ROOT)
 from torchpruner_b200 import workloads  # noqa: E402
 
 BATCH = 256
-PERMS_PER_STEP = 5   # permutations per GPU per layer per step (the reference's default sv_samples)
+SV_SAMPLES = 25      # the config's sv_samples: one step is the whole fixed job, at any N
+EVALS_PER_STEP = SV_SAMPLES * 4224   # 25 * sum of the 13 layers' channel counts
 METRIC = "shapley_channel_evals_per_s"
 UNIT = "channel-evals/s"
 
@@ -64,15 +65,33 @@ def tensor_peak():
     return 1400.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel):
+    """{"traffic": bytes per launch, "traffic_note": where it comes from} for `kernel`, from
+    profiles/ncu_traffic.json (written by profiles/summarize_ncu.py from an `ncu --set full`
+    capture of this round), else traffic null."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            entry = json.load(f)[kernel]
+        return {"traffic": float(entry["dram_bytes_per_launch"]),
+                "traffic_note": f"{entry['what']}; algorithmic {entry['algorithmic_bytes']:.4e} B; "
+                                f"{entry['source']}"}
+    except (OSError, KeyError, ValueError):
+        return {"traffic": None, "traffic_note": "no committed ncu capture of this kernel flavour"}
+
+
 def workload_description(n_gpus):
     return {
         "workload": "C3 VGG16-CIFAR10 layerwise Shapley: bs 256, 13 conv layers scored after "
-                    "BN+ReLU, 5 permutations (the reference's default sv_samples) per GPU per step "
-                    "= 21120 channel-evals/GPU/step (5 steps = the sv_samples=25 job); layers after the scored module run fp32-accurate "
-                    "(tcgen05 engine: 3 MMAs per fp32 product on an 11-bit fp16 split, TF32 split as fallback; "
-                    "verified against forward_partial; cuDNN/cuBLAS TF32 off)",
-        "batch": BATCH, "layers": 13, "channel_evals_per_gpu_step": 4224 * PERMS_PER_STEP,
-        "sv_samples_per_step": PERMS_PER_STEP * n_gpus, "parallelism": f"permutation-sharded x{n_gpus}",
+                    "BN+ReLU, sv_samples=25 = 105600 channel-evals per step, the same job at every "
+                    "N (sharded over the ranks: whole permutations first, the remainder cut, one "
+                    "halo evaluation per cut, one all-reduce per layer); layers after the scored "
+                    "module run fp32-accurate (tcgen05 engine: 3 MMAs per fp32 product on an "
+                    "11-bit fp16 split, TF32 split as fallback; verified against forward_partial; "
+                    "cuDNN/cuBLAS TF32 off); classifier at He scale so that scores are not "
+                    "rounding noise",
+        "batch": BATCH, "layers": 13, "channel_evals_per_step": EVALS_PER_STEP,
+        "sv_samples": SV_SAMPLES, "parallelism": f"(permutation, prefix)-sharded x{n_gpus}",
         "l2": "working set per step (stacked masked activations, up to 512 MiB per chunk) far "
               "exceeds the 126 MB L2; reduction kernels are timed with an L2 flush between "
               "iterations",
@@ -273,20 +292,24 @@ def run_product(args, rank, world, local_rank):
     convs = model.conv_layers()
     hx, hy = host_batch(shape, pin=True)
     dx, dy = hx.to(device), hy.to(device)
-    evals_per_rank_step = PERMS_PER_STEP * sum(c.out_channels for c in convs)
+    assert SV_SAMPLES * sum(c.out_channels for c in convs) == EVALS_PER_STEP
 
     def make_metric(loader):
         m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, device,
-                                     sv_samples=PERMS_PER_STEP * world, reduction="none")
+                                     sv_samples=SV_SAMPLES, reduction="none")
         m.shard = world > 1
         return m
+
+    rank_evals = [0]
 
     def device_step(step):
         np.random.seed(1000 + step)  # identical permutations on every rank
         m = make_metric(OneBatch(dx, dy))
+        rank_evals[0] = 0
         for conv in convs:
             module = m.find_evaluation_module(conv, find_best_evaluation_module=True)
-            m._scores_on_device(module, PERMS_PER_STEP * world)
+            m._scores_on_device(module, SV_SAMPLES)
+            rank_evals[0] += m.last_run_info["evaluations"]
 
     def e2e_step(step):
         np.random.seed(1000 + step)
@@ -297,6 +320,23 @@ def run_product(args, rank, world, local_rank):
             h2d += hx.numel() * 4 + hy.numel() * 8
             d2h += sv.nbytes
         return h2d, d2h
+
+    def shard_check():
+        """Outside every timed region: the table the sharded job all-reduces for one layer equals
+        the table one rank computes alone (the same per-evaluation losses; only the order of the
+        float64 additions differs)."""
+        conv = convs[9]   # features.30: 512 channels at 4x4, engine + incremental first layer
+        tables = []
+        for shard in (True, False):
+            np.random.seed(77)
+            m = make_metric(OneBatch(dx, dy))
+            m.shard = shard
+            module = m.find_evaluation_module(conv, find_best_evaluation_module=True)
+            tables.append(m._scores_on_device(module, SV_SAMPLES))
+        diff = float((tables[0] - tables[1]).abs().max())
+        scale = float(tables[1].abs().max())
+        return {"layer": "features.30", "max_abs_diff": diff, "max_abs_score": scale,
+                "ok": bool(diff <= 1e-12 * max(scale, 1.0))}
 
     def barrier():
         if world > 1:
@@ -322,7 +362,8 @@ def run_product(args, rank, world, local_rank):
         # end to end through the public API with host (pinned) inputs and host results
         e2e_steps = max(1, min(args.steps, 3))
         h2d = d2h = 0
-        e2e_s = float("nan")
+        e2e_s = cold_s = float("nan")
+        check = None
         if not args.core_only:
             e2e_step(-1)
             barrier()
@@ -331,14 +372,35 @@ def run_product(args, rank, world, local_rank):
                 h2d, d2h = e2e_step(args.warmup + s)
             barrier()
             e2e_s = time.perf_counter() - t0
+            # the same call as a user's FIRST one on this model: no cached plan, so every layer
+            # pays the trace of forward_partial, the weight preparation (fold, permute, split),
+            # the fp16 range calibration and the verification against forward_partial
+            from torchpruner_b200.attributions import native_tail
+            native_tail.forget_plans(model)
+            barrier()
+            t0 = time.perf_counter()
+            e2e_step(args.warmup + e2e_steps)
+            barrier()
+            cold_s = time.perf_counter() - t0
+            if world > 1:
+                check = shard_check()
 
-    t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device=device)
+    t = torch.tensor([total_ms, e2e_s, cold_s], dtype=torch.float64, device=device)
+    mine = t.clone()
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_s = float(t[0]), float(t[1])
+        per_rank = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(per_rank, mine)
+        evals = torch.tensor([rank_evals[0]], dtype=torch.int64, device=device)
+        per_rank_evals = [torch.zeros_like(evals) for _ in range(world)]
+        dist.all_gather(per_rank_evals, evals)
+    else:
+        per_rank, per_rank_evals = [mine], [torch.tensor([rank_evals[0]])]
+    total_ms, e2e_s, cold_s = float(t[0]), float(t[1]), float(t[2])
     ms_per_step = total_ms / args.steps
-    value = world * evals_per_rank_step / (ms_per_step / 1e3)
-    e2e_value = world * evals_per_rank_step * e2e_steps / e2e_s
+    value = EVALS_PER_STEP / (ms_per_step / 1e3)
+    e2e_value = EVALS_PER_STEP * e2e_steps / e2e_s
+    e2e_cold_value = EVALS_PER_STEP / cold_s
 
     result = None
     if rank == 0:
@@ -356,15 +418,10 @@ def run_product(args, rank, world, local_rank):
             roofline = {
                 "kernel": dominant, "bound": "tensor", "achieved": executed, "peak": peak,
                 "unit": "TFLOP/s", "frac": executed / peak,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu --set
-                # full capture under profiles/ (not measured in this run)
-                "traffic": 1.0550e9 if half else 1.0998e9,
-                "traffic_note": "bytes per launch of the 4x4x512->512 layer (the step's largest "
-                                "share) at its Shapley stack size, "
-                                + ("N=16384: algorithmic 1.0737e9 (fp16 hi+lo in, hi+lo out); "
-                                   "profiles/r01_ncu_conv_f16x3_summary.txt" if half else
-                                   "N=8192: algorithmic 1.0737e9 (TF32 hi+lo in fp32 containers); "
-                                   "profiles/r01_ncu_conv_tf32x3_persistent_summary.txt"),
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel, read
+                # from the committed ncu --set full summary (a profiler cannot run inside the
+                # timed region); null when no capture of this flavour is committed
+                **ncu_traffic(dominant),
                 "peak_source": bf16[1] + (" bf16 sustained (fp16 and bf16 MMAs run at the same rate)"
                                          if half else
                                          " bf16 sustained / 2 (TF32 dense runs at half the bf16 rate)"),
@@ -397,12 +454,21 @@ def run_product(args, rank, world, local_rank):
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_description(world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "api": "ShapleyAttributionMetric.run(conv, find_best_evaluation_module=True) "
                            "x13, pinned host batch in, numpy [256,C] float64 out"},
+            "e2e_cold": {"value": e2e_cold_value, "unit": UNIT, "seconds": cold_s,
+                         "what": "one step of the same API calls with the plan cache emptied "
+                                 "first: a user's first run() on each layer (trace, weight "
+                                 "preparation, fp16 calibration, verification included)"},
+            "per_rank": {"ms_per_step": [float(p[0]) / args.steps for p in per_rank],
+                         "evaluations_per_step": [int(e[0]) for e in per_rank_evals],
+                         "note": "device time of each rank's own timed loop (the job's time is "
+                                 "the max); evaluations include one halo per cut"},
+            "shard_check": check,
             "gpu_launches": int(sum(v["launches"] for v in kernel_summary.values())),
             "own_kernels": own,
             "roofline": roofline,
@@ -593,7 +659,7 @@ def run_reference(args, rank, world):
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": cpu["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": cpu["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_description(world), "cpu_baseline": cpu,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

@@ -293,7 +293,11 @@ int tp_prefix_contrib_direct(const float* zc, const float* wt, const int64_t* pe
  *  - Every call on a device uses the same array.  It keeps the previous call's contents, so each
  *    call clears the C words it needs before use; two calls that overlap on the GPU (different
  *    streams, or several host threads without ordering) race on it and give undefined results.
- *    Calls ordered on one stream are safe. */
+ *    Calls ordered on one stream are safe.
+ *  - The array belongs to the device that is current when the call is made, so that device must
+ *    be the one that owns x, out_idx, out_count and the stream.  The call checks it (a pointer
+ *    attribute query on out_count, no allocation) and returns TP_ERR_INVALID for buffers of
+ *    another GPU or of the host instead of launching on a foreign address. */
 #define TP_NAN_STATIC_MAX_C 65536
 int tp_nan_any_dim1_static(const float* x, int64_t B, int64_t C, int64_t inner, int64_t* out_idx,
                            int64_t* out_count, tp_stream_t stream);

@@ -14,6 +14,7 @@ are applied by monkey-patch, as SURVEY.md 8(c) records:
 Inputs are regenerated from seeds by the tests (same torch version => same CPU random streams);
 only outputs are stored.
 """
+import copy
 import hashlib
 import io
 import contextlib
@@ -154,7 +155,7 @@ def gen_small_cnn():
 
 def gen_vgg():
     """Configs 2/3 on VGG16-CIFAR: mean Taylor/APoZ/Sensitivity for the 13 convs at bs 256, and
-    Shapley (sv=1, "none") on a 16-example batch for three layers."""
+    Shapley (sv=2, "none") on a 32-example batch for all 13 layers."""
     out = {}
     model, shape = workloads.build("vgg16_cifar")
     loader = workloads.synthetic_batches(shape, n=256, batch_size=256)
@@ -169,13 +170,26 @@ def gen_vgg():
         out[f"{tag}/apoz"] = quiet(mk(APoZAttributionMetric).run, layer, find_best_evaluation_module=True)
         out[f"{tag}/weight_norm"] = quiet(mk(WeightNormAttributionMetric).run, layer)
         print("  vgg", tag, flush=True)
-    small = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
-    for tag in ("features.0", "features.24", "features.40"):
-        layer = dict(model.named_modules())[tag]
+    # Config 3 at a size the CPU finishes in minutes: Shapley (sv_samples=2, "none") on a
+    # 32-example batch for ALL 13 layers, from the reference in fp32 (the golden) and from the
+    # same reference code on a float64 copy of the model and data (the arbiter: how far the
+    # reference's own fp32 arithmetic is from the exact value of the same estimator).
+    small = workloads.synthetic_batches(shape, n=32, batch_size=32, seed=5)
+    x32, y32 = next(iter(small))
+    twin = copy.deepcopy(model).double()
+    small64 = DataLoader(TensorDataset(x32.double(), y32), batch_size=32, shuffle=False)
+    twin_modules = dict(twin.named_modules())
+    for layer in model.conv_layers():
+        tag = names[layer]
         np.random.seed(3)
-        m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, "cpu", sv_samples=1, reduction="none")
-        out[f"{tag}/shapley16"] = quiet(m.run, layer, find_best_evaluation_module=True)
-        print("  vgg shapley", tag, flush=True)
+        m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, "cpu", sv_samples=2, reduction="none")
+        out[f"{tag}/shapley32"] = quiet(m.run, layer, find_best_evaluation_module=True)
+        np.random.seed(3)
+        m = ShapleyAttributionMetric(twin, small64, workloads.cross_entropy, "cpu", sv_samples=2, reduction="none")
+        out[f"{tag}/shapley32_f64"] = quiet(m.run, twin_modules[tag], find_best_evaluation_module=True)
+        a, b = out[f"{tag}/shapley32"], out[f"{tag}/shapley32_f64"]
+        print("  vgg shapley", tag, "max|score| %.3e  reference fp32 vs fp64 twin: %.2e of max" % (
+            np.abs(b).max(), np.abs(a - b).max() / np.abs(b).max()), flush=True)
     np.savez_compressed(os.path.join(HERE, "vgg16.npz"), **out)
     print("vgg16:", len(out), "arrays")
 

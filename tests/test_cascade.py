@@ -255,3 +255,37 @@ def test_random_sequential_models_resolve_like_the_nan_trick(seed):
         chosen = [m for m in listeners if rng.rand() < 0.7]
         got = cascade.resolve(trace, model, module, units, chosen)
         assert_same(got, probe(model, module, units, chosen, shape, seed=seed))
+
+
+def test_stale_trace_resolves_against_the_live_widths():
+    """A trace recorded before a prune still describes the chain, but every width in it is the
+    old one.  Pruning the same layer a second time must use the sizes the model has NOW: negative
+    indices wrap modulo the current width, out-of-range ones are rejected like the reference's
+    ``index_fill_`` does, Dropout's ``original_len`` is the current input width, and "everything
+    behind a Linear is dead" spans the current width."""
+    torch.manual_seed(0)
+    model = nn.Sequential(nn.Linear(10, 100), nn.ReLU(), nn.Dropout(0.5), nn.Linear(100, 20),
+                          nn.ReLU(), nn.Linear(20, 3)).eval()
+    shape = (10,)
+    trace = cascade.trace_chain(model, shape)
+    fc1, drop, fc2, fc3 = model[0], model[2], model[3], model[5]
+    np.random.seed(0)
+    oracle.OraclePruner(model, shape).prune_model(fc1, list(range(10)), [drop, fc2])
+    assert fc1.weight.shape[0] == 90 and drop.p == 0.5 * 0.9
+    # second prune of the same layer, through the trace recorded at width 100
+    for units in ([0, 5, -1, 88, 12, 40, 41, 42, 43], [89], [-90]):
+        got = cascade.resolve(trace, model, fc1, units, [drop, fc2, fc3])
+        assert_same(got, probe(model, fc1, units, [drop, fc2, fc3], shape))
+        assert got[id(drop)][0] == 90.0
+    for bad in ([90], [95], [-91]):   # valid for the recorded width, not for the model as it is
+        with pytest.raises(IndexError):
+            cascade.resolve(trace, model, fc1, bad, [drop, fc2])
+    # the layer behind was narrowed as well: "everything dead" is the current 17 units, not 20
+    np.random.seed(0)
+    oracle.OraclePruner(model, shape).prune_model(fc2, [1, 2, 3], [fc3])
+    got = cascade.resolve(trace, model, fc1, [4], [fc2, fc3])
+    assert_same(got, probe(model, fc1, [4], [fc2, fc3], shape))
+    assert got[id(fc3)][0] == 17.0 and got[id(fc3)][1].size == 17
+    # a model whose widths no longer fit together is left to the probe forward (which raises)
+    fc2.weight.data = fc2.weight.data[:, :50]
+    assert cascade.resolve(trace, model, fc1, [4], [fc2]) is None

@@ -223,21 +223,52 @@ def test_vgg16_scores_match_reference():
     assert worst["taylor"] <= 2e-3 and worst["sensitivity"] <= 2e-3 and worst["apoz"] <= 2e-3, worst
 
 
-@pytest.mark.parametrize("tag", ["features.0", "features.24", "features.40"])
+VGG_CONV_TAGS = ["features.%d" % i for i in (0, 3, 7, 10, 14, 17, 20, 24, 27, 30, 34, 37, 40)]
+
+
+def spearman(a, b):
+    """Rank correlation with average ranks for ties (scipy.stats.spearmanr on flattened input)."""
+    from scipy.stats import spearmanr
+    return float(spearmanr(np.ravel(a), np.ravel(b)).statistic)
+
+
+@pytest.mark.parametrize("tag", VGG_CONV_TAGS)
 def test_vgg16_shapley_matches_reference(tag):
+    """Config 3 at a size the CPU reference finishes in minutes — sv_samples=2, 32 examples — on
+    ALL 13 layers, against tables the unmodified reference produced (make_golden.py gen_vgg).
+    The workload's classifier is at He scale, so scores are O(0.1-1) numbers: the bar is
+    max|difference| <= 1e-4 of the largest score of the layer, and rank correlation >= 0.999 of
+    both the [32, C] table and the per-channel means a user prunes by.  (The reference's own fp32
+    arithmetic is 0.7-2.2e-5 of max away from its float64 twin on these tables; the engine's
+    distance to the same twin is asserted to be no worse than three times that.)"""
     g = gold("vgg16.npz")
     model, shape = workloads.build("vgg16_cifar")
     model.to(DEV)
-    small = workloads.synthetic_batches(shape, n=16, batch_size=16, seed=5)
+    small = workloads.synthetic_batches(shape, n=32, batch_size=32, seed=5)
     layer = dict(model.named_modules())[tag]
     np.random.seed(3)
-    m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, DEV, sv_samples=1, reduction="none")
+    m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, DEV, sv_samples=2, reduction="none")
     sv = m.run(layer, find_best_evaluation_module=True)
-    want = g[f"{tag}/shapley16"]
-    assert sv.shape == want.shape
-    # per-evaluation losses agree to ~1e-6 relative; scores are differences of |loss| ~ 2.3
-    assert np.abs(sv - want).max() <= 3e-5, np.abs(sv - want).max()
-    assert m.last_run_info["stacked"] is True
+    want, twin = g[f"{tag}/shapley32"], g[f"{tag}/shapley32_f64"]
+    assert sv.shape == want.shape == (32, layer.out_channels) and sv.dtype == np.float64
+    info = m.last_run_info
+    assert info["stacked"] is True and info["native_tail"] and info["incremental_first"], info
+    scale = np.abs(want).max()
+    assert scale > 0.1     # the comparison can fail: scores are not rounding noise
+    err, err_twin, ref_twin = (np.abs(sv - want).max() / scale, np.abs(sv - twin).max() / scale,
+                               np.abs(want - twin).max() / scale)
+    print(f"C3 parity {tag}: max|score| {scale:.3f}  engine-reference {err:.2e}  "
+          f"engine-fp64 {err_twin:.2e}  reference-fp64 {ref_twin:.2e}  (of max|score|)")
+    assert err <= 1e-4, err
+    assert err_twin <= max(3 * ref_twin, 2e-5), (err_twin, ref_twin)
+    assert spearman(sv, want) >= 0.999
+    assert spearman(sv.mean(0), want.mean(0)) >= 0.999
+    # the generic path (the user's forward_partial on stacked masks) meets the same bar
+    np.random.seed(3)
+    m.native_tail = False
+    sv2 = m.run(layer, find_best_evaluation_module=True)
+    assert m.last_run_info["native_tail"] is False
+    assert np.abs(sv2 - want).max() / scale <= 1e-4
 
 
 def test_shapley_schedules_agree():
@@ -417,6 +448,34 @@ def test_analytic_cascade_falls_back_to_the_probe():
     assert p.last_cascade == "probe" and list(net.b.weight.shape) == [2, 2]
 
 
+@pytest.mark.parametrize("mode", ["analytic", "probe"])
+def test_pruning_one_layer_twice_uses_the_current_widths(mode, capsys):
+    """A second prune_model of an already narrowed layer (Dropout in the cascade, negative
+    indices) against the oracle: the analytic cascade resolves from a trace recorded at the old
+    widths and has to read the current ones from the model (cascade.py)."""
+    torch.manual_seed(3)
+    cpu = nn.Sequential(nn.Linear(10, 100), nn.ReLU(), nn.Dropout(0.5), nn.Linear(100, 16),
+                        nn.ReLU(), nn.Linear(16, 3)).eval()
+    gpu = copy.deepcopy(cpu).to(DEV)
+    pruner, ref = Pruner(gpu, (10,), DEV, cascade=mode), oracle.OraclePruner(cpu, (10,))
+    rounds = [(0, list(range(10)), [2, 3]), (0, [0, 5, -1, 88, 12, 40, 41, 42, 43], [2, 3]),
+              (3, [1, -2], [5]), (0, [-81, 7], [2, 3, 5])]
+    for r, (layer, units, casc) in enumerate(rounds):
+        np.random.seed(40 + r)
+        pruner.prune_model(gpu[layer], units, [gpu[i] for i in casc])
+        np.random.seed(40 + r)
+        ref.prune_model(cpu[layer], units, [cpu[i] for i in casc])
+        assert np.random.random() == np.random.RandomState(40 + r).random_sample(21)[-1]
+        assert pruner.last_cascade == ("probe" if (mode == "probe" or r == 0) else "analytic")
+        assert gpu[2].p == cpu[2].p
+        for (k, a), b in zip(gpu.state_dict().items(), cpu.state_dict().values()):
+            assert torch.equal(a.cpu(), b), (r, k)
+    assert list(gpu[0].weight.shape) == [79, 10] and list(gpu[5].weight.shape) == [3, 14]
+    with pytest.raises(IndexError):   # 79 units are left: 79 was a valid index two rounds ago
+        pruner.prune_model(gpu[0], [79], [gpu[3]])
+    capsys.readouterr()
+
+
 @pytest.mark.parametrize("momentum", [0.0, 0.01])
 def test_training_step_after_pruning(momentum):
     """test_pruner.py:180-228 (the momentum case raises KeyError in the reference on torch>=1.6)."""
@@ -543,11 +602,12 @@ def test_shapley_full_size_telescopes():
         l1 = workloads.cross_entropy(model.forward_partial(torch.zeros_like(z), from_module=relu), y,
                                      reduction="none")
     want = (l1 - l0).double().cpu().numpy()
-    # Adjacent losses differ by far less than a factor of two, so every fp32 difference is exact
-    # (Sterbenz) and the fp64 sum telescopes exactly: what is left is the few-ulp difference
-    # between the engine's and torch's loss for the fully masked activation (ulp(2.3) = 2.4e-7).
-    assert np.abs(sv.sum(1) - want).max() <= 2e-6, np.abs(sv.sum(1) - want).max()
-    assert np.abs(want).max() > 1e-4   # random-init VGG: the signal itself is only ~2e-4
+    # Each fp32 difference of adjacent losses is exact or off by half an ulp of the difference,
+    # and the fp64 sum adds nothing: what is left is a random walk of those half-ulps over 512
+    # steps plus the few-ulp difference between the engine's and torch's loss at both ends
+    # (losses of 2-10: ulp up to 9.5e-7).
+    assert np.abs(sv.sum(1) - want).max() <= 2e-5, np.abs(sv.sum(1) - want).max()
+    assert np.abs(want).max() > 1.0   # He-scale classifier: removing a whole layer moves the loss
 
 
 # ------------------------------------------------------------------ ablation curve
@@ -580,6 +640,34 @@ def test_ablation_curve_matches_reference(cfg, tag, n, native):
                                  native_tail=native)
     np.testing.assert_allclose(loss2 / 2.0, want_loss, rtol=2e-6)
     assert int((acc2 != want_acc).sum()) <= 1
+
+
+def test_ablation_then_shapley_on_a_tail_the_engine_does_not_run():
+    """The notebook loops Taylor -> ablation -> Shapley over one unchanged model.  When the
+    layers after the module are outside the engine's vocabulary (conv1 of the small CNN is
+    followed by a 3x3 convolution with padding 2) ablation remembers "no plan"; Shapley must
+    read that entry as such and take forward_partial, like ablation did."""
+    from torchpruner_b200.ablation import ablation_curve
+
+    model, shape = workloads.build("small_cnn")
+    cpu_model = copy.deepcopy(model)
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=8, batch_size=8, seed=2)
+    x, y = next(iter(loader))
+    conv1 = model.features[0]
+    ranking = np.random.RandomState(1).permutation(32)
+    loss, _ = ablation_curve(model, x.to(DEV), y.to(DEV), conv1, ranking,
+                             criterion=workloads.cross_entropy)
+    assert np.isfinite(loss).all()
+    np.random.seed(6)
+    m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=2,
+                                 reduction="none")
+    sv = m.run(conv1, find_best_evaluation_module=True)
+    assert m.last_run_info["native_tail"] is False
+    np.random.seed(6)
+    want = oracle.shapley_with_partial(cpu_model, loader, workloads.cross_entropy, 2, 8,
+                                       cpu_model.features[1])
+    assert np.abs(sv - want).max() <= 5e-6 * max(1.0, np.abs(want).max())
 
 
 def test_ablation_curve_redoes_an_fp16_overflow_in_tf32():

@@ -221,6 +221,17 @@ def test_cached_plan_is_dropped_when_the_model_changes():
         assert info["native_tail"] and not info["native"].get("cached")
         want, _ = run(False)
         assert np.abs(got - want).max() <= 2e-5 and np.abs(got - first).max() > 1e-5
+        # a write through .data (older masking / fine-tuning code) bumps no version counter and
+        # moves no pointer: only the plan's checksum of the weight bits can see it
+        _, info = run("auto")
+        assert info["native"].get("cached") is True
+        before = got
+        model.features[34].weight.data[:40].mul_(0.0)
+        model.classifier[1].bias.data.add_(0.25)
+        got, info = run("auto")
+        assert info["native_tail"] and not info["native"].get("cached")
+        want, _ = run(False)
+        assert np.abs(got - want).max() <= 2e-5 and np.abs(got - before).max() > 1e-5
         with contextlib.redirect_stdout(io.StringIO()):
             pruner = Pruner(model, shape, DEV)
             pruner.prune_model(model.features[37], list(range(64)),

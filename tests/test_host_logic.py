@@ -150,7 +150,7 @@ def test_cudnn_flags_are_restored():
                                                     (3, 10, 1), (2, 5, 4)])
 def test_shard_spans_partition_the_work(samples, channels, world):
     seen = np.zeros((samples, channels), dtype=int)
-    sizes = []
+    sizes, cuts = [], []
     for rank in range(world):
         spans = shard_spans(samples, channels, world, rank)
         count = 0
@@ -159,11 +159,26 @@ def test_shard_spans_partition_the_work(samples, channels, world):
             seen[j, a:b] += 1
             count += b - a
         sizes.append(count)
-        # contiguous in j-major order
-        flat = [j * channels + k for j, a, b in spans for k in range(a, b)]
+        # whole permutations first (no halo, no start inside a permutation) ...
+        whole = [s for s in spans if s[1] == 0 and s[2] == channels]
+        assert len(whole) >= samples // world
+        # ... and the spans that are cut from the left-over permutations are contiguous
+        part = [s for s in spans if s not in whole[:samples // world]]
+        flat = [j * channels + k for j, a, b in part for k in range(a, b)]
         assert flat == list(range(flat[0], flat[0] + len(flat))) if flat else True
+        cuts.append(sum(1 for j, a, b in spans if a > 0))
     assert (seen == 1).all()
     assert max(sizes) - min(sizes) <= 1
+    assert max(cuts) <= 1 if channels >= world else True   # at most one halo evaluation per rank
+
+
+def test_shard_spans_of_the_named_job():
+    """sv_samples=25 over 8 GPUs: three whole permutations per rank, the 25th cut in eight."""
+    for rank in range(8):
+        spans = shard_spans(25, 512, 8, rank)
+        assert spans[:3] == [(3 * rank + i, 0, 512) for i in range(3)]
+        assert spans[3:] == [(24, 64 * rank, 64 * rank + 64)]
+    assert shard_spans(25, 64, 1, 0) == [(j, 0, 64) for j in range(25)]
 
 
 def test_pruner_dropout_and_validation():

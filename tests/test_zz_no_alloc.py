@@ -73,3 +73,28 @@ def test_static_scratch_variant_rejects_oversize():
     x[0, -1] = float("nan")
     _lib.nan_any_dim1_static(x, idx, cnt)
     assert int(cnt.item()) == 1 and int(idx[0].item()) == _lib.TP_NAN_STATIC_MAX_C - 1
+
+
+def test_static_scratch_variant_rejects_buffers_that_are_not_on_the_current_gpu():
+    """The built-in work area belongs to the GPU that is current during the call.  Output buffers
+    somewhere else (here: pinned host memory; on a multi-GPU box, another device) are refused with
+    an error instead of being paired with the wrong device's array."""
+    x = torch.zeros((2, 8, 3), device=DEV)
+    idx = torch.full((8,), -5, dtype=torch.int64, device=DEV)
+    host_cnt = torch.full((1,), -5, dtype=torch.int64).pin_memory()
+    with pytest.raises(_lib.TorchPrunerB200Error, match="current device"):
+        _lib.nan_any_dim1_static(x, idx, host_cnt)
+    assert int(host_cnt[0]) == -5 and int(idx.min().item()) == -5
+    if torch.cuda.device_count() > 1:
+        other = torch.device("cuda:1")
+        x1 = torch.zeros((2, 8, 3), device=other)
+        x1[1, 3, 0] = float("nan")
+        idx1 = torch.empty(8, dtype=torch.int64, device=other)
+        cnt1 = torch.empty(1, dtype=torch.int64, device=other)
+        _lib.nan_any_dim1_static(x1, idx1, cnt1)    # the wrapper makes x's device current
+        assert int(cnt1.item()) == 1 and int(idx1[0].item()) == 3
+        with torch.cuda.device(DEV):                # through the C-ABI with the wrong device current
+            rc = _lib.load().tp_nan_any_dim1_static(
+                x1.data_ptr(), 2, 8, 3, idx1.data_ptr(), cnt1.data_ptr(),
+                torch.cuda.current_stream(DEV).cuda_stream)
+            assert rc != 0

@@ -79,7 +79,7 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
                 if not ok:
                     native = None
         if native_tail and stack_safe and n and not found:
-            remember_plan(model, module_nl, z, native, info)
+            remember_plan(model, module_nl, z, native, info or {"verified": False})
         if native is None:
             P_max = int(max(1, min(max_stack, max(n, 1), max_stack_bytes // max(1, z.numel() * 4))))
             if not stack_safe:

@@ -1,5 +1,6 @@
 import logging
 import os
+import weakref
 
 import numpy as np
 import torch
@@ -14,21 +15,29 @@ _ZERO_BITS = 0x00000000
 
 
 def shard_spans(sv_samples, n_channels, world_size, rank):
-    """Work items are the ``sv_samples * n_channels`` (permutation j, prefix position k) pairs in
-    j-major order.  Rank ``rank`` owns one contiguous span of them; the result lists, per
-    permutation touched, the half-open prefix range ``(j, k_begin, k_end)`` it evaluates.
-    25 permutations do not divide over 8 GPUs, so the split is over (j, k) pairs, not over j.
+    """The half-open prefix ranges ``(j, k_begin, k_end)`` of permutation j that ``rank``
+    evaluates; over all ranks every (permutation, prefix position) pair is covered exactly once.
+
+    Whole permutations first: each rank gets ``sv_samples // world_size`` of them, which need no
+    halo evaluation and no start inside a permutation.  Only the ``sv_samples % world_size``
+    permutations left over (25 = 8 * 3 + 1) are cut: their (j, k) pairs, in j-major order, are
+    split into ``world_size`` contiguous spans, so work per rank differs by at most one
+    evaluation and a rank pays at most one halo per cut it starts behind.
     """
-    total = sv_samples * n_channels
+    spans = []
+    if n_channels <= 0 or sv_samples <= 0:
+        return spans
+    whole = sv_samples // world_size
+    spans += [(j, 0, n_channels) for j in range(rank * whole, (rank + 1) * whole)]
+    first_cut = whole * world_size
+    total = (sv_samples - first_cut) * n_channels
     lo = rank * total // world_size
     hi = (rank + 1) * total // world_size
-    spans = []
-    if hi <= lo or n_channels == 0:
-        return spans
-    for j in range(lo // n_channels, (hi - 1) // n_channels + 1):
-        k_begin = max(lo, j * n_channels) - j * n_channels
-        k_end = min(hi, (j + 1) * n_channels) - j * n_channels
-        spans.append((j, k_begin, k_end))
+    if hi > lo:
+        for j in range(lo // n_channels, (hi - 1) // n_channels + 1):
+            k_begin = max(lo, j * n_channels) - j * n_channels
+            k_end = min(hi, (j + 1) * n_channels) - j * n_channels
+            spans.append((first_cut + j, k_begin, k_end))
     return spans
 
 
@@ -50,6 +59,53 @@ def any_rank(flag, device, group=None):
     t = torch.tensor([1.0 if flag else 0.0], device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return bool(t.item())
+
+
+def agree_on_plan(native, has_work, device, group=None):
+    """Make the execution plan of one (layer, batch) the same on every rank: one MIN all-reduce
+    of (engine usable, fp16 flavour, incremental first layer).  Ranks verify their plans on their
+    own masks, and a verification that lands a hair on either side of its tolerance must not
+    leave one rank on the library path (measured: one such rank made an 8-GPU step wait 700 ms
+    at the all-reduce).  A rank without work votes "don't care".  Returns the plan to use."""
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return native   # single process (or ranks emulated in one process by the tests)
+    if has_work:
+        mine = [int(native is not None), int(native is not None and native.use_f16),
+                int(native is not None and native.incremental)]
+    else:
+        mine = [1, 1, 1]
+    t = torch.tensor(mine, dtype=torch.int32, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    usable, f16, incremental = (bool(v) for v in t.tolist())
+    if native is None:
+        return None
+    if not usable:
+        native.release()
+        return None
+    if not f16:
+        native.use_f16 = False
+    if not incremental and native.incremental:
+        native.release()   # drops the per-batch contributions; the first layer runs per mask
+    return native
+
+
+_WARNED_GENERIC = weakref.WeakSet()
+
+
+def _warn_generic_path(model, module):
+    """Say once per model that its layers after ``module`` are evaluated through the model's own
+    ``forward_partial`` (library kernels, measured ~20x slower than the engine on VGG16)."""
+    if model in _WARNED_GENERIC:
+        return
+    _WARNED_GENERIC.add(model)
+    logging.warning(
+        "torchpruner_b200: the layers after %s are outside the tensor-core engine's vocabulary "
+        "(chains of 3x3/stride 1/pad 1 Conv2d, BatchNorm2d, ReLU/LeakyReLU, MaxPool2d(2), Flatten, "
+        "Dropout, Linear in eval mode) or did not verify against forward_partial; Shapley masks "
+        "are evaluated through the model's forward_partial instead (same results, slower)",
+        type(module).__name__)
 
 
 class ShapleyAttributionMetric(_base._AttributionMetric):
@@ -205,37 +261,29 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
 
                 # --- how the layers after `module` are executed for this batch
                 use_engine = bool(self.native_tail and stack_safe and spans)
-                found, native = False, None
-                if use_engine:
-                    found, native, info = cached_plan(self.model, module, z)
-                    if found:
-                        native_info = dict(info, cached=True)
-                    if native is not None and getattr(self, "_f16_banned", False):
-                        native.use_f16 = False
+                native, P_max, buf_hi, buf_lo = None, None, None, None
+                banned = getattr(self, "_f16_banned", False)
 
                 def engine_buffers():
-                    native.prepare_batch(z, allow_incremental=self.incremental_first)
-                    per_copy = 8 * native.stack_elems(B, 1)  # hi + lo
-                    p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
-                    per_copy = per_copy // (2 if native.use_f16 else 1)
+                    per_copy = (4 if native.use_f16 else 8) * native.stack_elems(B, 1)  # hi + lo
                     p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
                     hi = torch.empty(native.stack_elems(B, max(p_max, min(2, n))),
                                      dtype=native.stack_dtype, device=z.device)
                     return p_max, hi, torch.empty_like(hi)
 
-                if native is not None:
-                    # A plan verified against forward_partial for this very model state: the
-                    # unmasked loss comes from it too, so the whole ladder is self-consistent and
-                    # the library forward of the tail is not needed at all.
-                    P_max, buf_hi, buf_lo = engine_buffers()
-                    logits0 = native.unmasked_logits(z, inv_dev[0], buf_hi, buf_lo)
-                    original_loss = self.criterion(logits0, y, reduction="none")
-                else:
-                    logits0, original_loss = self.run_forward_partial(original_z, y_true=y,
-                                                                      from_module=module)
-                    if use_engine and not found:
-                        native = NativeTail.build(self.model, module, z)
+                if use_engine:
+                    found, native, info = cached_plan(self.model, module, z)
+                    if found:
+                        native_info = dict(info or {}, cached=True)
                         if native is not None:
+                            native.use_f16 = native.use_f16 and not banned
+                            native.prepare_batch(z, allow_incremental=self.incremental_first)
+                    else:
+                        native = NativeTail.build(self.model, module, z)
+                        native_info = {"verified": False}
+                        if native is not None:
+                            native.use_f16 = native.use_f16 and not banned
+                            native.prepare_batch(z, allow_incremental=self.incremental_first)
                             P_max, buf_hi, buf_lo = engine_buffers()
                             j0, k0v, _ = spans[0]
                             ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0],
@@ -250,9 +298,26 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                             if not ok:
                                 native.release()
                                 native = None
-                                del buf_hi, buf_lo
-                        remember_plan(self.model, module, z, native,
-                                      native_info or {"verified": False})
+                        remember_plan(self.model, module, z, native, native_info)
+                    if native is None:
+                        _warn_generic_path(self.model, module)
+                if world > 1:
+                    # every rank must run the same flavour, or the slowest plan sets the pace of
+                    # the whole job at the all-reduce (and tables would mix roundings)
+                    native = agree_on_plan(native, bool(spans), z.device, group)
+
+                if native is not None:
+                    # A plan verified against forward_partial for this very model state: the
+                    # unmasked loss comes from it too, so the whole ladder is self-consistent and
+                    # the library forward of the tail is not needed at all.
+                    if buf_hi is None or buf_hi.dtype != native.stack_dtype:
+                        P_max, buf_hi, buf_lo = engine_buffers()
+                    logits0 = native.unmasked_logits(z, inv_dev[0], buf_hi, buf_lo)
+                    original_loss = self.criterion(logits0, y, reduction="none")
+                else:
+                    buf_hi = buf_lo = None
+                    logits0, original_loss = self.run_forward_partial(original_z, y_true=y,
+                                                                      from_module=module)
 
                 loss0 = self._per_example(original_loss, B)
                 fused_ce = self._fused_ce_ok(logits0, y, loss0)

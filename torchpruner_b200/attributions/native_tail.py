@@ -101,12 +101,54 @@ def _tensor_key(*tensors):
                  for t in tensors)
 
 
+def _digest(tensors):
+    """Order-independent integer checksum of the bit patterns of ``tensors`` (one int64 each,
+    left on the device)."""
+    sums = []
+    for t in tensors:
+        t = t.detach().reshape(-1)
+        if t.element_size() == 4:
+            sums.append(t.view(torch.int32).sum(dtype=torch.int64))
+        elif t.element_size() == 8:
+            sums.append(t.view(torch.int64).sum())
+        elif t.element_size() == 2:
+            sums.append(t.view(torch.int16).sum(dtype=torch.int64))
+        else:
+            sums.append(t.view(torch.uint8).sum(dtype=torch.int64))
+    return torch.stack(sums) if sums else None
+
+
 def cached_plan(model, module, z):
-    """(found, plan, info) for this model state."""
-    entry = _PLANS.get(model, {}).get((id(module), tuple(z.shape[1:])))
+    """(found, plan, info) for this model state.
+
+    The signature catches everything PyTorch itself can see: replaced or resized tensors
+    (pruning), in-place writes that bump ``_version``, mode changes.  A write through ``.data``
+    (``p.data.mul_(mask)``, ``p.data.copy_(w)`` in older masking / fine-tuning code) or from a
+    raw kernel leaves all of that unchanged, and the plan holds its own folded, split copies of
+    the weights — so a hit is additionally checked against a checksum of the bits of every
+    tensor the plan was made from (one small reduction per tensor and one 8-byte-per-tensor
+    comparison; the pipeline is idle at this point of a run anyway).  A mismatch drops the entry
+    and the caller rebuilds and re-verifies."""
+    key = (id(module), tuple(z.shape[1:]))
+    entry = _PLANS.get(model, {}).get(key)
     if entry is not None and entry[0] == _signature(model):
-        return True, entry[1], entry[2]
+        plan = entry[1]
+        if plan is not None and plan.watched and \
+                not torch.equal(_digest(plan.watched), plan.digest):
+            forget_plans(model)
+            return False, None, None
+        return True, plan, entry[2]
     return False, None, None
+
+
+def forget_plans(model=None):
+    """Drop every cached plan and prepared weight copy of ``model`` (of all models when None)."""
+    if model is None:
+        _PLANS.clear()
+        _LAYERS.clear()
+    else:
+        _PLANS.pop(model, None)
+        _LAYERS.pop(model, None)
 
 
 def remember_plan(model, module, z, plan, info):
@@ -167,6 +209,7 @@ class NativeTail:
         self._T = self._s_all = self._base = self._zc = None
         self._perm = None
         self._pos = 0
+        self.watched, self.digest = [], None   # see cached_plan()
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -219,6 +262,7 @@ class NativeTail:
         first = None
         flat = z.dim() == 2
         dev = z.device
+        watched = []   # every model tensor the plan's own copies are derived from
         while i < len(mods):
             m = mods[i]
             if isinstance(m, (nn.Dropout, nn.Dropout2d, nn.Identity)):
@@ -312,6 +356,10 @@ class NativeTail:
                 w = wd.reshape(4 * cout_p, 4 * Cp)
                 scale, shift = scale.repeat(4), shift.repeat(4)
                 k_cin, k_cout, k_taps = 4 * Cp, 4 * cout_p, 1
+            watched += [t for t in (m.weight, m.bias) if t is not None]
+            if bn_used is not None:
+                watched += [t for t in (bn_used.weight, bn_used.bias, bn_used.running_mean,
+                                        bn_used.running_var) if t is not None]
             key = (_tensor_key(m.weight, m.bias) + (
                 _tensor_key(bn_used.weight, bn_used.bias, bn_used.running_mean, bn_used.running_var)
                 if bn_used is not None else ()), w.shape[1], H * W if taps == 1 else 0, dense2x2)
@@ -366,7 +414,10 @@ class NativeTail:
         in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
         if len(steps) < 2:
             first = None   # the only layer produces the logits: nothing to chain after it
-        return cls(steps, pool_first, in_shape, logits.shape[1], first)
+        plan = cls(steps, pool_first, in_shape, logits.shape[1], first)
+        plan.watched = watched
+        plan.digest = _digest(watched)
+        return plan
 
     # ------------------------------------------------------------------ execution
     def _first_out_geometry(self, B):

@@ -3,6 +3,8 @@
 
 #include <string.h>
 
+#include <atomic>
+
 namespace tp {
 
 static thread_local char g_err[512] = {0};
@@ -17,18 +19,22 @@ void set_error(const char* fmt, ...) {
 int sm_count() {
   // One entry per device ordinal; filled lazily.  cudaDeviceGetAttribute is cheap but this is
   // on the launch path of microsecond kernels.
-  static int cached[64] = {0};
+  // (atomics: entry points may be called from several host threads — autograd runs backward
+  // hooks on its own — and two threads filling the same slot write the same value)
+  static std::atomic<int> cached[64];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
-    int n = 0;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
       n = 148;
-    cached[dev] = n;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached[dev];
+  return n;
 }
 
+// Process-wide knobs for experiments (tp_set_tuning).  Plain ints read on every launch: set them
+// before other threads launch, not concurrently with launches.
 Tuning& tuning() {
   static Tuning t;
   return t;

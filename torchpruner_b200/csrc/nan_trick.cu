@@ -134,6 +134,19 @@ int tp_nan_any_dim1_static(const float* x, int64_t B, int64_t C, int64_t inner, 
   }
   TP_REQUIRE(out_idx != nullptr, TP_ERR_INVALID, "tp_nan_any_dim1_static: out_idx is NULL");
   TP_REQUIRE(B * inner == 0 || x != nullptr, TP_ERR_INVALID, "tp_nan_any_dim1_static: x is NULL");
+  // The scratch lives on the CURRENT device; buffers that belong to another GPU would make the
+  // kernels dereference a foreign symbol address.  (Attribute query only: nothing is allocated.)
+  {
+    int dev = -1;
+    TP_CUDA(cudaGetDevice(&dev));
+    cudaPointerAttributes attr;
+    TP_CUDA(cudaPointerGetAttributes(&attr, out_count));
+    TP_REQUIRE((attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) &&
+                   (attr.type == cudaMemoryTypeManaged || attr.device == dev),
+               TP_ERR_INVALID,
+               "tp_nan_any_dim1_static: the buffers are not device memory of the current device "
+               "(%d); make the device that owns them current before the call", dev);
+  }
   int32_t* flags = nullptr;
   const int rc = tp::static_flags_address(&flags);
   if (rc != TP_OK) return rc;

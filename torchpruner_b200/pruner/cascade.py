@@ -194,16 +194,24 @@ def resolve(trace, model, module, indices, cascading_modules):
             return None
         wanted[pos] = m
     first = trace.calls[start]
-    if len(first.out_shape) < 2:
+    if len(first.out_shape) < 2 or not isinstance(module, (nn.Linear, _ConvNd)):
         return None
-    n_units = first.out_shape[1]
-    dead = normalise_indices(indices, n_units)
+    # Two widths are carried along the chain.  ``rec`` is what the trace saw when it was recorded
+    # and is only compared with the trace (is this still the chain that was proven?).  ``live`` is
+    # what the model holds NOW, read from the parameters: an earlier prune_model has sliced them
+    # since the recording (the structure signature deliberately ignores sizes), and indices,
+    # Dropout's ``original_len`` and the everything-dead range must refer to the current widths.
+    rec = first.out_shape[1]
+    live = int(module.weight.shape[0])
+    dead = normalise_indices(indices, live)
     result = {}
     for pos, m in wanted.items():
         if pos <= start:  # runs before the poisoned module: reached, nothing dead
-            result[id(m)] = (float(trace.calls[pos].in_shape[1]), np.zeros(0, np.int64))
+            width_now = _live_width_into(trace, pos)
+            if width_now is None:
+                return None
+            result[id(m)] = (float(width_now), np.zeros(0, np.int64))
     last = max(wanted) if wanted else start
-    width = n_units
     for i in range(start, last):
         link = trace.link(i)
         if link is None:
@@ -212,12 +220,16 @@ def resolve(trace, model, module, indices, cascading_modules):
         if link == "flatten":
             k = int(np.prod(trace.calls[i].out_shape[2:]))
             dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
-            width *= k
-        if len(nxt.in_shape) < 2 or nxt.in_shape[1] != width:
+            rec *= k
+            live *= k
+        if len(nxt.in_shape) < 2 or nxt.in_shape[1] != rec:
             return None
         m = nxt.module
+        width_now = _live_in_width(m)
+        if width_now is not None and width_now != live:
+            return None   # the model no longer fits together here: let the probe forward say so
         if (i + 1) in wanted:
-            result[id(m)] = (float(width), dead.astype(np.int64))
+            result[id(m)] = (float(live), dead.astype(np.int64))
         if i + 1 == last:
             break
         # what the module hands on
@@ -226,17 +238,65 @@ def resolve(trace, model, module, indices, cascading_modules):
                 return None
             if len(nxt.out_shape) < 2:
                 return None
-            width = nxt.out_shape[1]
-            dead = np.arange(width, dtype=np.int64) if dead.size else dead
+            rec = nxt.out_shape[1]
+            live = int(m.weight.shape[0])
+            dead = np.arange(live, dtype=np.int64) if dead.size else dead
         elif isinstance(m, nn.Flatten):
             if m.start_dim != 1 or m.end_dim not in (-1, len(nxt.in_shape) - 1):
                 return None
             k = int(np.prod(nxt.in_shape[2:])) if len(nxt.in_shape) > 2 else 1
             dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
-            width *= k
+            rec *= k
+            live *= k
         elif isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
-            if len(nxt.out_shape) < 2 or nxt.out_shape[1] != width:
+            if len(nxt.out_shape) < 2 or nxt.out_shape[1] != rec:
                 return None
         else:
             return None
     return result
+
+
+def _live_in_width(m):
+    """Input positions along dim 1 that module ``m`` accepts right now, read from its tensors
+    (None for modules that hold none: their width is whatever arrives)."""
+    if isinstance(m, (nn.Linear, _ConvNd)):
+        return int(m.weight.shape[1]) * (m.groups if isinstance(m, _ConvNd) else 1)
+    if isinstance(m, _BatchNorm):
+        for t in (m.weight, m.running_mean):
+            if t is not None:
+                return int(t.shape[0])
+    return None
+
+
+def _live_width_into(trace, pos):
+    """Current dim-1 width of what call ``pos`` receives: from its own tensors when it has some,
+    else carried forward from the nearest Linear / convolution before it (or the model input,
+    which pruning never narrows).  None when a link on the way is unproven."""
+    width = _live_in_width(trace.calls[pos].module)
+    if width is not None:
+        return width
+    j = pos - 1
+    while j >= 0 and not isinstance(trace.calls[j].module, (nn.Linear, _ConvNd)):
+        j -= 1
+    if j < 0:
+        j = 0
+        if len(trace.calls[0].in_shape) < 2:
+            return None
+        width = trace.calls[0].in_shape[1]
+    for i in range(j, pos):
+        call = trace.calls[i]
+        m = call.module
+        if isinstance(m, (nn.Linear, _ConvNd)):
+            width = int(m.weight.shape[0])
+        elif isinstance(m, nn.Flatten):
+            if m.start_dim != 1 or m.end_dim not in (-1, len(call.in_shape) - 1):
+                return None
+            width *= int(np.prod(call.in_shape[2:])) if len(call.in_shape) > 2 else 1
+        elif not isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
+            return None
+        link = trace.link(i)
+        if link is None:
+            return None
+        if link == "flatten":
+            width *= int(np.prod(call.out_shape[2:]))
+    return width

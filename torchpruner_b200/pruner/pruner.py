@@ -82,13 +82,19 @@ class _GatherPlan:
             return
         flat = np.concatenate([arr for _, arr in self.keep_lists]) if self.keep_len else \
             np.zeros(0, np.int64)
-        dev = self.entries[0][1].device
-        keep_dev = torch.from_numpy(flat).to(dev)
-        descs = [
-            _lib.GatherDesc(src.data_ptr(), dst.data_ptr(), outer, n_src, n_keep, inner, offset)
-            for _, src, dst, (outer, n_src, n_keep, inner, offset) in self.entries
-        ]
-        _lib.multi_gather(descs, keep_dev, dev)
+        # One index upload and one launch per device that holds a tensor of the plan: a model
+        # split over several GPUs is sliced where its tensors live, like the reference's
+        # per-tensor index_select.
+        by_device = {}
+        for entry in self.entries:
+            by_device.setdefault(entry[1].device, []).append(entry)
+        for dev, entries in by_device.items():
+            keep_dev = torch.from_numpy(flat).to(dev)
+            descs = [
+                _lib.GatherDesc(src.data_ptr(), dst.data_ptr(), outer, n_src, n_keep, inner, offset)
+                for _, src, dst, (outer, n_src, n_keep, inner, offset) in entries
+            ]
+            _lib.multi_gather(descs, keep_dev, dev)
         for holder, _, dst, _ in self.entries:
             holder.data = dst
         self.entries = []
@@ -96,18 +102,22 @@ class _GatherPlan:
         self.keep_len = 0
 
 
-# Detection hooks are static in the reference and may be installed by hand (its tests do); the
-# results they leave on the device are collected here until the probe forward is over.
+# Detection hooks are static in the reference and may be installed by hand (its tests do).  The
+# results they leave on the device wait in a list until the probe forward is over: the list of the
+# Pruner that installed the hooks, or, for hooks installed by hand, this one.
 _PENDING_DETECTIONS = []
 
 
-def _resolve_detections():
+def _resolve_detections(pending_list=None):
     """One device->host copy for every cascading module of the probe forward (the reference
     synchronises once per module, pruner.py:160-162)."""
-    if not _PENDING_DETECTIONS:
-        return
     pending = list(_PENDING_DETECTIONS)
     _PENDING_DETECTIONS.clear()
+    if pending_list is not None:
+        pending += pending_list
+        pending_list.clear()
+    if not pending:
+        return
     packed = torch.cat([torch.cat([cnt, idx]) for _, idx, cnt in pending]).cpu().numpy()
     pos = 0
     for module, idx, _ in pending:
@@ -134,6 +144,7 @@ class Pruner:
         assert self.cascade in ("analytic", "probe"), "cascade should be 'analytic' or 'probe'"
         self._trace = None
         self.last_cascade = None  # "analytic" / "probe": how the last prune_model resolved it
+        self._pending = []        # detections of this pruner's probe forward, still on the device
 
     @contextlib.contextmanager
     def _batched(self):
@@ -159,7 +170,8 @@ class Pruner:
         if not self._resolve_analytically(module, indices, cascading_modules):
             self.last_cascade = "probe"
             module_handle = module.register_forward_hook(self._nanify_hook(indices))
-            handles = [m.register_forward_hook(self._detect_nan_hook()) for m in cascading_modules]
+            handles = [m.register_forward_hook(self._detect_nan_hook(self._pending))
+                       for m in cascading_modules]
             # the first probe forward doubles as the structure trace later calls resolve from
             recorder = contextlib.nullcontext()
             if self.cascade == "analytic" and self._trace is None:
@@ -173,7 +185,7 @@ class Pruner:
                 module_handle.remove()
                 for handle in handles:
                     handle.remove()
-                _PENDING_DETECTIONS.clear()
+                self._pending.clear()
 
         with self._batched():
             for next_module in cascading_modules:
@@ -289,7 +301,7 @@ class Pruner:
         return _hook
 
     @staticmethod
-    def _detect_nan_hook():
+    def _detect_nan_hook(sink=None):
         """Forward hook that records which positions along dim 1 of a module's input are NaN
         after summing over every other dim (pruner.py:146-168).  ``_activation_len`` is set at
         once; ``_nan_indices`` (ascending int64 numpy array, only when non-empty) appears when
@@ -303,7 +315,7 @@ class Pruner:
             idx = torch.empty(max(C, 1), dtype=torch.int64, device=x.device)
             cnt = torch.empty(1, dtype=torch.int64, device=x.device)
             _lib.nan_any_dim1(x.detach(), flags, idx, cnt)
-            _PENDING_DETECTIONS.append((module, idx, cnt))
+            (_PENDING_DETECTIONS if sink is None else sink).append((module, idx, cnt))
 
         return _hook
 
@@ -317,7 +329,7 @@ class Pruner:
             if x is None:
                 x = torch.tensor(np.random.random((2,) + tuple(self.input_size))).float().to(self.device)
             y = self.model(x)
-            _resolve_detections()
+            _resolve_detections(self._pending)
         finally:
             torch.backends.cudnn.deterministic = d
             torch.backends.cudnn.benchmark = b

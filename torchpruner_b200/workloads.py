@@ -71,7 +71,12 @@ class VGG16Cifar(_PartialSequential):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
             elif isinstance(m, nn.Linear):
-                nn.init.normal_(m.weight, 0, 0.01)
+                # torchvision draws the classifier from N(0, 0.01): every logit is then ~1e-4 and
+                # every loss ln(10) +- 1e-4, so Shapley scores (differences of losses) are 1e-5
+                # numbers that no parity test can tell from zero.  The reference is meant for
+                # trained networks (logits of a few units); with no checkpoint offline, He
+                # scaling gives the classifier that dynamic range.
+                nn.init.kaiming_normal_(m.weight, mode="fan_in", nonlinearity="relu")
                 nn.init.constant_(m.bias, 0)
 
     def conv_layers(self):
@@ -176,15 +181,23 @@ class ResNet50HookFriendly(nn.Module):
 
 
 def warm_batchnorm(model, shape, n=64, seed=1234):
-    """One train-mode forward on ``n`` random examples so BatchNorm running statistics are not
-    the (0, 1) defaults, then eval mode."""
+    """One train-mode forward on ``n`` random examples with BatchNorm momentum 1, so the running
+    statistics ARE that batch's statistics (with the default momentum 0.1 one forward moves them a
+    tenth of the way from (0, 1): eval-mode activations then shrink layer by layer, to 0.03 after
+    the thirteenth), then eval mode."""
     g = torch.Generator().manual_seed(seed)
     x = torch.randn((n,) + tuple(shape), generator=g)
     dev = next(model.parameters()).device
+    norms = [m for m in model.modules() if isinstance(m, nn.modules.batchnorm._BatchNorm)]
+    momenta = [m.momentum for m in norms]
+    for m in norms:
+        m.momentum = 1.0
     model.train()
     with torch.no_grad():
         model(x.to(dev))
     model.eval()
+    for m, mom in zip(norms, momenta):
+        m.momentum = mom
     return model
 
 
