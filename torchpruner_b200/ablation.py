@@ -15,7 +15,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
-from .attributions.native_tail import NativeTail, cached_plan, remember_plan
+from .attributions.native_tail import NativeTail, cached_plan, head_plan, remember_plan
 from .utils import find_best_module_for_attributions
 
 
@@ -33,7 +33,14 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
         else module
     ranking = np.asarray(ranking, dtype=np.int64)
     with torch.no_grad():
-        z = model.forward_partial(x, to_module=module_nl).detach().float().contiguous()
+        stack_safe = not any(m.training and isinstance(
+            m, (torch.nn.modules.batchnorm._BatchNorm, torch.nn.modules.dropout._DropoutNd))
+            for m in model.modules())
+        head = head_plan(model, module_nl, x)[0] if (native_tail and stack_safe) else None
+        if head is not None:   # the activation itself on the fp32-accurate engine (head_plan)
+            z = head.activation(x)
+        else:
+            z = model.forward_partial(x, to_module=module_nl).detach().float().contiguous()
         B, C = z.shape[0], z.shape[1]
         if ranking.size and (ranking.min() < 0 or ranking.max() >= C):
             raise IndexError(f"ranking refers to units outside [0, {C})")
@@ -48,10 +55,6 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
             fused = (probe.dim() == 2 and y.dim() == 1 and y.dtype == torch.int64 and
                      torch.allclose(criterion(probe, y, reduction="none"),
                                     F.cross_entropy(probe, y, reduction="none"), rtol=2e-6, atol=2e-6))
-        stack_safe = not any(m.training and isinstance(
-            m, (torch.nn.modules.batchnorm._BatchNorm, torch.nn.modules.dropout._DropoutNd))
-            for m in model.modules())
-
         native = None
         if native_tail and stack_safe and n:
             found, native, info = cached_plan(model, module_nl, z)

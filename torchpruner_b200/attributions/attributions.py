@@ -58,6 +58,7 @@ class _AttributionMetric(ABC):
         self.reduction = reduction
         self.deterministic = False
         self.benchmark = False
+        self._tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
 
     @abstractmethod
     def run(self, module, **kwargs):
@@ -131,11 +132,21 @@ class _AttributionMetric(ABC):
         return self.reduction(attributions)
 
     def set_deterministic(self):
+        """cuDNN deterministic and not auto-tuned for the data pass, as the reference does
+        (attributions.py:108-111).  Also: no TF32 in cuDNN / cuBLAS for its duration.  The
+        scores are specified against the reference's fp32 arithmetic, and PyTorch's default
+        (``cudnn.allow_tf32 = True``) would silently run the model's convolutions with 10-bit
+        operands on this GPU, which moves Taylor / Sensitivity scores by 1e-2 and Shapley
+        scores by more than their own size."""
         self.deterministic = torch.backends.cudnn.deterministic
         self.benchmark = torch.backends.cudnn.benchmark
+        self._tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
         torch.backends.cudnn.deterministic = True
         torch.backends.cudnn.benchmark = False
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
 
     def restore_deterministic(self):
         torch.backends.cudnn.deterministic = self.deterministic
         torch.backends.cudnn.benchmark = self.benchmark
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = self._tf32

@@ -8,7 +8,7 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
-from ..native_tail import NativeTail, cached_plan, remember_plan
+from ..native_tail import NativeTail, cached_plan, head_plan, remember_plan
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -150,6 +150,10 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         # first layer of the tail evaluated incrementally along each permutation (one channel's
         # contribution subtracted per mask) instead of once per mask
         self.incremental_first = os.environ.get("TORCHPRUNER_B200_INCREMENTAL", "1") != "0"
+        # the layers BEFORE the evaluation module (input -> cached activation) on the engine as
+        # well, when they are a recognised chain: the model's own fp32 forward on the GPU is the
+        # largest single source of distance to the reference's tables (native_tail.head_plan)
+        self.native_head = os.environ.get("TORCHPRUNER_B200_HEAD", "1") != "0"
         self.last_run_info = {}
 
     def run(self, module, sv_samples=None, **kwargs):
@@ -237,12 +241,24 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         row = 0
         n_evals = 0
         stack_safe = self._stack_safe()
-        native = None
-        native_info = {}
+        native = head = None
+        native_info, head_info = {}, {}
 
         with torch.no_grad():
             for x, y in self._batches():
-                original_z, _ = self.run_forward_partial(x, to_module=module)
+                # the evaluation module's output for this batch (shapley_values.py:42): on the
+                # engine when the layers up to it are a recognised chain (see head_plan), else
+                # through the model's forward_partial
+                head, head_info = None, {}
+                if self.native_tail and self.native_head and stack_safe:
+                    head, head_info = head_plan(self.model, module, x,
+                                                ban_f16=getattr(self, "_f16_banned", False))
+                if world > 1:
+                    head = agree_on_plan(head, True, x.device, group)
+                if head is not None:
+                    original_z = head.activation(x)
+                else:
+                    original_z, _ = self.run_forward_partial(x, to_module=module)
                 z = original_z.detach().float().contiguous()
                 B, n = z.shape[0], z.shape[1]
                 if perm_dev is None:
@@ -378,7 +394,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 native.release()
             if sv is None:
                 return None
-            used_f16 = bool(native is not None and native.use_f16)
+            used_f16 = bool((native is not None and native.use_f16) or
+                            (head is not None and head.use_f16))
             f16_somewhere = used_f16
             if world > 1:
                 allreduce_scores(sv, group)
@@ -388,7 +405,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
                                   "incremental_first": incremental_used, "f16": used_f16,
-                                  "f16_any_rank": f16_somewhere, "native": native_info}
+                                  "f16_any_rank": f16_somewhere, "native": native_info,
+                                  "native_head": head is not None, "head": head_info}
             return sv
 
     # ------------------------------------------------------------------ slow path

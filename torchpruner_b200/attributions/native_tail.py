@@ -118,7 +118,7 @@ def _digest(tensors):
     return torch.stack(sums) if sums else None
 
 
-def cached_plan(model, module, z):
+def cached_plan(model, module, z, kind="tail"):
     """(found, plan, info) for this model state.
 
     The signature catches everything PyTorch itself can see: replaced or resized tensors
@@ -129,7 +129,7 @@ def cached_plan(model, module, z):
     tensor the plan was made from (one small reduction per tensor and one 8-byte-per-tensor
     comparison; the pipeline is idle at this point of a run anyway).  A mismatch drops the entry
     and the caller rebuilds and re-verifies."""
-    key = (id(module), tuple(z.shape[1:]))
+    key = (kind, id(module), tuple(z.shape[1:]))
     entry = _PLANS.get(model, {}).get(key)
     if entry is not None and entry[0] == _signature(model):
         plan = entry[1]
@@ -151,13 +151,15 @@ def forget_plans(model=None):
         _LAYERS.pop(model, None)
 
 
-def remember_plan(model, module, z, plan, info):
-    _PLANS.setdefault(model, {})[(id(module), tuple(z.shape[1:]))] = (_signature(model), plan, info)
+def remember_plan(model, module, z, plan, info, kind="tail"):
+    _PLANS.setdefault(model, {})[(kind, id(module), tuple(z.shape[1:]))] = \
+        (_signature(model), plan, info)
 
 
-def _trace_chain(model, z, module):
-    """Leaf modules executed by ``model.forward_partial(z, from_module=module)``, in order, with
-    the tensors they consumed and produced."""
+def _trace_chain(model, z, module, head=False):
+    """Leaf modules executed by ``model.forward_partial(z, from_module=module)`` (or, for
+    ``head``, by ``model.forward_partial(z, to_module=module)``), in order, with the tensors they
+    consumed and produced."""
     calls = []
     handles = []
 
@@ -172,7 +174,10 @@ def _trace_chain(model, z, module):
             handles.append(m.register_forward_hook(hook))
     try:
         with torch.no_grad():
-            logits = model.forward_partial(z, to_module=None, from_module=module)
+            if head:
+                logits = model.forward_partial(z, to_module=module)
+            else:
+                logits = model.forward_partial(z, to_module=None, from_module=module)
     finally:
         for h in handles:
             h.remove()
@@ -210,14 +215,16 @@ class NativeTail:
         self._perm = None
         self._pos = 0
         self.watched, self.digest = [], None   # see cached_plan()
+        self.head_out = None   # (C, H, W) when this plan is a head (input -> evaluation module)
 
     # ------------------------------------------------------------------ construction
     @classmethod
-    def build(cls, model, module, z):
-        """Plan for the layers after ``module`` given a sample activation ``z`` — or None when
-        the tail is not a supported chain.  Never raises for an unsupported model."""
+    def build(cls, model, module, z, head=False):
+        """Plan for the layers after ``module`` given a sample activation ``z`` — or, with
+        ``head``, for the layers from the model input ``z`` up to and including ``module`` — or
+        None when they are not a supported chain.  Never raises for an unsupported model."""
         try:
-            return cls._build(model, module, z)
+            return cls._build(model, module, z, head)
         except _Unsupported:
             return None
         except Exception as exc:   # a model this tracer misreads must not break scoring
@@ -225,12 +232,12 @@ class NativeTail:
             return None
 
     @classmethod
-    def _build(cls, model, module, z):
+    def _build(cls, model, module, z, head=False):
         if z.dim() not in (2, 4) or z.dtype != torch.float32:
             raise _Unsupported("activation rank/dtype")
-        calls, logits = _trace_chain(model, z, module)
-        if not calls or logits.dim() != 2:
-            raise _Unsupported("empty tail or non-matrix output")
+        calls, logits = _trace_chain(model, z, module, head)
+        if not calls or logits.dim() != (4 if head else 2):
+            raise _Unsupported("empty chain or unexpected output rank")
         # must be a chain: each layer consumes the previous layer's output (possibly reshaped)
         prev = z
         for mod, inp, out in calls:
@@ -294,7 +301,8 @@ class NativeTail:
                 cout = m.weight.shape[0]
                 # NCHW flatten order -> NHWC flatten order of the padded activation; the layer that
                 # produces the logits keeps its true width (its output is the unsplit fp32 result)
-                produces_logits = all(isinstance(r, (nn.Dropout, nn.Identity)) for r in mods[i + 1:])
+                produces_logits = not head and \
+                    all(isinstance(r, (nn.Dropout, nn.Identity)) for r in mods[i + 1:])
                 w = _pad_to(m.weight.detach().float().view(cout, C, H * W), 1, Cp)
                 w = _pad_to(w, 0, cout if produces_logits else _pad(cout))
                 w = w.permute(0, 2, 1).reshape(w.shape[0], -1)
@@ -392,7 +400,7 @@ class NativeTail:
                 scale, shift = scale_k[:cout_p], shift_k[:cout_p]
             else:
                 scale, shift = scale_k, shift_k
-            if len(steps) == 1 and cout_p % 4 == 0:
+            if len(steps) == 1 and cout_p % 4 == 0 and not head:
                 # contributions of the REAL channels of z (the permutation indexes those) to the
                 # padded outputs of the layer
                 if taps == 9:   # [Cout_p, Cin, 3, 3] -> [Cin, 9, Cout_p]
@@ -408,10 +416,21 @@ class NativeTail:
             C, Cp = cout, cout_p
             if pool:
                 H, W = H // 2, W // 2
+        in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
+        if head:
+            # ends at the evaluation module: a conv (+BN) (+activation) whose fp32 NHWC output,
+            # cut back to its real channels, is the activation the scores are computed on
+            if not steps or steps[-1]["pool"] or steps[-1]["taps"] != 9 or pool_first or \
+                    tuple(logits.shape[1:]) != (C, H, W):
+                raise _Unsupported("head does not end in a convolution block")
+            plan = cls(steps, False, in_shape, C, None)
+            plan.head_out = (C, H, W)
+            plan.watched = watched
+            plan.digest = _digest(watched)
+            return plan
         if not steps or steps[-1]["relu"] or steps[-1]["pool"] or steps[-1]["cout"] != logits.shape[1] \
                 or H * W != 1:
             raise _Unsupported("tail does not end in a linear read-out")
-        in_shape = (z.shape[1],) + ((z.shape[2], z.shape[3]) if z.dim() == 4 else (1, 1))
         if len(steps) < 2:
             first = None   # the only layer produces the logits: nothing to chain after it
         plan = cls(steps, pool_first, in_shape, logits.shape[1], first)
@@ -565,7 +584,43 @@ class NativeTail:
             if s["pool"]:
                 y_hi, y_lo = _lib.maxpool2_split_nhwc(y_hi, half=f16, scale=next_scale)
             x_hi, x_lo = y_hi, y_lo
+        if self.head_out is not None:
+            return x_hi   # [N, H, W, Cout padded] fp32
         return x_hi.view(x_hi.shape[0], self.n_out)
+
+    def activation(self, x):
+        """Head plans: the evaluation module's output for the input batch ``x`` as a contiguous
+        NCHW fp32 tensor, every layer on the fp32-accurate engine."""
+        C, H, W = self.head_out
+        B = x.shape[0]
+        buf_hi = torch.empty(self.stack_elems(B, 1), dtype=self.stack_dtype, device=x.device)
+        buf_lo = torch.empty_like(buf_hi)
+        no_mask = torch.zeros(x.shape[1], dtype=torch.int32, device=x.device)
+        nhwc = self.logits(x, no_mask, -1, 1, buf_hi, buf_lo)
+        return nhwc.view(B, H, W, -1)[..., :C].permute(0, 3, 1, 2).contiguous()
+
+    def verify_head(self, model, module, x):
+        """(ok, error): the head's activation against ``forward_partial(x, to_module=module)``,
+        relative to the largest activation — with the same arbitration by a float64 copy of the
+        model as ``verify`` when the difference is within what the library forward itself is off
+        by (its fp32 convolutions were measured up to ~1e-5 from the exact result per layer)."""
+        with torch.no_grad():
+            ref = model.forward_partial(x, to_module=module)
+        mine = self.activation(x)
+        if ref.shape != mine.shape:
+            return False, float("inf")
+        scale = float(ref.abs().max().clamp_min(1e-30))
+        worst = float((ref - mine).abs().max()) / scale
+        if worst <= VERIFY_RTOL:
+            return True, worst
+        if worst > VERIFY_ARBITRATE_BELOW:
+            return False, worst
+        ref64 = _float64_forward(model, module, x, head=True)
+        if ref64 is None or ref64.shape != ref.shape:
+            return False, worst
+        lib_err = float((ref.double() - ref64).abs().max()) / scale
+        mine_err = float((mine.double() - ref64).abs().max()) / scale
+        return mine_err <= max(VERIFY_RTOL / 10, lib_err), mine_err
 
     def unmasked_logits(self, z, inv_perm, buf_hi, buf_lo):
         """[B, n_out] logits with no channel removed (prefix index -1), through the direct form
@@ -616,7 +671,39 @@ class NativeTail:
         return mine_err <= max(VERIFY_RTOL / 10, lib_err), mine_err
 
 
-def _float64_forward(model, module, stacked):
+def head_plan(model, module, x, ban_f16=False):
+    """(plan or None, info): a verified engine plan for the layers from the model input ``x`` to
+    the evaluation module ``module``, from the cache or built and verified now.
+
+    Why the head runs on the engine too: the cached activation is the input of every marginal
+    evaluation.  Taken from the model's own fp32 forward on the GPU (cuDNN) it is up to ~1e-5
+    (relative) from the exact activation, ten layers deep, and that alone put VGG16 Shapley
+    tables 0.6-1.3e-4 of the largest score away from a float64 evaluation of the same estimator;
+    with an exact activation the engine's tables are 0.3-3e-5 away, the distance the
+    reference's own CPU fp32 arithmetic has (profiles/r02_parity_sources.txt)."""
+    if not (x.dim() == 4 and x.dtype == torch.float32 and x.is_cuda):
+        return None, {}
+    found, plan, info = cached_plan(model, module, x, kind="head")
+    if found:
+        if plan is not None and ban_f16:
+            plan.use_f16 = False
+        return plan, dict(info or {}, cached=True)
+    plan = NativeTail.build(model, module, x, head=True)
+    info = {"verified": False}
+    if plan is not None:
+        plan.use_f16 = plan.use_f16 and not ban_f16
+        ok, err = plan.verify_head(model, module, x)
+        if not ok and plan.use_f16:
+            plan.use_f16 = False
+            ok, err = plan.verify_head(model, module, x)
+        info = {"verified": ok, "verify_rel_err": err, "f16": plan.use_f16}
+        if not ok:
+            plan = None
+    remember_plan(model, module, x, plan, info, kind="head")
+    return plan, info
+
+
+def _float64_forward(model, module, stacked, head=False):
     """``forward_partial`` of a float64 deep copy of the model (None when the model cannot be
     copied or run that way)."""
     import copy
@@ -625,6 +712,8 @@ def _float64_forward(model, module, stacked):
         twin = copy.deepcopy(model).double()
         twin_module = twin.get_submodule(name) if name else twin
         with torch.no_grad():
+            if head:
+                return twin.forward_partial(stacked.double(), to_module=twin_module)
             return twin.forward_partial(stacked.double(), to_module=None, from_module=twin_module)
     except Exception:
         return None
