@@ -251,8 +251,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 # through the model's forward_partial
                 head, head_info = None, {}
                 if self.native_tail and self.native_head and stack_safe:
-                    head, head_info = head_plan(self.model, module, x,
-                                                ban_f16=getattr(self, "_f16_banned", False))
+                    head, head_info = head_plan(self.model, module, x)
                 if world > 1:
                     head = agree_on_plan(head, True, x.device, group)
                 if head is not None:
@@ -394,8 +393,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 native.release()
             if sv is None:
                 return None
-            used_f16 = bool((native is not None and native.use_f16) or
-                            (head is not None and head.use_f16))
+            used_f16 = bool(native is not None and native.use_f16)
             f16_somewhere = used_f16
             if world > 1:
                 allreduce_scores(sv, group)

@@ -216,6 +216,7 @@ class NativeTail:
         self._pos = 0
         self.watched, self.digest = [], None   # see cached_plan()
         self.head_out = None   # (C, H, W) when this plan is a head (input -> evaluation module)
+        self.exact = []        # head plans: per-layer operands of the exact form (activation())
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -270,6 +271,7 @@ class NativeTail:
         flat = z.dim() == 2
         dev = z.device
         watched = []   # every model tensor the plan's own copies are derived from
+        exact, pool_pending = [], False   # head plans: see activation()
         while i < len(mods):
             m = mods[i]
             if isinstance(m, (nn.Dropout, nn.Dropout2d, nn.Identity)):
@@ -318,6 +320,7 @@ class NativeTail:
             cout_p = w.shape[0]
             scale = torch.ones(cout, device=dev)
             shift = bias.clone()
+            scale64, shift64 = scale.double(), shift.double()
             bn_used = None
             i += 1
             if i < len(mods) and isinstance(mods[i], nn.BatchNorm2d) and taps == 9:
@@ -330,6 +333,7 @@ class NativeTail:
                 shift = (bias.double() - bn.running_mean.detach().double()) * a
                 if bn.affine:
                     shift = shift + bn.bias.detach().double()
+                scale64, shift64 = a, shift
                 scale, shift = a.float(), shift.float()
                 i += 1
             relu = False   # activation spec: False, True (ReLU) or ("leaky", slope)
@@ -400,6 +404,18 @@ class NativeTail:
                 scale, shift = scale_k[:cout_p], shift_k[:cout_p]
             else:
                 scale, shift = scale_k, shift_k
+            if head:
+                if taps != 9 or cout_p % 4:
+                    raise _Unsupported("head layer is not a 3x3 convolution")
+                # this layer in the exact form of csrc/incremental.cu: per-input-channel fp32
+                # contributions summed in float64 (wt over the REAL input channels)
+                c_in = m.weight.shape[1]
+                exact.append({"wt": w4[:, :c_in].permute(1, 2, 3, 0).reshape(c_in, 9, cout_p).contiguous(),
+                              "C1": cout_p, "cout": cout, "scale64": scale64, "shift64": shift64,
+                              "relu": relu, "pool_before": pool_pending,
+                              "unit": torch.ones(cout_p, device=dev),
+                              "zero": torch.zeros(cout_p, device=dev)})
+                pool_pending = pool
             if len(steps) == 1 and cout_p % 4 == 0 and not head:
                 # contributions of the REAL channels of z (the permutation indexes those) to the
                 # padded outputs of the layer
@@ -420,11 +436,13 @@ class NativeTail:
         if head:
             # ends at the evaluation module: a conv (+BN) (+activation) whose fp32 NHWC output,
             # cut back to its real channels, is the activation the scores are computed on
-            if not steps or steps[-1]["pool"] or steps[-1]["taps"] != 9 or pool_first or \
+            if not exact or len(exact) != len(steps) or steps[-1]["pool"] or pool_first or \
                     tuple(logits.shape[1:]) != (C, H, W):
                 raise _Unsupported("head does not end in a convolution block")
             plan = cls(steps, False, in_shape, C, None)
             plan.head_out = (C, H, W)
+            plan.exact = exact
+            plan.use_f16 = False   # the head never runs on the fp16 operand path
             plan.watched = watched
             plan.digest = _digest(watched)
             return plan
@@ -590,14 +608,36 @@ class NativeTail:
 
     def activation(self, x):
         """Head plans: the evaluation module's output for the input batch ``x`` as a contiguous
-        NCHW fp32 tensor, every layer on the fp32-accurate engine."""
-        C, H, W = self.head_out
-        B = x.shape[0]
-        buf_hi = torch.empty(self.stack_elems(B, 1), dtype=self.stack_dtype, device=x.device)
-        buf_lo = torch.empty_like(buf_hi)
-        no_mask = torch.zeros(x.shape[1], dtype=torch.int32, device=x.device)
-        nhwc = self.logits(x, no_mask, -1, 1, buf_hi, buf_lo)
-        return nhwc.view(B, H, W, -1)[..., :C].permute(0, 3, 1, 2).contiguous()
+        NCHW fp32 tensor.
+
+        Every convolution runs in the exact form the incremental first layer uses
+        (``tp_channel_major`` + ``tp_prefix_contrib_direct`` with all channels added): fp32
+        products, the 9 taps of one input channel summed in fp32, the channels summed in
+        FLOAT64; BatchNorm (folded in float64) and the activation are applied to that float64
+        sum, which is rounded to fp32 once per layer — like the reference's fp32 activations
+        between layers, but without its layer-internal rounding.  This pass runs once per batch
+        on B examples (the masked evaluations run 25*C times on the tensor-core engine), so its
+        cost is noise, and its accuracy sets the floor for every score: with the model's own
+        fp32 forward on the GPU (cuDNN) supplying this activation, VGG16 Shapley tables were
+        0.6-1.3e-4 of the largest score from a float64 evaluation; with the tensor-core engine's
+        22-bit operands 3-7e-5; with this, 0.3-3e-5, the reference's own CPU fp32 distance
+        (profiles/r02_parity_sources.txt)."""
+        cur = x
+        for e in self.exact:
+            zc = _lib.channel_major(cur, e["pool_before"])
+            B, C = cur.shape[0], cur.shape[1]
+            H, W = (cur.shape[2] // 2, cur.shape[3] // 2) if e["pool_before"] else \
+                (cur.shape[2], cur.shape[3])
+            acc = torch.zeros(B * H * W * e["C1"], dtype=torch.float64, device=x.device)
+            _lib.prefix_contrib_direct(zc, e["wt"], None, 0, C, acc, e["unit"], e["zero"], B, C, H, W,
+                                       0, False, False, sign=1.0)
+            y = acc.view(B, H, W, e["C1"])[..., :e["cout"]] * e["scale64"] + e["shift64"]
+            if e["relu"] is True:
+                y = torch.where(y < 0, torch.zeros_like(y), y)   # NaN-propagating, like ATen's
+            elif e["relu"]:
+                y = torch.where(y < 0, y * e["relu"][1], y)
+            cur = y.permute(0, 3, 1, 2).float().contiguous()
+        return cur
 
     def verify_head(self, model, module, x):
         """(ok, error): the head's activation against ``forward_partial(x, to_module=module)``,
@@ -671,32 +711,21 @@ class NativeTail:
         return mine_err <= max(VERIFY_RTOL / 10, lib_err), mine_err
 
 
-def head_plan(model, module, x, ban_f16=False):
-    """(plan or None, info): a verified engine plan for the layers from the model input ``x`` to
-    the evaluation module ``module``, from the cache or built and verified now.
-
-    Why the head runs on the engine too: the cached activation is the input of every marginal
-    evaluation.  Taken from the model's own fp32 forward on the GPU (cuDNN) it is up to ~1e-5
-    (relative) from the exact activation, ten layers deep, and that alone put VGG16 Shapley
-    tables 0.6-1.3e-4 of the largest score away from a float64 evaluation of the same estimator;
-    with an exact activation the engine's tables are 0.3-3e-5 away, the distance the
-    reference's own CPU fp32 arithmetic has (profiles/r02_parity_sources.txt)."""
+def head_plan(model, module, x):
+    """(plan or None, info): a verified plan for the layers from the model input ``x`` to the
+    evaluation module ``module`` (a chain of 3x3 convolutions / BatchNorm / activations /
+    MaxPool2d(2)), from the cache or built and verified now.  See ``NativeTail.activation`` for
+    why the library computes the cached activation itself when it can."""
     if not (x.dim() == 4 and x.dtype == torch.float32 and x.is_cuda):
         return None, {}
     found, plan, info = cached_plan(model, module, x, kind="head")
     if found:
-        if plan is not None and ban_f16:
-            plan.use_f16 = False
         return plan, dict(info or {}, cached=True)
     plan = NativeTail.build(model, module, x, head=True)
     info = {"verified": False}
     if plan is not None:
-        plan.use_f16 = plan.use_f16 and not ban_f16
         ok, err = plan.verify_head(model, module, x)
-        if not ok and plan.use_f16:
-            plan.use_f16 = False
-            ok, err = plan.verify_head(model, module, x)
-        info = {"verified": ok, "verify_rel_err": err, "f16": plan.use_f16}
+        info = {"verified": ok, "verify_rel_err": err}
         if not ok:
             plan = None
     remember_plan(model, module, x, plan, info, kind="head")
