@@ -1,7 +1,7 @@
 """Where does the distance between the GPU Shapley tables and the float64 twin come from?
 For VGG16 layers (sv_samples=2, 32 examples, the tests' golden case): the table's distance to the
 reference's float64-twin table, normalised by the largest score, with the cached activation z
-taken from (a) the model's own fp32 forward on the GPU (cuDNN), (b) the engine's head plan,
+taken from (a) the model's own fp32 forward on the GPU (cuDNN), (b) the library's own head plan ("engine": fp32 products, float64 channel sums),
 (c) a float64 forward rounded to fp32 — each for the engine tail and the forward_partial tail.
 
     python profiles/parity_probe.py [features.N ...]  >  profiles/r02_parity_sources.txt
@@ -66,3 +66,34 @@ for tag in tags:
             cells.append("%.2e" % (np.abs(sv - want).max() / scale))
     print(f"{tag:12s}  {scale:9.3f}   {np.abs(ref - want).max() / scale:.2e}            "
           + "  ".join(cells), flush=True)
+
+
+# Per-evaluation losses (the 1e-5 relative bar of north_star is meaningful on these): one
+# permutation, 32 examples; L[k, b] rebuilt from the score table (sv_samples=1: the fp32 loss
+# differences are exact in the float64 table, so L_k = L_0 + cumulative sum along the permutation)
+# against the same ladder evaluated by the float64 twin.
+print("# per-evaluation loss, max over (k, b) of |L - L_f64| / |L_f64|")
+for tag in tags:
+    layer = dict(model.named_modules())[tag]
+    np.random.seed(11)
+    m = ShapleyAttributionMetric(model, small, workloads.cross_entropy, DEV, sv_samples=1,
+                                 reduction="none")
+    with contextlib.redirect_stdout(io.StringIO()):
+        sv = m.run(layer, find_best_evaluation_module=True)
+        module = m.find_evaluation_module(layer, find_best_evaluation_module=True)
+    np.random.seed(11)
+    perm = np.random.permutation(layer.out_channels)
+    x, y = next(iter(small))
+    x, y = x.to(DEV), y.to(DEV)
+    tm = dict(twin.named_modules())[names[module]]
+    worst = 0.0
+    with torch.no_grad():
+        z = twin.forward_partial(x.double(), to_module=tm)
+        l0 = workloads.cross_entropy(twin.forward_partial(z, from_module=tm), y, reduction="none")
+        ladder = l0.cpu().numpy() + np.cumsum(sv[:, perm], axis=1).T      # [C, 32], engine
+        for k, c in enumerate(perm):
+            z[:, c] = 0.0
+            lk = workloads.cross_entropy(twin.forward_partial(z, from_module=tm), y,
+                                         reduction="none").cpu().numpy()
+            worst = max(worst, float(np.max(np.abs(ladder[k] - lk) / np.abs(lk))))
+    print(f"{tag:12s}  {worst:.2e}", flush=True)
