@@ -98,3 +98,58 @@ def test_ranks_agree_on_repeating_a_run(tmp_path):
     mp.spawn(_flag_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     for rank in range(world):
         assert open(tmp_path / f"flags{rank}.txt").read() == "[True, False, True]"
+
+
+class _FakePlan:
+    """Stands in for a NativeTail on the CPU: the host logic under test only reads these."""
+
+    def __init__(self, use_f16=True, incremental=True, head_out=None):
+        self.use_f16, self.incremental, self.head_out = use_f16, incremental, head_out
+        self.released = 0
+
+    def release(self):
+        self.released += 1
+        self.incremental = False
+
+    def activation(self, x):
+        return x[:, :1] * 2.0 + x[:, 1:2]
+
+
+def _plan_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from torchpruner_b200.attributions.methods.shapley_values import (agree_on_plan,
+                                                                          sharded_activation)
+
+        lines = []
+        # rank 1 lost its plan (verification a hair over the tolerance): both take the library path
+        mine = None if rank == 1 else _FakePlan()
+        got = agree_on_plan(mine, True, "cpu")
+        lines.append(repr((got is None, mine.released if mine else None)))
+        # rank 0's plan is on the TF32 flavour, rank 1's cannot run the incremental first layer
+        mine = _FakePlan(use_f16=rank == 1, incremental=rank == 0)
+        got = agree_on_plan(mine, True, "cpu")
+        lines.append(repr((got is mine, got.use_f16, got.incremental)))
+        # a rank without work does not veto
+        mine = _FakePlan() if rank == 0 else None
+        got = agree_on_plan(mine, rank == 0, "cpu")
+        lines.append(repr(got is mine))
+        # the batch's activation: each rank computes ceil(5 / 2) rows, one all-gather
+        x = torch.arange(5 * 2 * 3 * 3, dtype=torch.float32).view(5, 2, 3, 3)
+        z = sharded_activation(_FakePlan(head_out=(1, 3, 3)), x, rank, world)
+        lines.append(repr(bool(torch.equal(z, x[:, :1] * 2.0 + x[:, 1:2])) and tuple(z.shape)))
+        with open(os.path.join(out_dir, f"plan{rank}.txt"), "w") as f:
+            f.write("\n".join(lines))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ranks_agree_on_the_execution_plan_and_share_the_activation(tmp_path):
+    world = 2
+    mp.spawn(_plan_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    want0 = ["(True, 1)", "(True, False, False)", "True", "(5, 1, 3, 3)"]
+    want1 = ["(True, None)", "(True, False, False)", "True", "(5, 1, 3, 3)"]
+    assert open(tmp_path / "plan0.txt").read().splitlines() == want0
+    assert open(tmp_path / "plan1.txt").read().splitlines() == want1

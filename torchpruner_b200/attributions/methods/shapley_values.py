@@ -91,6 +91,29 @@ def agree_on_plan(native, has_work, device, group=None):
     return native
 
 
+def sharded_activation(head, x, rank, world, group=None):
+    """The cached activation of the batch ``x``, each rank computing the rows of
+    ``ceil(B / world)`` examples and one all-gather putting the batch together.  Per-example
+    arithmetic does not depend on which rank (or which slice) an example is in, so every rank ends
+    up with the bits a single GPU computes.  Without this the once-per-batch forward to the
+    evaluation module is replicated on every rank and does not shrink as GPUs are added (the
+    serial fraction of the strong-scaling job)."""
+    import torch.distributed as dist
+
+    B = x.shape[0]
+    if world <= 1 or B < 2 or not (dist.is_available() and dist.is_initialized()):
+        return head.activation(x)
+    chunk = -(-B // world)
+    lo, hi = min(rank * chunk, B), min((rank + 1) * chunk, B)
+    C, H, W = head.head_out
+    gathered = torch.zeros((world * chunk, C, H, W), dtype=torch.float32, device=x.device)
+    if hi > lo:
+        gathered[rank * chunk: rank * chunk + (hi - lo)] = head.activation(x[lo:hi].contiguous())
+    dist.all_gather_into_tensor(gathered, gathered[rank * chunk:(rank + 1) * chunk].clone(),
+                                group=group)
+    return gathered[:B]
+
+
 _WARNED_GENERIC = weakref.WeakSet()
 
 
@@ -255,7 +278,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 if world > 1:
                     head = agree_on_plan(head, True, x.device, group)
                 if head is not None:
-                    original_z = head.activation(x)
+                    original_z = sharded_activation(head, x, rank, world, group)
                 else:
                     original_z, _ = self.run_forward_partial(x, to_module=module)
                 z = original_z.detach().float().contiguous()
