@@ -882,3 +882,51 @@ def test_conv_pool2_fusable_limits():
     one = torch.ones(64, device=DEV)
     with pytest.raises(_lib.TorchPrunerB200Error, match="position-major"):
         _lib.conv_tf32x3(x, x, w, w, 9, one, one, True, split=True, pool=True)
+
+
+@pytest.mark.parametrize("half", [True, False], ids=["f16x3", "tf32x3"])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,taps,pool", [
+    (8, 32, 32, 64, 64, 9, False),       # row tiles, 8 image blocks of one image, BLOCK_N = 64
+    (5, 16, 16, 64, 128, 9, False),      # odd image count: the last pair's second CTA is outside
+    (512, 4, 4, 128, 256, 9, False),     # position-major, 4 image blocks, two N tiles
+    (384, 4, 4, 64, 192, 9, False),      # 3 image blocks (odd), Cout not a multiple of 128
+    (300, 8, 8, 64, 128, 9, True),       # fused MaxPool (running maximum in TMEM), ragged block
+    (640, 2, 2, 128, 128, 9, False),     # 2x2 position-major: 4 of 9 taps
+    (700, 1, 1, 512, 512, 1, False),     # linear layer, ragged rows
+    (256, 1, 1, 200, 64, 1, False),      # K tail zero-filled by TMA
+])
+def test_conv_cta_pairs_give_the_same_bits_as_single_cta_tiles(N, H, W, Cin, Cout, taps, pool, half):
+    """256-row tiles on CTA pairs (tcgen05 cta_group::2: each SM holds its own 128 rows of A and
+    half of the weight tile) against the single-CTA kernel: every output element is the same
+    K-ordered sum on the same operands, so the results are compared bit for bit."""
+    if pool and not half:
+        pytest.skip("pool fusion exists in the fp16 flavour only")
+    gen = torch.Generator(device=DEV).manual_seed(N + 7 * Cin)
+    x = torch.randn((N, H, W, Cin), device=DEV, generator=gen)
+    x = x * (torch.rand((N, H, W, Cin), device=DEV, generator=gen) > 0.3)
+    w = torch.randn((Cout, taps * Cin), device=DEV, generator=gen) / (taps * Cin) ** 0.5
+    scale = torch.rand(Cout, device=DEV, generator=gen) + 0.5
+    shift = torch.randn(Cout, device=DEV, generator=gen) * 0.1
+    if half:
+        x_hi, x_lo = _lib.f16_split(x, 4.0)
+        w_hi, w_lo = _lib.f16_split(w, 8.0)
+        scale = scale / 32.0
+    else:
+        x_hi, x_lo = _lib.tf32_split(x)
+        w_hi, w_lo = _lib.tf32_split(w)
+    outs = {}
+    try:
+        for pair_off in (1, 0):
+            _lib.set_tuning("conv_pair", pair_off)
+            outs[pair_off] = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, True,
+                                              split=True, pool=pool, out_scale=2.0 if half else 1.0)
+    finally:
+        _lib.set_tuning("conv_pair", 0)
+    torch.cuda.synchronize()
+    for a, b in zip(outs[0], outs[1]):
+        assert a.shape == b.shape and torch.equal(a, b)
+    y = (outs[0][0].float() + outs[0][1].float()) / (2.0 if half else 1.0)
+    want = _ref64(x, w, taps, scale * (32.0 if half else 1.0), shift, True)
+    if pool:
+        want = F.max_pool2d(want.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+    assert float((y.double() - want).abs().max()) <= 2e-6 * max(1.0, float(want.abs().max()))

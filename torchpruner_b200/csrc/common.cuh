@@ -55,6 +55,7 @@ struct Tuning {
   int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
   int conv_pos_major = 0;        // 0 auto (position-major tiles for small images), 1 never
   int conv_pos_major_max_hw = 64;  // largest H*W that gets position-major tiles
+  int conv_pair = 0;             // 0 auto (CTA pairs, cta_group::2), 1 single-CTA tiles only
 };
 Tuning& tuning();
 
@@ -107,13 +108,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // landing, an MMA group retiring, an epilogue draining a TMEM buffer).  A phase that never
 // completes — a tensor map that does not describe the buffer it is used on, a byte count that
 // does not match the copy — would otherwise spin until the watchdog, if there is one, kills the
-// process: after 2^28 failed polls (seconds) the kernel traps instead, the launch fails with a
+// process: after 2^26 failed polls (seconds) the kernel traps instead, the launch fails with a
 // sticky CUDA error and the next entry point returns TP_ERR_CUDA.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++polls == (1u << 28)) __trap();
+    if (++polls == (1u << 26)) __trap();
   }
 }
 

@@ -150,11 +150,99 @@ __device__ __forceinline__ void umma_x(uint32_t tmem_d, uint64_t desc_a, uint64_
   }
 }
 // Instruction descriptor: D = F32 (bits 4-5 = 1); A = B = TF32 (2) or F16 (0) in bits 7-9 / 10-12;
-// both K-major; N>>3 at bit 17, M>>4 at bit 24.
-template <int BLOCK_N, bool F16>
+// both K-major; N>>3 at bit 17, M>>4 at bit 24 (M = 256 for a CTA pair: 128 rows per CTA).
+template <int BLOCK_N, bool F16, bool PAIR = false>
 __device__ __forceinline__ constexpr uint32_t make_idesc() {
   return (1u << 4) | ((F16 ? 0u : 2u) << 7) | ((F16 ? 0u : 2u) << 10) |
-         ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+         ((uint32_t)(BLOCK_N >> 3) << 17) | ((uint32_t)((PAIR ? 2 * kBlockM : kBlockM) >> 4) << 24);
+}
+
+// ---- CTA pairs (cta_group::2) -----------------------------------------------------------
+// Two CTAs of a cluster, on the two SMs of one TPC, compute one 256-row x BLOCK_N tile: each
+// holds its own 128 rows of A and HALF of the B tile in shared memory, the leader (cluster rank
+// 0) issues tcgen05.mma.cta_group::2, which reads both CTAs' shared memory and writes both
+// CTAs' TMEM.  Per SM and per FLOP a quarter of the operand bytes (half of B) no longer has to
+// come in from L2 — the single-CTA kernel was bound by exactly that: 61 B/clk/SM of L2->SM
+// traffic at 74 % tensor-pipe activity (profiles/r01_ncu_conv_f16x3_summary.txt).
+// All tensor maps of this file describe buffers in the memory of the GPU that runs the kernel.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;"
+               ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA tile loads of a CTA pair: data lands in the executing CTA's shared memory, completion bytes
+// are counted on the LEADER's mbarrier (`bar_cluster` = its shared::cluster address).
+__device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const CUtensorMap* map, int c0,
+                                                 int c1, int c2, int c3, uint32_t bar_cluster) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, int c0,
+                                                 int c1, uint32_t bar_cluster) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+template <bool F16>
+__device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  if (F16) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// One arrival on the mbarrier at this shared-memory offset in BOTH CTAs of the pair when every
+// MMA issued so far has completed.
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_dst, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_dst)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t cols) {  // whole warp
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+               : "memory");
 }
 // Elements per 128-byte k-block row.
 template <bool F16>
@@ -450,12 +538,13 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
 // TMA stores (full 128-byte lines instead of one scattered row per thread) — overlaps the MMAs
 // of tile i+1.
 // =====================================================================================
-template <int BLOCK_N>
+template <int BLOCK_N, bool PAIR = false>
 struct ConvCfgP {
   static constexpr int kABytes = kBlockM * kBlockK * 4;
-  static constexpr int kBBytes = BLOCK_N * kBlockK * 4;
+  static constexpr int kBRows = PAIR ? BLOCK_N / 2 : BLOCK_N;   // B rows held by one CTA
+  static constexpr int kBBytes = kBRows * kBlockK * 4;
   static constexpr int kStageBytes = 2 * kABytes + 2 * kBBytes;
-  static constexpr int kStages = (BLOCK_N >= 128) ? 3 : 4;
+  static constexpr int kStages = (kStageBytes > 48 * 1024) ? 3 : 4;
   static constexpr int kNumAcc = 4;
   static constexpr int kTmemCols = kNumAcc * BLOCK_N;  // 512 / 256
   static constexpr int kStoreBytes = kBlockM * 32 * 4;  // one [128 rows][32 cols] staging tile
@@ -510,7 +599,21 @@ __device__ __forceinline__ void bulk_wait_read() {
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <int BLOCK_N, bool F16>
+// Tile -> pixel box origin of CTA `rank` of a pair: the two CTAs take the SAME position (so they
+// walk the same taps) in two adjacent image blocks.  An odd image-block count leaves the last
+// pair's second CTA outside the tensor: its loads are zero-filled and its stores clipped.
+__device__ __forceinline__ void tile_origin_pair(const ConvGeom& g, int mp, int rank, int& n0,
+                                                 int& h0, int& w0) {
+  const int per_block = g.tiles_h * g.tiles_w;
+  const int nbp = mp / per_block;
+  const int rem = mp - nbp * per_block;
+  const int ht = rem / g.tiles_w;
+  n0 = (2 * nbp + rank) * g.bn;
+  h0 = ht * g.bh;
+  w0 = (rem - ht * g.tiles_w) * g.bw;
+}
+
+template <int BLOCK_N, bool F16, bool PAIR>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                        const __grid_constant__ CUtensorMap tm_a_lo,
@@ -520,7 +623,11 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                        const __grid_constant__ CUtensorMap tm_y_lo, const ConvGeom g,
                        const float* __restrict__ scale, const float* __restrict__ shift,
                        int m_tiles, int n_tiles) {
-  using Cfg = ConvCfgP<BLOCK_N>;
+  // PAIR: m_tiles counts 256-row pair tiles; blockIdx.x >> 1 is the pair, cluster rank the half
+  using Cfg = ConvCfgP<BLOCK_N, PAIR>;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int first_tile = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* store_buf = smem + Cfg::kStages * Cfg::kStageBytes;  // 2 x 16 KB, 1024-aligned
@@ -548,19 +655,24 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     prefetch_tensormap(&tm_y_hi);
     prefetch_tensormap(&tm_y_lo);
     for (int s = 0; s < Cfg::kStages; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], PAIR ? 2 : 1);   // pair: the leader's own arrival + the peer producer's
       mbar_init(&empty[s], 1);
     }
     for (int b = 0; b < Cfg::kNumAcc; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], 4);
+      mbar_init(&acc_empty[b], PAIR ? 8 : 4);   // pair: the epilogue warps of both CTAs
     }
     fence_mbar_init();
   } else if (warp == 1) {
-    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    if (PAIR) {
+      tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
+    } else {
+      tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();   // the peer's barriers exist before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -570,10 +682,14 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
       const int kc = (g.Cin + kKE - 1) / kKE;
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
         int n0, hb, wb;
-        tile_origin(g, mt, n0, hb, wb);
+        if (PAIR) {
+          tile_origin_pair(g, mt, rank, n0, hb, wb);
+        } else {
+          tile_origin(g, mt, n0, hb, wb);
+        }
         for (int sub = 0; sub < subs; ++sub) {
           const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
           const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
@@ -584,14 +700,32 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             for (int cb = 0; cb < kc; ++cb) {
               const int kb = tap * kc + cb;  // k-block of the weight matrix
               mbar_wait(&empty[stage], phase ^ 1u);
-              mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
               uint8_t* st = smem + stage * Cfg::kStageBytes;
-              tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
-              tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
-                          &full[stage]);
-              tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N, &full[stage]);
-              tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
-                          nt * BLOCK_N, &full[stage]);
+              if (PAIR) {
+                // both CTAs' bytes are counted on the leader's barrier
+                const uint32_t bar = mapa_shared(smem_u32(&full[stage]), 0);
+                if (rank == 0) {
+                  mbar_arrive_expect_tx(&full[stage], 2 * Cfg::kStageBytes);
+                } else {
+                  mbar_arrive_cluster(bar);
+                }
+                const int brow = nt * BLOCK_N + rank * Cfg::kBRows;
+                tma_load_4d_pair(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, bar);
+                tma_load_4d_pair(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
+                                 bar);
+                tma_load_2d_pair(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, brow, bar);
+                tma_load_2d_pair(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE, brow,
+                                 bar);
+              } else {
+                mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+                tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
+                tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
+                            &full[stage]);
+                tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N,
+                            &full[stage]);
+                tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
+                            nt * BLOCK_N, &full[stage]);
+              }
               if (++stage == Cfg::kStages) {
                 stage = 0;
                 phase ^= 1u;
@@ -603,15 +737,19 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
-      constexpr uint32_t idesc = make_idesc<BLOCK_N, F16>();
+    if (lane == 0 && rank == 0) {  // ===== MMA issuer (the leader CTA of a pair) =====
+      constexpr uint32_t idesc = make_idesc<BLOCK_N, F16, PAIR>();
       int stage = 0;
       uint32_t phase = 0;
       int buf = 0;
       uint32_t acc_phase = 0;  // flips every time buf wraps
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         int n0, hb, wb;
-        tile_origin(g, tile / n_tiles, n0, hb, wb);
+        if (PAIR) {
+          tile_origin_pair(g, tile / n_tiles, 0, n0, hb, wb);
+        } else {
+          tile_origin(g, tile / n_tiles, n0, hb, wb);
+        }
         for (int sub = 0; sub < subs; ++sub) {
           const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
           const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
@@ -633,17 +771,31 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 #pragma unroll
             for (int kk = 0; kk < kBlockK / 8; ++kk) {
               const uint64_t off = (uint64_t)(kk * 32 >> 4);
-              umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-              umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-              umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+              if (PAIR) {
+                umma_pair<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+                umma_pair<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+                umma_pair<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+              } else {
+                umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+                umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+                umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+              }
             }
-            umma_commit(&empty[stage]);
+            if (PAIR) {
+              umma_commit_pair(&empty[stage]);   // frees the stage in both CTAs
+            } else {
+              umma_commit(&empty[stage]);
+            }
             if (++stage == Cfg::kStages) {
               stage = 0;
               phase ^= 1u;
             }
             if (++in_chunk == g.promote || kb == nk - 1) {
-              umma_commit(&acc_full[buf]);
+              if (PAIR) {
+                umma_commit_pair(&acc_full[buf]);   // wakes the epilogue warps of both CTAs
+              } else {
+                umma_commit(&acc_full[buf]);
+              }
               in_chunk = 0;
               if (++buf == num_acc) {
                 buf = 0;
@@ -664,10 +816,14 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     int buf = 0;
     uint32_t acc_phase = 0;
     uint32_t stores = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
       const int mt = tile / n_tiles, nt = tile - mt * n_tiles;
       int n0, hb, wb;
-      tile_origin(g, mt, n0, hb, wb);
+      if (PAIR) {
+        tile_origin_pair(g, mt, rank, n0, hb, wb);
+      } else {
+        tile_origin(g, mt, n0, hb, wb);
+      }
       for (int sub = 0; sub < subs; ++sub) {
         const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
         const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
@@ -697,7 +853,13 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&acc_empty[buf]);
+          if (lane == 0) {
+            if (PAIR) {   // the MMA issuer lives in the leader CTA: tell it there
+              mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[buf]), 0));
+            } else {
+              mbar_arrive(&acc_empty[buf]);
+            }
+          }
           if (++buf == num_acc) {
             buf = 0;
             acc_phase ^= 1u;
@@ -816,7 +978,14 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  if (PAIR) {
+    // neither CTA may leave (or free its TMEM) while the other can still read its shared
+    // memory through an MMA or signal one of its barriers
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+  } else {
+    if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
 }
 
 // ---- small elementwise companions ------------------------------------------------------
@@ -984,15 +1153,15 @@ static int launch_conv(const CUtensorMap& a_hi, const CUtensorMap& a_lo, const v
 }
 
 
-template <int BLOCK_N, bool F16>
+template <int BLOCK_N, bool F16, bool PAIR>
 static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_lo,
                                   const void* w_hi, const void* w_lo, const ConvGeom& g,
                                   const float* scale, const float* shift, void* y_hi, void* y_lo,
                                   cudaStream_t st) {
-  using Cfg = ConvCfgP<BLOCK_N>;
+  using Cfg = ConvCfgP<BLOCK_N, PAIR>;
   CUtensorMap b_hi, b_lo, o_hi, o_lo;
   const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
-  const cuuint32_t bbox[2] = {(cuuint32_t)KBlock<F16>::kElems, BLOCK_N};
+  const cuuint32_t bbox[2] = {(cuuint32_t)KBlock<F16>::kElems, (cuuint32_t)Cfg::kBRows};
   int rc = make_map(&b_hi, w_hi, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
   rc = make_map(&b_lo, w_lo, 2, bdims, bbox, F16);
@@ -1007,17 +1176,30 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   if (rc != TP_OK) return rc;
   rc = make_map(&o_lo, y_lo ? y_lo : y_hi, 4, ydims, ybox, half_out);
   if (rc != TP_OK) return rc;
-  auto kern = conv_tf32x3_persistent<BLOCK_N, F16>;
+  auto kern = conv_tf32x3_persistent<BLOCK_N, F16, PAIR>;
   TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-  const long long img_blocks = (g.N + g.bn - 1) / g.bn;
+  long long img_blocks = (g.N + g.bn - 1) / g.bn;
+  if (PAIR) img_blocks = (img_blocks + 1) / 2;   // pairs of image blocks
   const long long m_tiles = img_blocks * g.tiles_h * g.tiles_w;
   const int n_tiles = (g.Cout + BLOCK_N - 1) / BLOCK_N;
-  TP_REQUIRE(m_tiles * n_tiles < (1ll << 31), TP_ERR_LIMIT, "tp_conv_tf32x3: too many tiles");
-  long long grid = m_tiles * n_tiles;
-  if (grid > sm_count()) grid = sm_count();
-  kern<<<(unsigned)grid, kConvThreads, Cfg::kSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, o_hi, o_lo, g,
-                                                             scale, shift, (int)m_tiles, n_tiles);
-  TP_LAUNCH_CHECK("conv_tf32x3_persistent");
+  TP_REQUIRE(m_tiles * n_tiles < (1ll << 30), TP_ERR_LIMIT, "tp_conv_tf32x3: too many tiles");
+  long long grid = m_tiles * n_tiles * (PAIR ? 2 : 1);
+  const long long cap = PAIR ? (sm_count() & ~1) : sm_count();
+  if (grid > cap) grid = cap;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = PAIR ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TP_CUDA(cudaLaunchKernelEx(&cfg, kern, a_hi, a_lo, b_hi, b_lo, o_hi, o_lo, g, scale, shift,
+                             (int)m_tiles, n_tiles));
   return TP_OK;
 }
 
@@ -1115,11 +1297,20 @@ static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H
   if (Cout <= 16)
     return launch_conv<16, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
   if (persistent) {
-    if (Cout <= 64)
-      return launch_conv_persistent<64, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo,
-                                             st);
-    return launch_conv_persistent<128, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi, y_lo,
-                                            st);
+    // CTA pairs (256-row tiles, half of B per SM) whenever there are at least two image blocks
+    const bool pair = tuning().conv_pair != 1 && (N + g.bn - 1) / g.bn >= 2;
+    if (Cout <= 64) {
+      if (pair)
+        return launch_conv_persistent<64, F16, true>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi,
+                                                     y_lo, st);
+      return launch_conv_persistent<64, F16, false>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi,
+                                                    y_lo, st);
+    }
+    if (pair)
+      return launch_conv_persistent<128, F16, true>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi,
+                                                    y_lo, st);
+    return launch_conv_persistent<128, F16, false>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi,
+                                                   y_lo, st);
   }
   if (Cout <= 64)
     return launch_conv<64, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
