@@ -44,8 +44,8 @@ int tp_device_check(int device);
  *   reduce_variant (0 auto, 1 direct-load, 2 TMA-bulk tiles), reduce_stages (2..8),
  *   reduce_tile_floats (multiple of 256), reduce_ctas_per_sm, reduce_tma_min_elems,
  *   reduce_ldg_waves; conv_variant (0 persistent, 1 one tile per CTA), conv_promote (k-blocks per
- *   TMEM partial sum), conv_pos_major (0 auto, 1 never), conv_pos_major_max_hw, conv_pair (0 auto:
- *   256-row tiles on CTA pairs, 1: single-CTA tiles only).
+ *   TMEM partial sum), conv_pos_major (0 auto, 1 never), conv_pos_major_max_hw, conv_pair (256-row
+ *   tiles on CTA pairs: 0 where measured faster, 1 never, 2 wherever possible).
  * Returns TP_ERR_INVALID for an unknown key or an out-of-range value. */
 int tp_set_tuning(const char* key, int64_t value);
 

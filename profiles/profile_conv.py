@@ -77,6 +77,21 @@ def main():
         for shp in (LAYERS[0], LAYERS[6]):
             run(*shp, (images_for_f16 if F16 else images_for)(*shp[:3]), iters=1)
         return
+    if "pair" in sys.argv:   # A/B: single-CTA tiles (conv_pair=1) against CTA pairs (0)
+        print("pair  H  W  Cin Cout taps      N     ms  executed_TF/s (3 MMAs per product, skipped taps not counted)")
+        for single in (1, 0):
+            _lib.set_tuning("conv_pair", 1 if single else 2)
+            tot_ms = tot_fl = 0.0
+            for (H, W, Cin, Cout, taps) in LAYERS:
+                N = (images_for_f16 if F16 else images_for)(H, W, Cin)
+                ms, _ = run(H, W, Cin, Cout, taps, N)
+                fl = 3.0 * _lib.load().tp_conv_tf32x3_flops(N, H, W, Cin, Cout, taps)
+                tot_ms += ms
+                tot_fl += fl
+                print(f"{1 - single:4d} {H:2d} {W:2d} {Cin:4d} {Cout:4d} {taps:4d} {N:6d} {ms:7.3f} {fl / ms / 1e9:10.1f}")
+            print(f"# pair={1 - single}: weighted {tot_fl / tot_ms / 1e9:.1f} executed TF/s")
+        _lib.set_tuning("conv_pair", 0)
+        return
     print("variant promote  H  W  Cin Cout taps      N     ms  useful_TF/s  executed_TF/s")
     print("# (variant 2 = persistent kernel with position-major tiles disabled; FLOPs are the")
     print("#  nominal 2*pixels*Cout*9*Cin, so skipped padding taps show up as > peak)")

@@ -90,7 +90,7 @@ int tp_set_tuning(const char* key, int64_t value) {
     TP_REQUIRE(value == 0 || value == 1, TP_ERR_INVALID, "conv_variant must be 0 or 1");
     t.conv_variant = (int)value;
   } else if (!strcmp(key, "conv_pair")) {
-    TP_REQUIRE(value == 0 || value == 1, TP_ERR_INVALID, "conv_pair must be 0 or 1");
+    TP_REQUIRE(value >= 0 && value <= 2, TP_ERR_INVALID, "conv_pair must be 0, 1 or 2");
     t.conv_pair = (int)value;
   } else if (!strcmp(key, "conv_promote")) {
     TP_REQUIRE(value >= 1 && value <= 4096, TP_ERR_INVALID, "conv_promote must be in [1,4096]");

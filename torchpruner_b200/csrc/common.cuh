@@ -55,7 +55,7 @@ struct Tuning {
   int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
   int conv_pos_major = 0;        // 0 auto (position-major tiles for small images), 1 never
   int conv_pos_major_max_hw = 64;  // largest H*W that gets position-major tiles
-  int conv_pair = 0;             // 0 auto (CTA pairs, cta_group::2), 1 single-CTA tiles only
+  int conv_pair = 0;             // CTA pairs (cta_group::2): 0 where measured faster, 1 never, 2 always
 };
 Tuning& tuning();
 

@@ -1297,8 +1297,15 @@ static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H
   if (Cout <= 16)
     return launch_conv<16, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
   if (persistent) {
-    // CTA pairs (256-row tiles, half of B per SM) whenever there are at least two image blocks
-    const bool pair = tuning().conv_pair != 1 && (N + g.bn - 1) / g.bn >= 2;
+    // CTA pairs (256-row tiles, half of B per SM) where they were measured faster than single-CTA
+    // tiles (profiles/r02_conv_pair_ab.txt): long reductions — K >= 4608, the 512-channel 3x3
+    // layers (+5..7 %) — and wide linear layers (+10 %).  With a short K loop the extra
+    // cross-SM hand-shakes per tile cost more than the saved operand traffic (-20 % at K = 576).
+    // conv_pair = 2 forces pairs wherever they are possible (tests).
+    const long long K = (long long)taps * Cin;
+    const bool pair_wins = K >= 4608 || (taps == 1 && K >= 512 && Cout >= 128);
+    const bool pair = tuning().conv_pair != 1 && (N + g.bn - 1) / g.bn >= 2 &&
+                      (pair_wins || tuning().conv_pair == 2);
     if (Cout <= 64) {
       if (pair)
         return launch_conv_persistent<64, F16, true>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, y_hi,
