@@ -207,7 +207,7 @@ def time_reductions(device, hbm_peak):
     stream = torch.cuda.current_stream(device)
 
     def timed(fn, iters=9):
-        for _ in range(3):
+        for _ in range(2):
             fn()
         ms = []
         for _ in range(iters):
@@ -230,9 +230,16 @@ def time_reductions(device, hbm_peak):
         "apoz": (lambda i: _lib.apoz_count(zs[i]), 4),
         "sensitivity": (lambda i: _lib.abs_sum(gs[i]), 4),
     }
+    # the 13 layers in ONE launch (tp_reduce_rows_multi, what `run_many` issues per batch)
+    multi = {
+        "taylor": lambda: _lib.reduce_rows_multi("taylor", list(zip(zs, gs))),
+        "apoz": lambda: _lib.reduce_rows_multi("apoz", zs),
+        "sensitivity": lambda: _lib.reduce_rows_multi("abs_sum", gs),
+    }
     out = {}
     for op, (fn, mult) in ops.items():
         nbytes = [mult * int(np.prod(s)) + 4 * s[0] * s[1] for s in layer_shapes]
+        multi_ms = timed(multi[op])
         sweep_ms = timed(lambda: [fn(i) for i in range(13)])
         # the same 13 launches captured once in a CUDA graph and replayed: launch-bound inner
         # loops belong in graphs; this removes the host enqueue cost from the device timeline
@@ -253,24 +260,63 @@ def time_reductions(device, hbm_peak):
         for i in (0, 2, 4, 7, 10):
             per["x".join(map(str, layer_shapes[i]))] = round(nbytes[i] / timed(lambda: fn(i)) / 1e6, 1)
         out[op] = {
-            "c2_sweep_gbs": sum(nbytes) / sweep_ms / 1e6,
-            "c2_sweep_frac": sum(nbytes) / sweep_ms / 1e6 / hbm_peak,
-            "c2_sweep_us": sweep_ms * 1e3, "c2_sweep_bytes": sum(nbytes), "c2_sweep_launches": 13,
+            "c2_sweep_gbs": sum(nbytes) / multi_ms / 1e6,
+            "c2_sweep_frac": sum(nbytes) / multi_ms / 1e6 / hbm_peak,
+            "c2_sweep_us": multi_ms * 1e3, "c2_sweep_bytes": sum(nbytes), "c2_sweep_launches": 1,
+            "c2_sweep_note": "all 13 layers' tensors in one tp_reduce_rows_multi launch, eager "
+                             "(no CUDA graph); *_13_launches = one launch per layer",
+            "c2_sweep_13_launches_gbs": sum(nbytes) / sweep_ms / 1e6,
+            "c2_sweep_13_launches_frac": sum(nbytes) / sweep_ms / 1e6 / hbm_peak,
+            "c2_sweep_13_launches_us": sweep_ms * 1e3,
             "c2_sweep_graph_gbs": (sum(nbytes) / graph_ms / 1e6) if graph_ms else None,
             "c2_sweep_graph_frac": (sum(nbytes) / graph_ms / 1e6 / hbm_peak) if graph_ms else None,
             "per_shape_gbs": per,
         }
     del zs, gs
-    z = torch.relu(torch.randn(big, device=device))
-    g = torch.randn(big, device=device)
-    n, rows = z.numel(), big[0] * big[1]
-    for op, fn, nb in (("taylor", lambda: _lib.taylor_reduce(z, g), 8 * n + 4 * rows),
-                       ("apoz", lambda: _lib.apoz_count(z), 4 * n + 4 * rows),
-                       ("sensitivity", lambda: _lib.abs_sum(g), 4 * n + 4 * rows)):
-        gbs = nb / timed(fn) / 1e6
-        out[op]["c4_largest_gbs"] = gbs
-        out[op]["c4_largest_frac"] = gbs / hbm_peak
-    del z, g, flush
+    # Config 4: every convolution output of ResNet-50 at bs 256 (53 tensors, 11.4 GB of
+    # activations: 25.7 MB ... 822 MB each), one launch per tensor as `run()` issues them.  Shapes
+    # are read off torchvision's model; each distinct shape is timed once and weighted by how
+    # often it occurs.  Rows of 7x7 = 49 floats are not 16-byte aligned.
+    shapes = {}
+    try:
+        import torchvision
+        net = torchvision.models.resnet50(num_classes=10).to(device).eval()
+        hooks = [m.register_forward_hook(
+            lambda _m, _i, o: shapes.__setitem__(tuple(o.shape[1:]), shapes.get(tuple(o.shape[1:]), 0) + 1))
+            for m in net.modules() if isinstance(m, torch.nn.Conv2d)]
+        with torch.no_grad():
+            net(torch.zeros((1, 3, 224, 224), device=device))
+        for h in hooks:
+            h.remove()
+        del net
+    except Exception as e:  # noqa: BLE001
+        log(f"bench.py: ResNet-50 shapes unavailable ({e}); timing the largest one only")
+        shapes = {(64, 112, 112): 1}
+    totals = {op: [0.0, 0.0] for op in ops}   # bytes, ms
+    per_shape = {op: {} for op in ops}
+    for (C, H, W), count in sorted(shapes.items(), key=lambda kv: -kv[0][0] * kv[0][1] * kv[0][2]):
+        z = torch.relu(torch.randn((256, C, H, W), device=device))
+        g = torch.randn((256, C, H, W), device=device)
+        n, rows = z.numel(), 256 * C
+        for op, fn, nb in (("taylor", lambda: _lib.taylor_reduce(z, g), 8 * n + 4 * rows),
+                           ("apoz", lambda: _lib.apoz_count(z), 4 * n + 4 * rows),
+                           ("sensitivity", lambda: _lib.abs_sum(g), 4 * n + 4 * rows)):
+            ms = timed(fn, iters=5)
+            totals[op][0] += count * nb
+            totals[op][1] += count * ms
+            per_shape[op][f"256x{C}x{H}x{W} (x{count})"] = round(nb / ms / 1e6, 1)
+            if (C, H, W) == (64, 112, 112):
+                out[op]["c4_largest_gbs"] = nb / ms / 1e6
+                out[op]["c4_largest_frac"] = nb / ms / 1e6 / hbm_peak
+        del z, g
+    for op in ops:
+        nbytes, ms = totals[op]
+        out[op]["c4_sweep_gbs"] = nbytes / ms / 1e6
+        out[op]["c4_sweep_frac"] = nbytes / ms / 1e6 / hbm_peak
+        out[op]["c4_sweep_bytes"] = nbytes
+        out[op]["c4_sweep_launches"] = sum(shapes.values())
+        out[op]["c4_per_shape_gbs"] = per_shape[op]
+    del flush
     torch.cuda.empty_cache()
     return out
 
@@ -519,6 +565,16 @@ def secondary_configs(device):
                      "own_kernel_launches": sum(v[0] for v in prof.records.values())}
         _lib.profile_end()
         model.zero_grad()
+    for name, cls in classes.items():   # the 13 layers from ONE pass (run_many; not in the reference)
+        m = cls(model, loader, workloads.cross_entropy, device)
+        m.run_many(convs[:2], find_best_evaluation_module=True)
+        model.zero_grad()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        m.run_many(convs, find_best_evaluation_module=True)
+        torch.cuda.synchronize(device)
+        gpu[name]["seconds_13_layers_run_many"] = time.perf_counter() - t0
+        model.zero_grad()
     # CPU port: first, middle and last conv layer (3 of 13; every layer costs one full
     # forward(+backward) of the same model, so the 13-layer time is 13/3 of the sample)
     cpu_model = _CPU_STATE.setdefault("model", workloads.build("vgg16_cifar", seed=1)[0])
@@ -536,6 +592,9 @@ def secondary_configs(device):
             gpu[name]["seconds_13_layers"]
     out["c2_scores_e2e"] = dict(gpu, cpu_cores=torch.get_num_threads(),
                                 cpu_sample="layers features.0/20/40 of 13, x13/3")
+
+    out["c1_small_cnn"] = config1(device)
+    out["c4_scores_e2e"] = config4(device)
 
     # config 5
     def cascade(pruner_factory, dev):
@@ -566,6 +625,114 @@ def secondary_configs(device):
                                           "for every module, as the reference does",
                                "cpu_port_seconds": t_cpu, "modules": 15,
                                "own_kernel_launches": launches, "cpu_cores": torch.get_num_threads()}
+    return out
+
+
+def config1(device):
+    """Config 1 (small 2-conv + 2-fc CNN, 1x28x28, bs 64, N = 128): Taylor / APoZ / WeightNorm /
+    Shapley(sv_samples=5) on both convolutions plus the 3-module cascading prune, through the
+    public API, beside the CPU port on the host cores.  conv1's Shapley tail starts with a 3x3
+    convolution with padding 2 — outside the engine's vocabulary — so it runs the model's own
+    forward_partial (cuDNN / cuBLAS) on stacked masks; conv2's tail runs on the engine."""
+    from oracle import tp_oracle as oracle
+    from torchpruner_b200.attributions import (APoZAttributionMetric, ShapleyAttributionMetric,
+                                               TaylorAttributionMetric, WeightNormAttributionMetric)
+    from torchpruner_b200.pruner import Pruner
+    from torchpruner_b200.utils import find_best_module_for_attributions
+
+    def gpu_pass(model, shape):
+        loader = workloads.synthetic_batches(shape, n=128, batch_size=64, pin=True)
+        convs = [model.features[0], model.features[3]]
+        engine = []
+        for conv in convs:
+            for cls in (TaylorAttributionMetric, APoZAttributionMetric, WeightNormAttributionMetric):
+                cls(model, loader, workloads.cross_entropy, device).run(
+                    conv, find_best_evaluation_module=True)
+            np.random.seed(11)
+            sh = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, device, sv_samples=5)
+            sh.run(conv, find_best_evaluation_module=True)
+            engine.append(bool(sh.last_run_info["native_tail"]))
+        np.random.seed(21)
+        pruner = Pruner(model, shape, device)
+        for module, casc in model.get_pruning_graph():
+            pruner.prune_model(module, list(range(0, module.weight.shape[0], 4)), casc)
+        torch.cuda.synchronize(device)
+        return engine
+
+    model, shape = workloads.build("small_cnn")
+    gpu_pass(model.to(device), shape)   # warm-up (plans, cuDNN)
+    model, shape = workloads.build("small_cnn")
+    model.to(device)
+    torch.cuda.synchronize(device)
+    t0 = time.perf_counter()
+    engine = gpu_pass(model, shape)
+    t_gpu = time.perf_counter() - t0
+
+    cpu, shape = workloads.build("small_cnn")
+    loader = workloads.synthetic_batches(shape, n=128, batch_size=64)
+    t0 = time.perf_counter()
+    for conv in (cpu.features[0], cpu.features[3]):
+        module = find_best_module_for_attributions(cpu, conv)
+        for kind in ("taylor", "apoz"):
+            oracle.hook_scores(cpu, list(loader), workloads.cross_entropy, module, kind)
+        oracle.weight_norm(conv.weight.detach())
+        np.random.seed(11)
+        oracle.shapley_with_partial(cpu, loader, workloads.cross_entropy, 5, 128, module)
+    np.random.seed(21)
+    pr = oracle.OraclePruner(cpu, shape)
+    for module, casc in cpu.get_pruning_graph():
+        pr.prune_model(module, list(range(0, module.weight.shape[0], 4)), casc)
+    t_cpu = time.perf_counter() - t0
+    return {"seconds": t_gpu, "cpu_port_seconds": t_cpu, "speedup_vs_cpu_port": t_cpu / t_gpu,
+            "cpu_cores": torch.get_num_threads(),
+            "shapley_tail_on_engine": {"conv1": engine[0], "conv2": engine[1]},
+            "what": "Taylor + APoZ + WeightNorm + Shapley(sv_samples=5) on conv1 and conv2, then "
+                    "prune_model over the 3-entry graph; 128 examples in batches of 64"}
+
+
+def config4(device):
+    """Config 4 end to end: Taylor and APoZ `run(conv, find_best_evaluation_module=True)` on stock
+    torchvision ResNet-50, 3x224x224, bs 256, for a sample of the 37 layers the reference is
+    defined on (every run is a full forward(+backward) of the model at bs 256).  CPU port on a
+    bs-16 batch, scaled by 16 (the per-example cost of a ResNet-50 pass does not depend on the
+    batch size once the cores are busy)."""
+    from oracle import tp_oracle as oracle
+    from torchpruner_b200.attributions import APoZAttributionMetric, TaylorAttributionMetric
+    from torchpruner_b200.utils import find_best_module_for_attributions
+
+    picks = ("conv1", "layer1.0.conv2", "layer2.0.downsample.0", "layer4.2.conv2")
+    model, shape = workloads.build("resnet50_stock")
+    g = torch.Generator().manual_seed(4)
+    hx = torch.randn((BATCH,) + tuple(shape), generator=g).pin_memory()
+    hy = torch.randint(0, 10, (BATCH,), generator=g).pin_memory()
+    out = {"layers": list(picks), "batch": BATCH, "layers_defined": 37}
+    cpu_model = workloads.build("resnet50_stock")[0]
+    cx, cy = hx[:16].clone(), hy[:16].clone()
+    model.to(device)
+    mods, cpu_mods = dict(model.named_modules()), dict(cpu_model.named_modules())
+    for name, cls in (("taylor", TaylorAttributionMetric), ("apoz", APoZAttributionMetric)):
+        m = cls(model, OneBatch(hx, hy), workloads.cross_entropy, device)
+        m.run(mods[picks[0]], find_best_evaluation_module=True)   # warm-up
+        model.zero_grad()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        for p in picks:
+            m.run(mods[p], find_best_evaluation_module=True)
+        torch.cuda.synchronize(device)
+        t_gpu = (time.perf_counter() - t0) / len(picks)
+        model.zero_grad()
+        t0 = time.perf_counter()
+        module = find_best_module_for_attributions(cpu_model, cpu_mods[picks[1]])
+        oracle.hook_scores(cpu_model, [(cx, cy)], workloads.cross_entropy, module, name)
+        t_cpu = (time.perf_counter() - t0) * (BATCH / 16)
+        cpu_model.zero_grad()
+        out[name] = {"seconds_per_layer": t_gpu, "cpu_port_seconds_per_layer_extrapolated": t_cpu,
+                     "speedup_vs_cpu_port": t_cpu / t_gpu,
+                     "seconds_37_layers_extrapolated": 37 * t_gpu}
+    out["cpu_cores"] = torch.get_num_threads()
+    out["cpu_sample"] = "one layer on 16 of the 256 examples, x16"
+    del model
+    torch.cuda.empty_cache()
     return out
 
 

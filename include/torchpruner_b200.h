@@ -73,6 +73,30 @@ int tp_abs_sum(const float* g, int64_t B, int64_t C, int64_t HW, float* out,
  * (device->host copy of the weight, numpy abs, successive sum(-1)). */
 int tp_weight_abs_sum(const float* w, int64_t Cout, int64_t K, float* out, tp_stream_t stream);
 
+/* ---------------------------------------------------------------- K1-K4, several tensors
+ * The same per-row reductions for up to TP_REDUCE_MAX_DESCS tensors in ONE launch.  Replaces the
+ * per-layer hook arithmetic of taylor.py:40-44 / apoz.py:31-33 / sensitivity.py:27-29 /
+ * weight_norm.py:15-18 when several layers are scored from one data pass (the reference runs the
+ * whole model once per layer): small activations (2-134 MB on VGG16) are launch-latency bound
+ * one at a time.  For tensor i: out[r] = reduce over len of (a[r,:], b[r,:]) with
+ *   TP_REDUCE_TAYLOR  |-sum a*b| (a = gradient, b = activation; signed when is_signed != 0)
+ *   TP_REDUCE_APOZ    #{a > 0}         (b ignored)
+ *   TP_REDUCE_ABSSUM  sum |a|          (b ignored)
+ * APoZ counts are exact; the float sums equal the single-tensor entry points' up to the order
+ * of the fp32 additions within a row (fixed, so deterministic run to run).  Rows must be a multiple of 4 floats, at most reduce_tile_floats (4096 by
+ * default) long, in 16-byte aligned tensors; otherwise TP_ERR_LIMIT and nothing is launched. */
+enum { TP_REDUCE_TAYLOR = 0, TP_REDUCE_APOZ = 1, TP_REDUCE_ABSSUM = 2 };
+#define TP_REDUCE_MAX_DESCS 64
+typedef struct {
+  const float* a;
+  const float* b;
+  float* out;     /* [rows] fp32 */
+  int64_t rows;
+  int64_t len;
+} tp_reduce_desc;
+int tp_reduce_rows_multi(int op, const tp_reduce_desc* descs, int64_t n, int is_signed,
+                         tp_stream_t stream);
+
 /* ---------------------------------------------------------------- K5
  * Stack of P prefix masks over a cached activation.  For p in [0,P):
  *   out[p,b,c,:] = (inv_perm[c] <= k0 + p) ? +0.0f : z[b,c,:]

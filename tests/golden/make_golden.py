@@ -281,7 +281,44 @@ def gen_ablation():
     print("ablation:", len(out), "arrays")
 
 
-GROUPS = {"ablation": gen_ablation, "ops": gen_ops, "max_model": gen_max_model, "small_cnn": gen_small_cnn, "vgg": gen_vgg,
+def gen_resnet():
+    """Config 4: the reference on STOCK torchvision ResNet-50 with find_best_evaluation_module=True
+    (8 examples of 3x96x96 in two batches; 96 leaves 3x3 = 9-float rows in the last stage, which are
+    not 16-byte aligned).  For each of the 53 convolutions: Taylor / APoZ / Sensitivity per-example
+    tables where the reference is defined, the exception class where it is not."""
+    out, lines = {}, []
+    model, _ = workloads.build("resnet50_stock")
+    loader = workloads.synthetic_batches((3, 96, 96), n=8, batch_size=4, seed=9)
+    names = {m: n for n, m in model.named_modules()}
+    convs = [m for m in model.modules() if isinstance(m, nn.Conv2d)]
+    assert len(convs) == 53
+    kinds = (("taylor", TaylorAttributionMetric), ("apoz", APoZAttributionMetric),
+             ("sensitivity", SensitivityAttributionMetric))
+    for conv in convs:
+        tag = names[conv]
+        best = quiet(find_best_module_for_attributions, model, conv)
+        for kind, cls in kinds:
+            for m in model.modules():   # a failed run leaves hooks' attributes behind
+                for attr in ("_tp_taylor", "_tp_activation", "_tp_nonzero_count", "_tp_gradient"):
+                    if hasattr(m, attr):
+                        delattr(m, attr)
+                m._forward_hooks.clear()
+                m._backward_hooks.clear()
+            model.zero_grad()
+            try:
+                metric = cls(model, loader, workloads.cross_entropy, "cpu", reduction="none")
+                out[f"{tag}/{kind}"] = quiet(metric.run, conv, find_best_evaluation_module=True)
+                lines.append(f"{tag} {kind} ok eval={names[best]} shape={out[f'{tag}/{kind}'].shape}")
+            except Exception as exc:  # noqa: BLE001 - the class of the failure IS the golden
+                lines.append(f"{tag} {kind} raises {type(exc).__name__} eval={names[best]}")
+        print("  resnet", lines[-1], flush=True)
+    np.savez_compressed(os.path.join(HERE, "resnet50.npz"), **out)
+    with open(os.path.join(HERE, "resnet50.txt"), "w") as f:
+        f.write("\n".join(lines) + "\n")
+    print("resnet50:", len(out), "arrays,", sum(" raises " in line for line in lines), "failures")
+
+
+GROUPS = {"resnet": gen_resnet, "ablation": gen_ablation, "ops": gen_ops, "max_model": gen_max_model, "small_cnn": gen_small_cnn, "vgg": gen_vgg,
           "mlp": gen_mlp, "graph": gen_graph, "prune": gen_prune}
 
 if __name__ == "__main__":

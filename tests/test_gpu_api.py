@@ -273,6 +273,69 @@ def test_vgg16_shapley_matches_reference(tag):
     assert np.abs(sv2 - want).max() / scale <= 5e-4
 
 
+def test_run_many_scores_every_layer_from_one_pass():
+    """`run_many(modules)`: all 13 VGG16 layers from ONE forward / backward per batch and one
+    reduction launch per batch, against 13 separate `run` calls (what the reference does)."""
+    from torchpruner_b200 import _lib
+    model, shape = workloads.build("vgg16_cifar")
+    model.to(DEV)
+    loader = workloads.synthetic_batches(shape, n=40, batch_size=16)   # ragged last batch
+    convs = model.conv_layers()
+    for cls, kw in ((TaylorAttributionMetric, {}), (TaylorAttributionMetric, {"signed": True}),
+                    (SensitivityAttributionMetric, {}), (APoZAttributionMetric, {}),
+                    (WeightNormAttributionMetric, {})):
+        m = cls(model, loader, workloads.cross_entropy, DEV, reduction="none", **kw)
+        prof = _lib.profile_begin(timed=False)
+        many = m.run_many(convs, find_best_evaluation_module=True)
+        launches = {k: v[0] for k, v in prof.records.items()}
+        _lib.profile_end()
+        model.zero_grad()
+        assert len(many) == 13
+        if cls is not WeightNormAttributionMetric:
+            assert sum(launches.values()) == 3, launches     # one launch per batch
+        for conv, got in zip(convs, many):
+            want = m.run(conv, find_best_evaluation_module=True)
+            model.zero_grad()
+            assert got.shape == want.shape and got.dtype == want.dtype
+            if cls is APoZAttributionMetric:
+                np.testing.assert_array_equal(got, want)
+            else:
+                assert norm_err(got, want) <= 1e-5
+    # the same module asked for twice, and the base class fallback (one run per module)
+    a = APoZAttributionMetric(model, loader, workloads.cross_entropy, DEV)
+    twice = a.run_many([convs[3], convs[3]], find_best_evaluation_module=True)
+    np.testing.assert_array_equal(twice[0], twice[1])
+    np.random.seed(0)
+    r = RandomAttributionMetric(model, loader, workloads.cross_entropy, DEV).run_many(convs[:2])
+    assert [x.shape for x in r] == [(64,), (64,)]
+
+
+def test_run_many_rescores_layers_whose_activation_is_overwritten():
+    """Stock ResNet-50: the evaluation module of conv1 / conv2 is a BatchNorm whose output the
+    block's in-place ReLU overwrites before the pass is over, and every conv3's is the shared
+    ReLU.  run_many must notice (version counters) and give those layers a pass of their own —
+    same numbers as `run`, same error for conv3."""
+    model, _ = workloads.build("resnet50_stock")
+    model.to(DEV)
+    loader = workloads.synthetic_batches((3, 96, 96), n=8, batch_size=4, seed=9)
+    mods = dict(model.named_modules())
+    picked = [mods[n] for n in ("conv1", "layer1.0.conv1", "layer2.1.conv2", "layer3.0.downsample.0")]
+    for cls in (TaylorAttributionMetric, APoZAttributionMetric):
+        m = cls(model, loader, workloads.cross_entropy, DEV, reduction="none")
+        many = m.run_many(picked, find_best_evaluation_module=True)
+        model.zero_grad()
+        for mod, got in zip(picked, many):
+            want = m.run(mod, find_best_evaluation_module=True)
+            model.zero_grad()
+            if cls is APoZAttributionMetric:
+                np.testing.assert_array_equal(got, want)
+            else:
+                assert norm_err(got, want) <= 1e-5
+        with pytest.raises(RuntimeError, match="different channel counts"):
+            m.run_many([picked[0], mods["layer1.0.conv3"]], find_best_evaluation_module=True)
+        model.zero_grad()
+
+
 def test_shapley_schedules_agree():
     """Stacked evaluation, one-mask-at-a-time evaluation (train-mode fallback), any stack size and
     any rank split produce the same table up to fp32 rounding of the batched layers."""
@@ -582,6 +645,55 @@ def test_resnet50_all_convs_taylor_apoz_sensitivity():
         np.testing.assert_array_equal(a, wa)
         checked += 1
     assert checked >= 15
+
+
+def test_stock_resnet50_matches_the_reference_where_it_is_defined():
+    """Config 4 on torchvision's ResNet-50 as it ships, find_best_evaluation_module=True, against
+    the unmodified reference (tests/golden/resnet50.{npz,txt}, make_golden.py gen_resnet).
+
+    `find_best_module_for_attributions` walks declaration order (utils/graph.py:19-31), so the
+    evaluation module is the stem's ReLU for conv1, the following BatchNorm for every
+    conv1 / conv2 / downsample convolution — 37 layers on which all three hook metrics are
+    defined — and the block's single shared `relu` for every conv3, which fires three times per
+    forward with different channel counts: there the reference fails inside numpy / torch
+    (apoz.py:37, taylor.py:40) and this library raises a RuntimeError that says why."""
+    g = gold("resnet50.npz")
+    with open(os.path.join(GOLDEN, "resnet50.txt")) as f:
+        rows = [line.split() for line in f if line.strip()]
+    model, _ = workloads.build("resnet50_stock")
+    model.to(DEV)
+    loader = workloads.synthetic_batches((3, 96, 96), n=8, batch_size=4, seed=9)
+    modules = dict(model.named_modules())
+    classes = {"taylor": TaylorAttributionMetric, "apoz": APoZAttributionMetric,
+               "sensitivity": SensitivityAttributionMetric}
+    worst = {"taylor": 0.0, "sensitivity": 0.0}
+    apoz_cells = apoz_off = ok = failing = 0
+    for tag, kind, status, *rest in rows:
+        metric = classes[kind](model, loader, workloads.cross_entropy, DEV, reduction="none")
+        model.zero_grad()
+        if status == "raises":
+            assert tag.endswith("conv3") and rest[0] in ("ValueError", "RuntimeError")
+            with pytest.raises(RuntimeError, match="different channel counts|shared"):
+                metric.run(modules[tag], find_best_evaluation_module=True)
+            failing += 1
+            continue
+        got = metric.run(modules[tag], find_best_evaluation_module=True)
+        want = g[f"{tag}/{kind}"]
+        assert got.shape == want.shape and got.dtype == want.dtype == np.float32
+        if kind == "apoz":
+            # counts of `z > 0` behind a BatchNorm: a value within rounding of 0 can land on the
+            # other side after a differently rounded forward (SURVEY 8c, tier B)
+            apoz_cells += want.size
+            apoz_off += int((got != want).sum())
+            assert np.abs(got - want).max() <= 3
+        else:
+            worst[kind] = max(worst[kind], norm_err(got, want))
+        ok += 1
+    print("stock ResNet-50 vs reference-CPU: worst normalised error", worst,
+          f"APoZ cells differing {apoz_off} of {apoz_cells}")
+    assert ok == 111 and failing == 48
+    assert worst["taylor"] <= 1e-3 and worst["sensitivity"] <= 1e-3, worst
+    assert apoz_off <= apoz_cells // 200
 
 
 def test_shapley_full_size_telescopes():

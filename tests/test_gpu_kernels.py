@@ -52,6 +52,46 @@ def test_row_reductions_match_reference_vectors(name, variant):
     close(_lib.abs_sum(gc).cpu().numpy(), oracle.abs_sum_rows_f64(g))
 
 
+def test_several_tensors_in_one_launch_match_the_oracle():
+    """tp_reduce_rows_multi: the 13 activation shapes of VGG16 (scaled down), rows of 4 ... 1024
+    floats, plus tensors it cannot take (49-float rows, rows longer than a tile, an empty one)
+    that the wrapper sends through the single-tensor entry points — all against the oracle."""
+    shapes = [(6, 64, 32, 32), (6, 64, 32, 32), (6, 128, 16, 16), (5, 256, 8, 8), (7, 512, 4, 4),
+              (9, 512, 2, 2), (3, 512, 2, 2), (4, 33, 12), (2, 5, 4096), (11, 7, 4),
+              (4, 16, 7, 7), (2, 3, 8192), (0, 8, 4, 4), (3, 2048)]
+    gen = torch.Generator().manual_seed(5)
+    zs = [torch.relu(torch.randn(s, generator=gen)) for s in shapes]
+    gs = [torch.randn(s, generator=gen) / 7 for s in shapes]
+    zd, gd = [z.to(DEV) for z in zs], [g.to(DEV) for g in gs]
+    prof = _lib.profile_begin(timed=False)
+    tay = _lib.reduce_rows_multi("taylor", list(zip(zd, gd)), signed=True)
+    launches = {k: v[0] for k, v in prof.records.items()}
+    _lib.profile_end()
+    # 10 tensors in ONE launch; (4,16,7,7), (2,3,8192) and [3, 2048] viewed as rows of 1 go alone
+    assert launches.get("reduce_rows_multi[taylor]") == 1 and sum(launches.values()) <= 4, launches
+    apoz = _lib.reduce_rows_multi("apoz", zd)
+    sens = _lib.reduce_rows_multi("abs_sum", gd)
+    unsigned = _lib.reduce_rows_multi("taylor", list(zip(zd, gd)))
+    for i, (z, g) in enumerate(zip(zs, gs)):
+        if z.numel() == 0:
+            assert tay[i].numel() == 0 and apoz[i].shape == (0, 8)
+            continue
+        close(tay[i].cpu().numpy(), oracle.taylor_rows_f64(z, g, True))
+        close(unsigned[i].cpu().numpy(), oracle.taylor_rows(z, g))
+        close(sens[i].cpu().numpy(), oracle.abs_sum_rows_f64(g))
+        np.testing.assert_array_equal(apoz[i].cpu().numpy(), oracle.apoz_rows(z))
+    # more tensors than one descriptor table holds
+    many = [torch.relu(torch.randn((3, 4, 8), generator=gen)).to(DEV) for _ in range(70)]
+    for got, z in zip(_lib.reduce_rows_multi("apoz", many), many):
+        np.testing.assert_array_equal(got.cpu().numpy(), oracle.apoz_rows(z.cpu()))
+    # through the C-ABI: limits are errors, nothing is launched
+    bad = (_lib.ReduceDesc * 1)(_lib.ReduceDesc(zd[10].data_ptr(), 0, apoz[10].data_ptr(), 64, 49))
+    assert _lib.load().tp_reduce_rows_multi(1, bad, 1, 0, None) == -4      # TP_ERR_LIMIT
+    assert b"multiple" in _lib.load().tp_last_error()
+    assert _lib.load().tp_reduce_rows_multi(1, bad, 65, 0, None) == -4
+    assert _lib.load().tp_reduce_rows_multi(7, bad, 1, 0, None) == -1      # unknown op
+
+
 @pytest.mark.parametrize("name", sorted(cases.WEIGHT_SHAPES))
 def test_weight_norm_matches_reference_vectors(name, variant):
     w = cases.weight_input(name)

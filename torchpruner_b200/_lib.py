@@ -36,6 +36,15 @@ class GatherDesc(ctypes.Structure):
     ]
 
 
+class ReduceDesc(ctypes.Structure):
+    """Mirror of `tp_reduce_desc`."""
+
+    _fields_ = [("a", _vp), ("b", _vp), ("out", _vp), ("rows", _i64), ("len", _i64)]
+
+
+TP_REDUCE_MAX_DESCS = 64
+REDUCE_OPS = {"taylor": 0, "apoz": 1, "abs_sum": 2}
+
 _SIGNATURES = {
     "tp_version": (ctypes.c_int, []),
     "tp_last_error": (ctypes.c_char_p, []),
@@ -45,6 +54,8 @@ _SIGNATURES = {
     "tp_apoz_count": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "tp_abs_sum": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _vp]),
     "tp_weight_abs_sum": (ctypes.c_int, [_vp, _i64, _i64, _vp, _vp]),
+    "tp_reduce_rows_multi": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ReduceDesc), _i64,
+                                            ctypes.c_int, _vp]),
     "tp_prefix_mask_stack": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "tp_index_fill_dim1": (ctypes.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, ctypes.c_uint32, _vp]),
     "tp_loss_delta_scatter": (
@@ -263,6 +274,46 @@ def abs_sum(g, out=None):
     with torch.cuda.device(g.device), _launch("abs_sum", 4 * g.numel() + 4 * B * C, g, 1):
         _check(load().tp_abs_sum(g.data_ptr(), B, C, hw, out.data_ptr(), _stream(g)), "tp_abs_sum")
     return out
+
+
+def reduce_rows_multi(op, tensors, signed=False):
+    """The per-row reduction ``op`` ("taylor": pairs (z, g); "apoz" / "abs_sum": single tensors,
+    viewed as [shape[0] * shape[1], rest] — or [shape[0], rest] with ``rows_dim0`` semantics for
+    2-D weights, see ``weight_abs_sum_many``) of several tensors in as few launches as possible:
+    everything ``tp_reduce_rows_multi`` accepts goes into launches of up to 64 tensors, the rest
+    (rows that are no multiple of 4 floats, or longer than a tile) through the single-tensor
+    entry points.  Returns the [B, C] results in order."""
+    code = REDUCE_OPS[op]
+    outs, batch = [None] * len(tensors), []
+    tile = 4096
+    for i, item in enumerate(tensors):
+        a, b = (item[1], item[0]) if op == "taylor" else (item, None)   # a = gradient, b = z
+        a = _cuda_f32(a, "tensor")
+        B, C, hw = _bchw(a)
+        if b is not None:
+            b = _cuda_f32(b, "tensor")
+            if b.shape != a.shape:
+                raise TorchPrunerB200Error("activation and gradient shapes differ")
+        ok = hw % 4 == 0 and 0 < hw <= tile and a.data_ptr() % 16 == 0 and \
+            (b is None or b.data_ptr() % 16 == 0) and B * C > 0
+        if not ok:
+            outs[i] = taylor_reduce(b, a, signed) if op == "taylor" else \
+                (apoz_count(a) if op == "apoz" else abs_sum(a))
+            continue
+        out = torch.empty((B, C), dtype=torch.float32, device=a.device)
+        outs[i] = out
+        batch.append((a, b, out, B * C, hw))
+    for start in range(0, len(batch), TP_REDUCE_MAX_DESCS):
+        part = batch[start:start + TP_REDUCE_MAX_DESCS]
+        descs = (ReduceDesc * len(part))(*[
+            ReduceDesc(a.data_ptr(), b.data_ptr() if b is not None else 0, out.data_ptr(), rows, hw)
+            for a, b, out, rows, hw in part])
+        first = part[0][0]
+        nbytes = sum((8 if b is not None else 4) * a.numel() + 4 * rows for a, b, _, rows, _ in part)
+        with torch.cuda.device(first.device), _launch(f"reduce_rows_multi[{op}]", nbytes, first, 1):
+            _check(load().tp_reduce_rows_multi(code, descs, len(part), int(bool(signed)),
+                                               _stream(first)), "tp_reduce_rows_multi")
+    return outs
 
 
 def weight_abs_sum(w):

@@ -11,6 +11,8 @@ from abc import ABC, abstractmethod
 
 import numpy as np
 import torch
+
+from .. import _lib
 import torch.nn as nn
 from torch.nn.modules.conv import _ConvNd
 
@@ -47,6 +49,97 @@ class _RowCollector:
         return table.cpu().numpy()
 
 
+class _ManyCapture:
+    """Forward hooks on several evaluation modules for ONE pass over a batch: keeps a reference to
+    each module's output (and, on request, to the gradient that reaches it) until ``flush``.
+
+    Nothing is cloned.  A reference is only as good as the tensor stays unmodified, so the
+    version counter is noted at hook time and compared at flush time: a module whose output was
+    written in place in between (a BatchNorm followed by an in-place ReLU) is reported in
+    ``spoiled`` and has to be scored on its own with ``run``, which snapshots."""
+
+    def __init__(self, eval_modules, want_grad):
+        self.modules = eval_modules
+        self.want_grad = want_grad
+        self.z, self.version, self.grad = {}, {}, {}
+        self.spoiled = set()
+        self.handles = []
+
+    def __enter__(self):
+        for k, mod in enumerate(self.modules):
+            self.handles.append(mod.register_forward_hook(self._hook(k)))
+        return self
+
+    def __exit__(self, *exc):
+        for h in self.handles:
+            h.remove()
+        return False
+
+    def _hook(self, k):
+        def forward_hook(_mod, _inputs, output):
+            if not isinstance(output, torch.Tensor):
+                return
+            if k in self.z:   # fired twice in one forward: shared module, undefined per layer
+                self.spoiled.add(k)
+                return
+            if self.want_grad:
+                if not output.requires_grad:
+                    return
+                output.register_hook(lambda grad, k=k: self.grad.__setitem__(k, grad))
+            self.z[k] = output.detach()
+            self.version[k] = output._version
+        return forward_hook
+
+    def flush(self):
+        """[(k, z, grad or None)] of the modules captured intact in this batch; clears."""
+        items = []
+        for k, z in self.z.items():
+            if z._version != self.version[k]:
+                self.spoiled.add(k)
+            if k in self.spoiled or (self.want_grad and k not in self.grad):
+                continue
+            items.append((k, z, self.grad.get(k)))
+        self.z, self.version, self.grad = {}, {}, {}
+        return items
+
+
+def _score_many(metric, modules, kwargs, op, want_grad, what, signed=False):
+    """Shared body of the hook metrics' ``run_many``."""
+    evals = [_AttributionMetric.run(metric, m, **kwargs) for m in modules]
+    distinct = []
+    for e in evals:
+        if not any(e is d for d in distinct):
+            distinct.append(e)
+    rows = [_RowCollector() for _ in distinct]
+    with _ManyCapture(distinct, want_grad) as cap:
+        metric.set_deterministic()
+        try:
+            for x, y in metric._batches():
+                if want_grad:
+                    metric.criterion(metric.model(x), y).backward()
+                else:
+                    with torch.no_grad():
+                        metric.model(x)
+                items = cap.flush()
+                tensors = [(z, g) if op == "taylor" else (g if want_grad else z) for _, z, g in items]
+                for (k, _, _), out in zip(items, _lib.reduce_rows_multi(op, tensors, signed)):
+                    rows[k].add(out)
+        finally:
+            metric.restore_deterministic()
+    results = {}
+    for k, e in enumerate(distinct):
+        if k in cap.spoiled:   # needs the snapshot only a pass of its own can take
+            results[id(e)] = None
+        else:
+            results[id(e)] = metric.aggregate_over_samples(rows[k].numpy(what))
+    out = []
+    for m, e in zip(modules, evals):
+        if results[id(e)] is None:
+            results[id(e)] = metric.run(m, **kwargs)
+        out.append(results[id(e)])
+    return out
+
+
 class _AttributionMetric(ABC):
     def __init__(self, model, data_generator, criterion, device, reduction="mean"):
         assert reduction in ["mean", "none", "sum"] or callable(reduction), \
@@ -66,6 +159,13 @@ class _AttributionMetric(ABC):
         assert isinstance(module, tuple(SUPPORTED_OUT_PRUNING_MODULES)), \
             f"Attributions can be computed only for the following modules {SUPPORTED_OUT_PRUNING_MODULES}"
         return self.find_evaluation_module(module, **kwargs)
+
+    def run_many(self, modules, **kwargs):
+        """Scores of several layers: ``[run(m, **kwargs) for m in modules]``.  Not in the
+        reference.  The hook metrics override it to score every layer from ONE pass over the
+        data (the reference, and ``run``, repeat the whole forward / backward per layer) and to
+        reduce all the layers' activations in one launch."""
+        return [self.run(m, **kwargs) for m in modules]
 
     def find_evaluation_module(self, module, find_best_evaluation_module=False):
         if find_best_evaluation_module is True:

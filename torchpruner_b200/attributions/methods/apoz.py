@@ -28,3 +28,8 @@ class APoZAttributionMetric(_base._AttributionMetric):
             finally:
                 handle.remove()
             return self.aggregate_over_samples(rows.numpy("activation count"))
+
+    def run_many(self, modules, **kwargs):
+        """Activation counts of several layers from one forward pass per batch and one
+        ``tp_reduce_rows_multi`` launch; integer counts, so identical to ``run``."""
+        return _base._score_many(self, modules, kwargs, "apoz", False, "activation count")

@@ -25,3 +25,8 @@ class SensitivityAttributionMetric(_base._AttributionMetric):
         finally:
             handle.remove()
         return self.aggregate_over_samples(rows.numpy("gradient"))
+
+    def run_many(self, modules, **kwargs):
+        """``sum |dL/dz|`` of several layers from one forward / backward per batch and one
+        ``tp_reduce_rows_multi`` launch."""
+        return _base._score_many(self, modules, kwargs, "abs_sum", True, "gradient")

@@ -55,3 +55,11 @@ class TaylorAttributionMetric(_base._AttributionMetric):
         finally:
             handle.remove()
         return self.aggregate_over_samples(rows.numpy("Taylor score"))
+
+    def run_many(self, modules, **kwargs):
+        """Taylor scores of several layers from one forward / backward per batch, every layer's
+        ``| - sum g * z |`` in one ``tp_reduce_rows_multi`` launch.  Same numbers as ``run`` up to
+        the order of the fp32 additions within a row; parameter gradients accumulate once per
+        pass over the data instead of once per layer."""
+        return _base._score_many(self, modules, kwargs, "taylor", True, "Taylor score",
+                                 signed=self.signed)

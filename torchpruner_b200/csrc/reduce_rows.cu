@@ -371,6 +371,140 @@ reduce_rows_tma(const float* __restrict__ a, const float* __restrict__ b,
   }
 }
 
+// =====================================================================================
+// Several tensors, one launch.  The per-layer tensors of a VGG-sized model are 2-134 MB: a
+// launch per tensor spends as long starting and draining (~4 us of launch gap, first-byte
+// latency and tail) as streaming, and the 13-layer sweep of config 2 sat at 0.42-0.56 of the
+// HBM peak.  Here the tensors are cut into tiles of whole rows (<= tile_floats floats) that form
+// ONE list; persistent CTAs stride over it with the same TMA-bulk ring as reduce_rows_tma, so
+// the start-up and the tail are paid once per sweep and tiles of the next tensor are already in
+// flight while the last tiles of the previous one are reduced.
+// =====================================================================================
+struct MultiDesc {
+  const float* a;
+  const float* b;
+  float* out;
+  long long R;
+  long long end_tile;   // first tile index of the NEXT tensor
+  int L;
+  int tile_rows;
+  int lpr;
+  int pad_;
+};
+struct MultiTable {
+  int n;
+  int pad_;
+  MultiDesc d[TP_REDUCE_MAX_DESCS];
+};
+
+template <int OP>
+__global__ void __launch_bounds__(kTmaThreads)
+reduce_rows_multi_kernel(const __grid_constant__ MultiTable t, int is_signed, int stages,
+                         int tile_floats) {
+  using T = RowOpTraits<OP>;
+  using acc_t = typename T::acc_t;
+  constexpr int kStreams = T::kStreams;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* ring = reinterpret_cast<float*>(smem_raw);
+  uint64_t* bars =
+      reinterpret_cast<uint64_t*>(smem_raw + (size_t)stages * kStreams * tile_floats * 4);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const long long G = gridDim.x;
+  const long long total = t.d[t.n - 1].end_tile;
+
+  // (tile, tensor) cursors; tiles only move forward, so the tensor index does too
+  struct Cursor {
+    long long tile;
+    int di;
+  };
+  auto seek = [&](Cursor& c) {
+    while (c.tile < total && c.tile >= t.d[c.di].end_tile) ++c.di;
+  };
+  auto extent = [&](const Cursor& c, long long& r0, int& rows) {
+    const MultiDesc& d = t.d[c.di];
+    const long long first = c.di ? t.d[c.di - 1].end_tile : 0;
+    r0 = (c.tile - first) * d.tile_rows;
+    const long long left = d.R - r0;
+    rows = left < d.tile_rows ? (int)left : d.tile_rows;
+  };
+
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) mbar_init(&bars[s], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  Cursor prod{(long long)blockIdx.x, 0};
+  seek(prod);
+  int prod_stage = 0;
+  auto issue = [&]() {
+    long long r0;
+    int rows;
+    extent(prod, r0, rows);
+    const MultiDesc& d = t.d[prod.di];
+    const uint32_t bytes = (uint32_t)rows * (uint32_t)d.L * 4u;
+    mbar_arrive_expect_tx(&bars[prod_stage], bytes * kStreams);
+    float* dst = ring + (size_t)prod_stage * kStreams * tile_floats;
+    bulk_g2s(dst, d.a + r0 * d.L, bytes, &bars[prod_stage]);
+    if (kStreams == 2) bulk_g2s(dst + tile_floats, d.b + r0 * d.L, bytes, &bars[prod_stage]);
+    prod.tile += G;
+    seek(prod);
+    if (++prod_stage == stages) prod_stage = 0;
+  };
+  if (tid == 0) {
+    for (int s = 0; s < stages - 1 && prod.tile < total; ++s) issue();
+  }
+
+  Cursor cons{(long long)blockIdx.x, 0};
+  seek(cons);
+  int stage = 0;
+  uint32_t phase = 0;
+  for (; cons.tile < total; cons.tile += G, seek(cons)) {
+    if (tid == 0 && prod.tile < total) issue();
+    mbar_wait(&bars[stage], phase);
+    const MultiDesc& d = t.d[cons.di];
+    long long r0;
+    int rows;
+    extent(cons, r0, rows);
+    const int lpr = d.lpr, rpw = 32 / lpr, sub = lane % lpr, slot = lane / lpr;
+    const int n = d.L >> 2;
+    const float4* sa = reinterpret_cast<const float4*>(ring + (size_t)stage * kStreams * tile_floats);
+    const float4* sb = sa + (tile_floats >> 2);
+    float* out = d.out + r0;
+    for (int rb = wid * rpw; rb < rows; rb += (kTmaThreads / 32) * rpw * 2) {
+      const int r_0 = rb + slot;
+      const int r_1 = r_0 + (kTmaThreads / 32) * rpw;
+      const bool l0 = r_0 < rows, l1 = r_1 < rows;
+      const float4* pa0 = sa + (size_t)r_0 * n;
+      const float4* pb0 = sb + (size_t)r_0 * n;
+      const float4* pa1 = sa + (size_t)r_1 * n;
+      const float4* pb1 = sb + (size_t)r_1 * n;
+      acc_t acc0 = 0, acc1 = 0;
+      for (int j = sub; j < n; j += lpr) {
+        if (l0) {
+          const float4 va = pa0[j];
+          const float4 vb = (kStreams == 2) ? pb0[j] : va;
+          add4<OP>(acc0, va, vb);
+        }
+        if (l1) {
+          const float4 va = pa1[j];
+          const float4 vb = (kStreams == 2) ? pb1[j] : va;
+          add4<OP>(acc1, va, vb);
+        }
+      }
+      acc0 = group_reduce(acc0, lpr);
+      acc1 = group_reduce(acc1, lpr);
+      if (sub == 0 && l0) out[r_0] = T::finalize(acc0, is_signed);
+      if (sub == 0 && l1) out[r_1] = T::finalize(acc1, is_signed);
+    }
+    __syncthreads();  // stage fully consumed
+    if (++stage == stages) {
+      stage = 0;
+      phase ^= 1u;
+    }
+  }
+}
+
 // ---- host-side dispatch ---------------------------------------------------------------
 
 static inline int pow2_ceil(int64_t v) {
@@ -526,9 +660,85 @@ static int launch_reduce(const float* a, const float* b, float* out, int64_t R, 
   return launch_ldg<OP>(a, b, out, R, L, is_signed, st);
 }
 
+template <int OP>
+static int launch_multi(const tp_reduce_desc* descs, int64_t n, int is_signed, cudaStream_t st) {
+  constexpr int kStreams = RowOpTraits<OP>::kStreams;
+  const Tuning& tn = tuning();
+  const int tile_floats = tn.reduce_tile_floats;
+  MultiTable t;
+  t.n = 0;
+  long long tiles = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const tp_reduce_desc& d = descs[i];
+    TP_REQUIRE(d.rows >= 0 && d.len >= 0, TP_ERR_INVALID, "tp_reduce_rows_multi: negative size");
+    if (d.rows == 0) continue;
+    TP_REQUIRE(d.out != nullptr, TP_ERR_INVALID, "tp_reduce_rows_multi: out is NULL");
+    if (d.len == 0) {
+      TP_CUDA(cudaMemsetAsync(d.out, 0, (size_t)d.rows * 4, st));
+      continue;
+    }
+    TP_REQUIRE(d.a != nullptr && (kStreams == 1 || d.b != nullptr), TP_ERR_INVALID,
+               "tp_reduce_rows_multi: input pointer is NULL");
+    TP_REQUIRE(d.len % 4 == 0 && d.len <= tile_floats && (uintptr_t)d.a % 16 == 0 &&
+                   (kStreams == 1 || (uintptr_t)d.b % 16 == 0),
+               TP_ERR_LIMIT,
+               "tp_reduce_rows_multi: tensor %lld has rows of %lld floats; rows must be a multiple "
+               "of 4 floats, at most %d, in 16-byte aligned tensors (use the single-tensor entry "
+               "points otherwise)", (long long)i, (long long)d.len, tile_floats);
+    TP_REQUIRE(d.rows < (1ll << 40), TP_ERR_LIMIT, "tp_reduce_rows_multi: too many rows");
+    MultiDesc& m = t.d[t.n++];
+    m.a = d.a;
+    m.b = d.b;
+    m.out = d.out;
+    m.R = d.rows;
+    m.L = (int)d.len;
+    m.tile_rows = (int)(tile_floats / d.len);
+    m.lpr = lanes_per_row(d.len >> 2, true);
+    tiles += (d.rows + m.tile_rows - 1) / m.tile_rows;
+    m.end_tile = tiles;
+  }
+  if (t.n == 0) return TP_OK;
+  int ctas = tn.reduce_ctas_per_sm;
+  const size_t per_stage = (size_t)kStreams * tile_floats * 4;
+  while (ctas > 1 && ((size_t)(220 * 1024) / ctas - 256) < 3 * per_stage) --ctas;
+  const size_t budget = (size_t)(220 * 1024) / ctas - 256;
+  int stages = 8;
+  if ((size_t)stages * per_stage > budget) stages = (int)(budget / per_stage);
+  TP_REQUIRE(stages >= 2, TP_ERR_INVALID, "tp_reduce_rows_multi: reduce_tile_floats leaves < 2 stages");
+  const size_t smem = (size_t)stages * per_stage + (size_t)stages * 8 + 64;
+  long long grid = (long long)sm_count() * ctas;
+  if (grid > tiles) grid = tiles;
+  auto kern = reduce_rows_multi_kernel<OP>;
+  TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)grid, kTmaThreads, smem, st>>>(t, is_signed, stages, tile_floats);
+  TP_LAUNCH_CHECK("reduce_rows_multi_kernel");
+  return TP_OK;
+}
+
 }  // namespace tp
 
 extern "C" {
+
+int tp_reduce_rows_multi(int op, const tp_reduce_desc* descs, int64_t n, int is_signed,
+                         tp_stream_t stream) {
+  TP_REQUIRE(n >= 0 && n <= TP_REDUCE_MAX_DESCS, TP_ERR_LIMIT,
+             "tp_reduce_rows_multi: at most %d tensors per launch", (int)TP_REDUCE_MAX_DESCS);
+  if (n == 0) return TP_OK;
+  TP_REQUIRE(descs != nullptr, TP_ERR_INVALID, "tp_reduce_rows_multi: descs is NULL");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (op) {
+    case TP_REDUCE_TAYLOR: return tp::launch_multi<tp::OP_TAYLOR>(descs, n, is_signed, st);
+    case TP_REDUCE_APOZ:
+      for (int64_t i = 0; i < n; ++i)
+        TP_REQUIRE(descs[i].len < (1 << 24), TP_ERR_LIMIT,
+                   "tp_reduce_rows_multi: rows must be shorter than 2^24 for exact counts");
+      return tp::launch_multi<tp::OP_APOZ>(descs, n, 0, st);
+    case TP_REDUCE_ABSSUM: return tp::launch_multi<tp::OP_ABSSUM>(descs, n, 0, st);
+    default:
+      tp::set_error("tp_reduce_rows_multi: unknown op %d", op);
+      return TP_ERR_INVALID;
+  }
+}
 
 int tp_taylor_reduce(const float* z, const float* g, int64_t B, int64_t C, int64_t HW,
                      int is_signed, float* out, tp_stream_t stream) {

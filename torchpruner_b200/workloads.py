@@ -225,6 +225,15 @@ def build(name, seed=1):
         model = MLP()
         model.eval()
         return model, (1, 28, 28)
+    if name == "resnet50_stock":
+        # torchvision's ResNet-50 as it ships: ONE ReLU module per bottleneck, fired three times
+        # per forward with different channel counts.  The reference's hook metrics are defined
+        # on 37 of its 53 convolutions and raise on every conv3; config 4's
+        # parity set is exactly that behaviour.
+        import torchvision
+
+        model = torchvision.models.resnet50(num_classes=10)
+        return warm_batchnorm(model, (3, 224, 224), n=4), (3, 224, 224)
     if name == "resnet50":
         return warm_batchnorm(ResNet50HookFriendly(), (3, 224, 224), n=8), (3, 224, 224)
     raise KeyError(name)
