@@ -169,7 +169,13 @@ def test_unprovable_links_return_none():
     m = _Residual().eval()
     trace = cascade.trace_chain(m, shape)
     assert cascade.resolve(trace, m, m.a, [1], [m.b]) is not None       # a -> relu -> b is a chain
-    assert cascade.resolve(trace, m, m.b, [1], [m.c]) is None           # the add is invisible
+    for p in m.parameters():          # no autograd graph, no way to see the add behind m.b
+        p.requires_grad_(False)
+    blind = cascade.trace_chain(m, shape)
+    assert cascade.resolve(blind, m, m.b, [1], [m.c]) is None
+    assert cascade.resolve(blind, m, m.a, [1], [m.b]) is not None
+    for p in m.parameters():
+        p.requires_grad_(True)
     for inplace in (False, True):
         m = _Hidden(inplace).eval()
         assert cascade.resolve(cascade.trace_chain(m, shape), m, m.a, [1], [m.b]) is None
@@ -289,3 +295,64 @@ def test_stale_trace_resolves_against_the_live_widths():
     # a model whose widths no longer fit together is left to the probe forward (which raises)
     fc2.weight.data = fc2.weight.data[:, :50]
     assert cascade.resolve(trace, model, fc1, [4], [fc2]) is None
+
+
+# ------------------------------------------------------------------ residual networks
+def test_residual_add_is_resolved_from_the_autograd_graph():
+    """`b(h) + h`: no module sees the add, the input of `c` is a new tensor.  Its grad_fn is an
+    AddBackward0 whose operands are the outputs of `b` and of the ReLU, which the trace recorded,
+    so a dead channel of either operand is dead in the sum."""
+    shape = (3, 8, 8)
+    m = _Residual().eval()
+    trace = cascade.trace_chain(m, shape)
+    for module, units, listeners in ((m.b, [1, 6], [m.c]), (m.a, [0, 3], [m.b, m.c]),
+                                     (m.a, [7], [m.c])):
+        assert_same(cascade.resolve(trace, m, module, units, listeners),
+                    probe(m, module, units, listeners, shape))
+
+
+def _small_resnet(block="bottleneck"):
+    import torchvision
+    torch.manual_seed(3)
+    if block == "bottleneck":
+        net = torchvision.models.resnet.ResNet(torchvision.models.resnet.Bottleneck, [2, 2, 1, 1],
+                                               num_classes=7, width_per_group=16)
+    else:
+        net = torchvision.models.resnet.ResNet(torchvision.models.resnet.BasicBlock, [2, 1, 1, 1],
+                                               num_classes=7)
+    return net.eval()
+
+
+@pytest.mark.parametrize("block", ["bottleneck", "basic"])
+def test_resnet_graph_resolves_like_the_nan_trick(block):
+    """torchvision-style ResNets (`out += identity` in place, one shared ReLU per block, a
+    functional flatten before `fc`): every entry of get_resnet_pruning_graph, and prunes INTO the
+    residual stream with listeners further down, against the probe forward."""
+    from torchpruner_b200.utils import get_resnet_pruning_graph
+    net = _small_resnet(block)
+    shape = (3, 32, 32)
+    trace = cascade.trace_chain(net, shape)
+    assert trace is not None
+    graph = get_resnet_pruning_graph(net)
+    n_blocks = sum(1 for m in net.modules() if hasattr(m, "conv1") and m is not net)
+    assert len(graph) == (2 * n_blocks + 1 if block == "bottleneck" else n_blocks)
+    rng = np.random.RandomState(5)
+    for module, listeners in graph:
+        n = module.weight.shape[0]
+        units = sorted(rng.choice(n, size=max(1, n // 4), replace=False).tolist())
+        got = cascade.resolve(trace, net, module, units, listeners)
+        want = probe(net, module, units, listeners, shape)
+        assert_same(got, want)
+        for consumer in listeners:
+            if isinstance(consumer, nn.Conv2d):
+                np.testing.assert_array_equal(want[id(consumer)][1], units)
+    # into the stream: the block's last conv, heard in this block, the next one and the head
+    blocks = [m for m in net.modules() if hasattr(m, "conv1") and m is not net]
+    last_conv = blocks[0].conv3 if block == "bottleneck" else blocks[0].conv2
+    last_bn = blocks[0].bn3 if block == "bottleneck" else blocks[0].bn2
+    listeners = [last_bn, blocks[1].conv1, blocks[1].bn1, blocks[2].conv1, net.fc]
+    listeners += [m for m in blocks[2].downsample.modules() if isinstance(m, nn.Conv2d)]
+    got = cascade.resolve(trace, net, last_conv, [2, 5], listeners)
+    assert_same(got, probe(net, last_conv, [2, 5], listeners, shape))
+    assert got[id(blocks[1].conv1)][1].tolist() == [2, 5]        # through the add and the ReLU
+    assert got[id(net.fc)][1].size == net.fc.weight.shape[1]     # behind a convolution: all dead

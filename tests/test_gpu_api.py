@@ -543,6 +543,40 @@ def test_pruning_one_layer_twice_uses_the_current_widths(mode, capsys):
     capsys.readouterr()
 
 
+@pytest.mark.parametrize("mode", ["analytic", "probe"])
+def test_resnet_blocks_prune_bit_exact(mode, capsys):
+    """Cascading prune of every entry of get_resnet_pruning_graph on a torchvision-style
+    bottleneck ResNet (in-place residual adds, shared ReLUs) against the CPU oracle: same tensors,
+    same numpy RNG consumption; after the first probe forward the analytic cascade resolves every
+    entry from the recorded graph, residual adds included."""
+    from tests.test_cascade import _small_resnet
+    from torchpruner_b200.utils import get_resnet_pruning_graph
+    cpu = _small_resnet("bottleneck")
+    gpu = copy.deepcopy(cpu).to(DEV)
+    shape = (3, 32, 32)
+    pruner, ref = Pruner(gpu, shape, DEV, cascade=mode), oracle.OraclePruner(cpu, shape)
+    g_gpu, g_cpu = get_resnet_pruning_graph(gpu), get_resnet_pruning_graph(cpu)
+    rng = np.random.RandomState(8)
+    how = []
+    for r, ((mod, casc), (cmod, ccasc)) in enumerate(zip(g_gpu, g_cpu)):
+        n = mod.weight.shape[0]
+        units = sorted(rng.choice(n, size=max(1, n // 3), replace=False).tolist())
+        np.random.seed(60 + r)
+        pruner.prune_model(mod, units, casc)
+        how.append(pruner.last_cascade)
+        a = np.random.random()
+        np.random.seed(60 + r)
+        ref.prune_model(cmod, units, ccasc)
+        assert a == np.random.random()
+    assert how == ["probe"] + [mode] * (len(g_gpu) - 1)
+    for (k, a), b in zip(gpu.state_dict().items(), cpu.state_dict().values()):
+        assert torch.equal(a.cpu(), b), k
+    x = torch.randn((2,) + shape, generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        assert torch.allclose(gpu(x.to(DEV)).cpu(), cpu(x), atol=1e-4)
+    capsys.readouterr()
+
+
 @pytest.mark.parametrize("momentum", [0.0, 0.01])
 def test_training_step_after_pruning(momentum):
     """test_pruner.py:180-228 (the momentum case raises KeyError in the reference on torch>=1.6)."""

@@ -45,43 +45,90 @@ _POOLING = (nn.MaxPool1d, nn.MaxPool2d, nn.MaxPool3d, nn.AvgPool1d, nn.AvgPool2d
 
 
 class _Call:
-    __slots__ = ("module", "inp", "in_shape", "in_version", "out", "out_shape", "out_version")
+    __slots__ = ("module", "inp", "in_shape", "in_version", "in_fn", "out", "out_shape",
+                 "out_version", "out_fn")
 
 
-def _link(a, b):
-    """How call ``b`` receives the output of call ``a``: 'same', 'flatten' or None (unproven)."""
-    if a.out is None or b.inp is None:
-        return None
-    if b.inp is a.out:
-        return "same" if b.in_version == a.out_version else None
-    base = getattr(b.inp, "_base", None)
-    if base is None or not (base is a.out or base is getattr(a.out, "_base", None)):
+def _same_storage(x, y):
+    """x is y, or a view of it (or of the tensor y is a view of)."""
+    if x is y:
+        return True
+    base = getattr(x, "_base", None)
+    return base is not None and (base is y or base is getattr(y, "_base", None))
+
+
+def _direct(a, b):
+    """How call ``b`` receives the output of call ``a`` unchanged: 'same', 'flatten' or None."""
+    if a.out is None or b.inp is None or not _same_storage(b.inp, a.out):
         return None
     if b.in_version != a.out_version:
-        return None
+        return None   # written in place in between: see _sum_of for the one case that is provable
+    if b.inp is a.out or tuple(a.out_shape) == tuple(b.in_shape):
+        return "same"
     if len(a.out_shape) > 2 and len(b.in_shape) == 2 and a.out_shape[0] == b.in_shape[0] \
             and int(np.prod(a.out_shape[1:])) == b.in_shape[1]:
         return "flatten"
-    return "same" if tuple(a.out_shape) == tuple(b.in_shape) else None
+    return None
+
+
+def _sum_of(calls, i):
+    """Indices (or -1 for the model input) of the two tensors whose elementwise SUM call ``i``
+    receives — the residual add of a ResNet block, functional (``out = out + identity``) or in
+    place (``out += identity``) — or None.  A hook cannot see the add itself; the autograd graph
+    can: the input's grad_fn is an AddBackward0 node whose two operands are the grad_fns that
+    two recorded outputs (or inputs) had when they were produced."""
+    fn = calls[i].in_fn
+    if fn is None or type(fn).__name__ != "AddBackward0" or len(fn.next_functions) != 2:
+        return None
+    found = []
+    for node, _ in fn.next_functions:
+        if node is None:
+            return None
+        src = None
+        for j in range(i - 1, -1, -1):
+            if calls[j].out_fn is node and tuple(calls[j].out_shape) == tuple(calls[i].in_shape):
+                src = j
+                break
+        if src is None:
+            return None
+        found.append(src)
+    return found
 
 
 class ChainTrace:
-    """Leaf-module calls of one forward, in order, with what links them.  Only modules, shapes
-    and link kinds are kept; the activations seen while recording are released."""
+    """Leaf-module calls of one forward, in order, and where each one's input comes from: the
+    unchanged (or flattened) output of ONE earlier call, or the sum of two.  Only modules, shapes
+    and sources are kept; the activations seen while recording are released."""
 
     def __init__(self, calls, signature):
         self.signature = signature
-        self.links = [_link(calls[i], calls[i + 1]) for i in range(len(calls) - 1)]
         self.calls = calls
+        self.sources = []
+        for i, c in enumerate(calls):
+            src = None
+            for j in range(i - 1, -1, -1):   # the latest producer wins
+                kind = _direct(calls[j], c)
+                if kind is not None:
+                    src = (kind, j)
+                    break
+                if calls[j].out is not None and c.inp is not None and _same_storage(c.inp, calls[j].out):
+                    break   # its tensor, but modified since: not a plain hand-over
+            if src is None:
+                pair = _sum_of(calls, i)
+                if pair is not None:
+                    src = ("add", pair[0], pair[1])
+            self.sources.append(src)
         for c in calls:
-            c.inp = c.out = None
+            c.inp = c.out = c.in_fn = c.out_fn = None
         self.position = {}
         for i, c in enumerate(calls):
             # a module called twice has no single position: poison it
             self.position[id(c.module)] = i if id(c.module) not in self.position else -1
 
     def link(self, i):
-        return self.links[i]
+        """Source of call i+1 if it is simply call i's output ('same' / 'flatten'), else None."""
+        src = self.sources[i + 1]
+        return src[0] if src is not None and src[0] != "add" and src[1] == i else None
 
 
 def structure_signature(model, input_size):
@@ -109,17 +156,18 @@ class Recorder:
         c.module = module
         x = inputs[0] if inputs else None
         if isinstance(x, torch.Tensor):
-            c.inp, c.in_shape, c.in_version = x, tuple(x.shape), x._version
+            c.inp, c.in_shape, c.in_version, c.in_fn = x, tuple(x.shape), x._version, x.grad_fn
         else:
-            c.inp, c.in_shape, c.in_version = None, (), -1
+            c.inp, c.in_shape, c.in_version, c.in_fn = None, (), -1, None
         self._open.setdefault(id(module), []).append(c)
 
     def _post(self, module, inputs, output):
         c = self._open[id(module)].pop()
         if isinstance(output, torch.Tensor):
             c.out, c.out_shape, c.out_version = output, tuple(output.shape), output._version
+            c.out_fn = output.grad_fn
         else:
-            c.out, c.out_shape, c.out_version = None, (), -1
+            c.out, c.out_shape, c.out_version, c.out_fn = None, (), -1, None
         self.calls.append(c)
 
     def __enter__(self):
@@ -146,7 +194,7 @@ def trace_chain(model, input_size):
         return None
     param = next(model.parameters(), None)
     device = param.device if param is not None else torch.device("cpu")
-    with Recorder(model) as rec, torch.no_grad():
+    with Recorder(model) as rec:   # grad mode on, like the probe forward: adds show in grad_fn
         model(torch.zeros((2,) + tuple(input_size), dtype=torch.float32, device=device))
     return rec.trace(input_size)
 
@@ -196,63 +244,89 @@ def resolve(trace, model, module, indices, cascading_modules):
     first = trace.calls[start]
     if len(first.out_shape) < 2 or not isinstance(module, (nn.Linear, _ConvNd)):
         return None
-    # Two widths are carried along the chain.  ``rec`` is what the trace saw when it was recorded
-    # and is only compared with the trace (is this still the chain that was proven?).  ``live`` is
-    # what the model holds NOW, read from the parameters: an earlier prune_model has sliced them
-    # since the recording (the structure signature deliberately ignores sizes), and indices,
-    # Dropout's ``original_len`` and the everything-dead range must refer to the current widths.
-    rec = first.out_shape[1]
-    live = int(module.weight.shape[0])
-    dead = normalise_indices(indices, live)
+    # Per call, what its OUTPUT carries: (recorded width, live width, dead positions).  ``rec`` is
+    # what the trace saw when it was recorded and is only compared with the trace (is this still
+    # the graph that was proven?).  ``live`` is what the model holds NOW, read from the
+    # parameters: an earlier prune_model has sliced them since the recording (the structure
+    # signature deliberately ignores sizes), and indices, Dropout's ``original_len`` and the
+    # everything-dead range must refer to the current widths.  Calls that do not depend on the
+    # poisoned module have no entry: they are clean.
+    live0 = int(module.weight.shape[0])
+    state = {start: (first.out_shape[1], live0, normalise_indices(indices, live0))}
     result = {}
+    last = max(wanted) if wanted else start
     for pos, m in wanted.items():
         if pos <= start:  # runs before the poisoned module: reached, nothing dead
             width_now = _live_width_into(trace, pos)
             if width_now is None:
                 return None
             result[id(m)] = (float(width_now), np.zeros(0, np.int64))
-    last = max(wanted) if wanted else start
-    for i in range(start, last):
-        link = trace.link(i)
-        if link is None:
+    for i in range(start + 1, last + 1):
+        src = trace.sources[i]
+        call = trace.calls[i]
+        m = call.module
+        if src is None:
+            # Unknown origin.  Harmless only if nothing poisoned can have reached it: the first
+            # call of the model (fed by the input) — anything else may hide an op on dead data.
             return None
-        nxt = trace.calls[i + 1]
-        if link == "flatten":
-            k = int(np.prod(trace.calls[i].out_shape[2:]))
-            dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
-            rec *= k
-            live *= k
-        if len(nxt.in_shape) < 2 or nxt.in_shape[1] != rec:
+        if src[0] == "add":
+            parts = [state.get(j) for j in src[1:]]
+            if all(p is None for p in parts):
+                incoming = None
+            else:
+                known = [p for p in parts if p is not None]
+                if any(p[0] != known[0][0] or p[1] != known[0][1] for p in known):
+                    return None
+                # NaN + anything = NaN: a position is dead if it is dead in either operand
+                incoming = (known[0][0], known[0][1],
+                            np.unique(np.concatenate([p[2] for p in known])))
+        else:
+            kind, j = src
+            incoming = state.get(j)
+            if incoming is not None and kind == "flatten":
+                k = int(np.prod(trace.calls[j].out_shape[2:]))
+                rec, live, dead = incoming
+                dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
+                incoming = (rec * k, live * k, dead)
+        if incoming is None:   # a branch the poisoned module does not feed
+            if i in wanted:
+                width_now = _live_width_into(trace, i)
+                if width_now is None:
+                    return None
+                result[id(m)] = (float(width_now), np.zeros(0, np.int64))
+            continue
+        rec, live, dead = incoming
+        if len(call.in_shape) < 2 or call.in_shape[1] != rec:
             return None
-        m = nxt.module
         width_now = _live_in_width(m)
         if width_now is not None and width_now != live:
             return None   # the model no longer fits together here: let the probe forward say so
-        if (i + 1) in wanted:
+        if i in wanted:
             result[id(m)] = (float(live), dead.astype(np.int64))
-        if i + 1 == last:
-            break
         # what the module hands on
         if isinstance(m, (nn.Linear, _ConvNd)):
             if isinstance(m, _ConvNd) and m.groups != 1:
+                if i == last:
+                    break
                 return None
-            if len(nxt.out_shape) < 2:
+            if len(call.out_shape) < 2:
                 return None
-            rec = nxt.out_shape[1]
-            live = int(m.weight.shape[0])
+            rec, live = call.out_shape[1], int(m.weight.shape[0])
             dead = np.arange(live, dtype=np.int64) if dead.size else dead
         elif isinstance(m, nn.Flatten):
-            if m.start_dim != 1 or m.end_dim not in (-1, len(nxt.in_shape) - 1):
+            if m.start_dim != 1 or m.end_dim not in (-1, len(call.in_shape) - 1):
                 return None
-            k = int(np.prod(nxt.in_shape[2:])) if len(nxt.in_shape) > 2 else 1
+            k = int(np.prod(call.in_shape[2:])) if len(call.in_shape) > 2 else 1
             dead = (dead[:, None] * k + np.arange(k, dtype=np.int64)[None, :]).reshape(-1)
-            rec *= k
-            live *= k
+            rec, live = rec * k, live * k
         elif isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
-            if len(nxt.out_shape) < 2 or nxt.out_shape[1] != rec:
+            if len(call.out_shape) < 2 or call.out_shape[1] != rec:
                 return None
         else:
+            if i == last:
+                break
             return None
+        state[i] = (rec, live, dead)
     return result
 
 
@@ -270,33 +344,39 @@ def _live_in_width(m):
 
 def _live_width_into(trace, pos):
     """Current dim-1 width of what call ``pos`` receives: from its own tensors when it has some,
-    else carried forward from the nearest Linear / convolution before it (or the model input,
-    which pruning never narrows).  None when a link on the way is unproven."""
+    else followed back along the recorded sources to the nearest Linear / convolution (or the
+    model input, which pruning never narrows).  None when the origin is unproven."""
     width = _live_in_width(trace.calls[pos].module)
     if width is not None:
         return width
-    j = pos - 1
-    while j >= 0 and not isinstance(trace.calls[j].module, (nn.Linear, _ConvNd)):
-        j -= 1
-    if j < 0:
-        j = 0
-        if len(trace.calls[0].in_shape) < 2:
+    src = trace.sources[pos]
+    if src is None:
+        if pos == 0 and len(trace.calls[0].in_shape) >= 2:
+            return trace.calls[0].in_shape[1]
+        return None
+    if src[0] == "add":
+        return _live_width_out(trace, src[1])
+    out = _live_width_out(trace, src[1])
+    if out is None:
+        return None
+    if src[0] == "flatten":
+        out *= int(np.prod(trace.calls[src[1]].out_shape[2:]))
+    return out
+
+
+def _live_width_out(trace, j):
+    """Current dim-1 width of call ``j``'s output."""
+    call = trace.calls[j]
+    m = call.module
+    if isinstance(m, (nn.Linear, _ConvNd)):
+        return int(m.weight.shape[0])
+    width = _live_width_into(trace, j)
+    if width is None:
+        return None
+    if isinstance(m, nn.Flatten):
+        if m.start_dim != 1 or m.end_dim not in (-1, len(call.in_shape) - 1):
             return None
-        width = trace.calls[0].in_shape[1]
-    for i in range(j, pos):
-        call = trace.calls[i]
-        m = call.module
-        if isinstance(m, (nn.Linear, _ConvNd)):
-            width = int(m.weight.shape[0])
-        elif isinstance(m, nn.Flatten):
-            if m.start_dim != 1 or m.end_dim not in (-1, len(call.in_shape) - 1):
-                return None
-            width *= int(np.prod(call.in_shape[2:])) if len(call.in_shape) > 2 else 1
-        elif not isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
-            return None
-        link = trace.link(i)
-        if link is None:
-            return None
-        if link == "flatten":
-            width *= int(np.prod(call.out_shape[2:]))
-    return width
+        return width * (int(np.prod(call.in_shape[2:])) if len(call.in_shape) > 2 else 1)
+    if isinstance(m, (_BatchNorm, _DropoutNd) + _ELEMENTWISE + _POOLING):
+        return width
+    return None

@@ -65,3 +65,36 @@ def get_vgg_pruning_graph(vgg):
             entries[-1][1].append(m)
     entries.reverse()
     return entries[1:]
+
+
+def get_resnet_pruning_graph(resnet):
+    """``[(module, [cascading modules])]`` for a torchvision-style residual network, last block
+    first.  Not in the reference, whose only graph builder is the VGG one (graph.py:37-60).
+
+    What can be pruned without touching the residual stream are the layers INSIDE a block: in a
+    bottleneck (``conv1, bn1, conv2, bn2, conv3, bn3``) the outputs of ``conv1`` feed only
+    ``bn1 -> conv2`` and those of ``conv2`` only ``bn2 -> conv3``; in a basic block
+    (``conv1, bn1, conv2, bn2``) the outputs of ``conv1`` feed ``bn1 -> conv2``.  The stem
+    convolution (``conv1, bn1`` of the model itself) is included when the first block re-projects
+    its input (``downsample``), so that its channels are read by convolutions only.  ``conv3`` /
+    ``downsample`` outputs are summed into the stream every later block of the stage reads and
+    writes: removing channels there would need the same indices in all of them and is left out.
+    Cascade lists follow the VGG builder's order: the consumer convolution(s) first, then the
+    BatchNorm."""
+    entries = []
+    blocks = [m for m in resnet.modules()
+              if all(isinstance(getattr(m, n, None), nn.Conv2d) for n in ("conv1", "conv2"))
+              and all(isinstance(getattr(m, n, None), nn.BatchNorm2d) for n in ("bn1", "bn2"))
+              and m is not resnet]
+    stem = getattr(resnet, "conv1", None)
+    if isinstance(stem, nn.Conv2d) and isinstance(getattr(resnet, "bn1", None), nn.BatchNorm2d) \
+            and blocks and getattr(blocks[0], "downsample", None) is not None:
+        first = blocks[0]
+        readers = [first.conv1] + [m for m in first.downsample.modules() if isinstance(m, nn.Conv2d)]
+        entries.append((stem, readers + [resnet.bn1]))
+    for blk in blocks:
+        entries.append((blk.conv1, [blk.conv2, blk.bn1]))
+        if isinstance(getattr(blk, "conv3", None), nn.Conv2d):
+            entries.append((blk.conv2, [blk.conv3, blk.bn2]))
+    entries.reverse()
+    return entries
