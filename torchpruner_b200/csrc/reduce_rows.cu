@@ -87,9 +87,10 @@ reduce_rows_ldg(const float* __restrict__ a, const float* __restrict__ b,
   using acc_t = typename T::acc_t;
   constexpr bool kTwo = (T::kStreams == 2);
   constexpr int RPW = 32 / LPR;
-  // loads in flight per lane: 4 x 16 B vectors, or 8 x 4 B scalars (unaligned / odd-length rows
-  // need the deeper unroll to keep enough bytes in flight)
-  constexpr int U = VEC ? 4 : 8;
+  // loads in flight per lane: 4 x 16 B vectors per stream for two streams, 8 for one stream, or
+  // 8 x 4 B scalars (unaligned / odd-length rows need the deeper unroll to keep enough bytes in
+  // flight)
+  constexpr int U = (VEC && kTwo) ? 4 : 8;   // one stream: twice the loads to have the same bytes in flight
   const int lane = threadIdx.x & 31;
   const int sub = lane % LPR;
   const int slot = lane / LPR;
@@ -537,7 +538,8 @@ template <int OP, int LPR, bool VEC, bool LOOP>
 static int launch_ldg_inst(const float* a, const float* b, float* out, int64_t R, int64_t L,
                            int is_signed, cudaStream_t st) {
   constexpr int RPW = 32 / LPR;
-  const int64_t rows_per_warp = LOOP ? RPW : RPW * (VEC ? 4 : 8);
+  const int64_t rows_per_warp =
+      LOOP ? RPW : RPW * ((VEC && RowOpTraits<OP>::kStreams == 2) ? 4 : 8);
   const int64_t warps = (R + rows_per_warp - 1) / rows_per_warp;
   int64_t blocks = (warps + 7) / 8;
   const int64_t cap = (int64_t)sm_count() * 8 * tuning().reduce_ldg_waves;  // 8 resident CTAs/SM
@@ -664,7 +666,9 @@ template <int OP>
 static int launch_multi(const tp_reduce_desc* descs, int64_t n, int is_signed, cudaStream_t st) {
   constexpr int kStreams = RowOpTraits<OP>::kStreams;
   const Tuning& tn = tuning();
-  const int tile_floats = tn.reduce_tile_floats;
+  // per-tile costs (barrier, cursor arithmetic, one thread issuing the copies) are the same for
+  // one stream as for two: single-stream ops take tiles of twice the floats, i.e. the same bytes
+  const int tile_floats = tn.reduce_tile_floats * (kStreams == 1 ? 2 : 1);
   MultiTable t;
   t.n = 0;
   long long tiles = 0;
