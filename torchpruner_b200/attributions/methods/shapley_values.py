@@ -8,7 +8,7 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
-from ..native_tail import NativeTail, cached_plan, head_plan, remember_plan
+from ..native_tail import NativeTail, cached_plan, head_plan, note_agreement, remember_plan
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -61,16 +61,14 @@ def any_rank(flag, device, group=None):
     return bool(t.item())
 
 
-def agree_on_plan(native, has_work, device, group=None):
-    """Make the execution plan of one (layer, batch) the same on every rank: one MIN all-reduce
-    of (engine usable, fp16 flavour, incremental first layer).  Ranks verify their plans on their
-    own masks, and a verification that lands a hair on either side of its tolerance must not
-    leave one rank on the library path (measured: one such rank made an 8-GPU step wait 700 ms
-    at the all-reduce).  A rank without work votes "don't care".  Returns the plan to use."""
+def plan_vote(native, has_work, device, group=None):
+    """(engine usable, fp16 flavour, incremental first layer) as the MINIMUM over the ranks — one
+    tiny all-reduce — or None outside a process group (single process, or ranks emulated in one
+    process by the tests).  A rank without work votes "don't care"."""
     import torch.distributed as dist
 
     if not (dist.is_available() and dist.is_initialized()):
-        return native   # single process (or ranks emulated in one process by the tests)
+        return None
     if has_work:
         mine = [int(native is not None), int(native is not None and native.use_f16),
                 int(native is not None and native.incremental)]
@@ -78,9 +76,14 @@ def agree_on_plan(native, has_work, device, group=None):
         mine = [1, 1, 1]
     t = torch.tensor(mine, dtype=torch.int32, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
-    usable, f16, incremental = (bool(v) for v in t.tolist())
-    if native is None:
-        return None
+    return tuple(bool(v) for v in t.tolist())
+
+
+def apply_vote(native, outcome):
+    """The plan to run given what the ranks agreed on."""
+    if native is None or outcome is None:
+        return native
+    usable, f16, incremental = outcome
     if not usable:
         native.release()
         return None
@@ -89,6 +92,15 @@ def agree_on_plan(native, has_work, device, group=None):
     if not incremental and native.incremental:
         native.release()   # drops the per-batch contributions; the first layer runs per mask
     return native
+
+
+def agree_on_plan(native, has_work, device, group=None):
+    """Make the execution plan of one (layer, batch) the same on every rank.  Ranks verify their
+    plans on their own masks, and a verification that lands a hair on either side of its
+    tolerance must not leave one rank on the library path (measured: one such rank made an 8-GPU
+    step wait 700 ms at the all-reduce), nor may the tables mix roundings.  Returns the plan to
+    use."""
+    return apply_vote(native, plan_vote(native, has_work, device, group))
 
 
 def sharded_activation(head, x, rank, world, group=None):
@@ -200,6 +212,18 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         group = self.process_group
         return group, dist.get_world_size(group), dist.get_rank(group)
 
+    def _agreed(self, kind, plan, info, has_work, world, z, module, group):
+        """(plan to run, agreed outcome or None): the ranks' agreement on this plan, by a
+        collective the first time and from the plan cache afterwards (every rank stored the same
+        outcome, so every rank takes the same branch here)."""
+        key = (world, bool(getattr(self, "_f16_banned", False)), bool(self.incremental_first))
+        outcome = ((info or {}).get("agreed") or {}).get(key)
+        if outcome is None:
+            outcome = plan_vote(plan, has_work, z.device, group)
+            if outcome is not None:
+                note_agreement(self.model, module, z, kind, key, outcome)
+        return apply_vote(plan, outcome), outcome
+
     def _stack_safe(self):
         """Evaluating several masks as one batch is only the same computation if no layer mixes
         examples of a batch or draws per-call randomness: BatchNorm/Dropout must be in eval."""
@@ -264,7 +288,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         row = 0
         n_evals = 0
         stack_safe = self._stack_safe()
-        native = head = None
+        native = head = tail_vote = None
         native_info, head_info = {}, {}
 
         with torch.no_grad():
@@ -276,7 +300,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 if self.native_tail and self.native_head and stack_safe:
                     head, head_info = head_plan(self.model, module, x)
                 if world > 1:
-                    head = agree_on_plan(head, True, x.device, group)
+                    head, _ = self._agreed("head", head, head_info, True, world, x, module, group)
                 if head is not None:
                     original_z = sharded_activation(head, x, rank, world, group)
                 else:
@@ -298,7 +322,10 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                     sv = torch.zeros((d, n), dtype=torch.float64, device=z.device)
 
                 # --- how the layers after `module` are executed for this batch
-                use_engine = bool(self.native_tail and stack_safe and spans)
+                # (in a sharded job even a rank without work keeps a plan: what the ranks agreed on
+                # is stored with it, and every rank must find — or miss — that together)
+                use_engine = bool(self.native_tail and stack_safe and sv_samples > 0 and
+                                  (spans or world > 1))
                 native, P_max, buf_hi, buf_lo = None, None, None, None
                 banned = getattr(self, "_f16_banned", False)
 
@@ -323,7 +350,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                             native.use_f16 = native.use_f16 and not banned
                             native.prepare_batch(z, allow_incremental=self.incremental_first)
                             P_max, buf_hi, buf_lo = engine_buffers()
-                            j0, k0v, _ = spans[0]
+                            j0, k0v, _ = spans[0] if spans else (0, 0, 0)
                             ok, verr = native.verify(self.model, module, z, perm_dev[j0], inv_dev[j0],
                                                      k0v, min(2, n), buf_hi, buf_lo)
                             if not ok and native.use_f16:   # out of fp16 range? TF32 flavour
@@ -339,10 +366,12 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                         remember_plan(self.model, module, z, native, native_info)
                     if native is None:
                         _warn_generic_path(self.model, module)
+                tail_vote = None
                 if world > 1:
                     # every rank must run the same flavour, or the slowest plan sets the pace of
                     # the whole job at the all-reduce (and tables would mix roundings)
-                    native = agree_on_plan(native, bool(spans), z.device, group)
+                    native, tail_vote = self._agreed("tail", native, native_info, True, world, z,
+                                                     module, group)
 
                 if native is not None:
                     # A plan verified against forward_partial for this very model state: the
@@ -422,7 +451,9 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 allreduce_scores(sv, group)
                 # a NaN from one rank's fp16 overflow is in everybody's table now; whether the
                 # run is repeated must not depend on this rank's own flavour
-                f16_somewhere = any_rank(used_f16, sv.device, group)
+                # (after an agreement every rank knows the job's flavour without asking)
+                f16_somewhere = bool(tail_vote[0] and tail_vote[1]) if tail_vote is not None \
+                    else any_rank(used_f16, sv.device, group)
             self.last_run_info = {"evaluations": n_evals, "world_size": world, "rank": rank,
                                   "stacked": stack_safe, "native_tail": native is not None,
                                   "incremental_first": incremental_used, "f16": used_f16,

@@ -141,6 +141,22 @@ def cached_plan(model, module, z, kind="tail"):
     return False, None, None
 
 
+def note_agreement(model, module, z, kind, key, outcome):
+    """Remember, with the cached plan, what the ranks of a sharded job agreed on for it (see
+    shapley_values.agree_on_plan): the next run of the same job applies it without a collective.
+    Every rank stores the same outcome, so every rank skips — or does not skip — together."""
+    entries = _PLANS.get(model, {})
+    slot = (kind, id(module), tuple(z.shape[1:]))
+    entry = entries.get(slot)
+    if entry is None:
+        return
+    info = dict(entry[2] or {})
+    agreed = dict(info.get("agreed", {}))
+    agreed[key] = tuple(bool(v) for v in outcome)
+    info["agreed"] = agreed
+    entries[slot] = (entry[0], entry[1], info)
+
+
 def forget_plans(model=None):
     """Drop every cached plan and prepared weight copy of ``model`` (of all models when None)."""
     if model is None:
