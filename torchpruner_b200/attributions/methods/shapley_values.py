@@ -8,7 +8,8 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
-from ..native_tail import NativeTail, cached_plan, head_plan, note_agreement, remember_plan
+from ..native_tail import (NativeTail, cached_plan, head_plan, model_signature, note_agreement,
+                           remember_plan)
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -297,8 +298,9 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 # engine when the layers up to it are a recognised chain (see head_plan), else
                 # through the model's forward_partial
                 head, head_info = None, {}
+                sig = model_signature(self.model) if (self.native_tail and stack_safe) else None
                 if self.native_tail and self.native_head and stack_safe:
-                    head, head_info = head_plan(self.model, module, x)
+                    head, head_info = head_plan(self.model, module, x, sig=sig)
                 if world > 1:
                     head, _ = self._agreed("head", head, head_info, True, world, x, module, group)
                 if head is not None:
@@ -337,7 +339,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                     return p_max, hi, torch.empty_like(hi)
 
                 if use_engine:
-                    found, native, info = cached_plan(self.model, module, z)
+                    found, native, info = cached_plan(self.model, module, z, sig=sig)
                     if found:
                         native_info = dict(info or {}, cached=True)
                         if native is not None:
@@ -363,7 +365,7 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                             if not ok:
                                 native.release()
                                 native = None
-                        remember_plan(self.model, module, z, native, native_info)
+                        remember_plan(self.model, module, z, native, native_info, sig=sig)
                     if native is None:
                         _warn_generic_path(self.model, module)
                 tail_vote = None

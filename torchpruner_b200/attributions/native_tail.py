@@ -102,23 +102,21 @@ def _tensor_key(*tensors):
 
 
 def _digest(tensors):
-    """Order-independent integer checksum of the bit patterns of ``tensors`` (one int64 each,
-    left on the device)."""
-    sums = []
+    """Order-independent integer checksum of the bit patterns of ``tensors`` (left on the
+    device): per dtype size, one concatenation and one integer sum — three launches for a whole
+    tail instead of one per tensor."""
+    groups = {}
     for t in tensors:
-        t = t.detach().reshape(-1)
-        if t.element_size() == 4:
-            sums.append(t.view(torch.int32).sum(dtype=torch.int64))
-        elif t.element_size() == 8:
-            sums.append(t.view(torch.int64).sum())
-        elif t.element_size() == 2:
-            sums.append(t.view(torch.int16).sum(dtype=torch.int64))
-        else:
-            sums.append(t.view(torch.uint8).sum(dtype=torch.int64))
+        groups.setdefault(t.element_size(), []).append(t.detach().reshape(-1))
+    sums = []
+    for size in sorted(groups):
+        flat = groups[size][0] if len(groups[size]) == 1 else torch.cat(groups[size])
+        view = {8: torch.int64, 4: torch.int32, 2: torch.int16}.get(size, torch.uint8)
+        sums.append(flat.view(view).sum(dtype=torch.int64))
     return torch.stack(sums) if sums else None
 
 
-def cached_plan(model, module, z, kind="tail"):
+def cached_plan(model, module, z, kind="tail", sig=None):
     """(found, plan, info) for this model state.
 
     The signature catches everything PyTorch itself can see: replaced or resized tensors
@@ -131,7 +129,7 @@ def cached_plan(model, module, z, kind="tail"):
     and the caller rebuilds and re-verifies."""
     key = (kind, id(module), tuple(z.shape[1:]))
     entry = _PLANS.get(model, {}).get(key)
-    if entry is not None and entry[0] == _signature(model):
+    if entry is not None and entry[0] == (sig if sig is not None else _signature(model)):
         plan = entry[1]
         if plan is not None and plan.watched and \
                 not torch.equal(_digest(plan.watched), plan.digest):
@@ -167,9 +165,15 @@ def forget_plans(model=None):
         _LAYERS.pop(model, None)
 
 
-def remember_plan(model, module, z, plan, info, kind="tail"):
+def remember_plan(model, module, z, plan, info, kind="tail", sig=None):
     _PLANS.setdefault(model, {})[(kind, id(module), tuple(z.shape[1:]))] = \
-        (_signature(model), plan, info)
+        (sig if sig is not None else _signature(model), plan, info)
+
+
+def model_signature(model):
+    """What ``cached_plan`` compares (pass it as ``sig`` to look several plans up at the cost of
+    one walk over the model's tensors)."""
+    return _signature(model)
 
 
 def _trace_chain(model, z, module, head=False):
@@ -727,14 +731,14 @@ class NativeTail:
         return mine_err <= max(VERIFY_RTOL / 10, lib_err), mine_err
 
 
-def head_plan(model, module, x):
+def head_plan(model, module, x, sig=None):
     """(plan or None, info): a verified plan for the layers from the model input ``x`` to the
     evaluation module ``module`` (a chain of 3x3 convolutions / BatchNorm / activations /
     MaxPool2d(2)), from the cache or built and verified now.  See ``NativeTail.activation`` for
     why the library computes the cached activation itself when it can."""
     if not (x.dim() == 4 and x.dtype == torch.float32 and x.is_cuda):
         return None, {}
-    found, plan, info = cached_plan(model, module, x, kind="head")
+    found, plan, info = cached_plan(model, module, x, kind="head", sig=sig)
     if found:
         return plan, dict(info or {}, cached=True)
     plan = NativeTail.build(model, module, x, head=True)
@@ -744,7 +748,7 @@ def head_plan(model, module, x):
         info = {"verified": ok, "verify_rel_err": err}
         if not ok:
             plan = None
-    remember_plan(model, module, x, plan, info, kind="head")
+    remember_plan(model, module, x, plan, info, kind="head", sig=sig)
     return plan, info
 
 
