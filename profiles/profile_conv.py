@@ -77,6 +77,13 @@ def main():
         for shp in (LAYERS[0], LAYERS[6]):
             run(*shp, (images_for_f16 if F16 else images_for)(*shp[:3]), iters=1)
         return
+    if "ncu_pair" in sys.argv:   # two shapes, single-CTA tiles then CTA pairs (wrap in ncu)
+        for shp in ((4, 4, 256, 512, 9), (4, 4, 512, 512, 9)):
+            for knob in (1, 2):
+                _lib.set_tuning("conv_pair", knob)
+                run(*shp, images_for_f16(*shp[:3]), iters=1)
+        _lib.set_tuning("conv_pair", 0)
+        return
     if "pair" in sys.argv:   # A/B: single-CTA tiles (conv_pair=1) against CTA pairs (0)
         print("pair  H  W  Cin Cout taps      N     ms  executed_TF/s (3 MMAs per product, skipped taps not counted)")
         for single in (1, 0):
