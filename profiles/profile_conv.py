@@ -17,6 +17,9 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from torchpruner_b200 import _lib  # noqa: E402
 
+if os.environ.get("TP_LIB"):   # an alternative build of the library (A/B experiments)
+    _lib.LIB_PATH = os.path.abspath(os.environ["TP_LIB"])
+
 DEV = torch.device("cuda:0")
 # (H, W, Cin, Cout, taps): the 12 conv layers after features.0 and the three linear layers
 LAYERS = [(32, 32, 64, 64, 9), (16, 16, 64, 128, 9), (16, 16, 128, 128, 9), (8, 8, 128, 256, 9),
@@ -76,6 +79,17 @@ def main():
     if "ncu" in sys.argv:
         for shp in (LAYERS[0], LAYERS[6]):
             run(*shp, (images_for_f16 if F16 else images_for)(*shp[:3]), iters=1)
+        return
+    if "quick" in sys.argv:   # default tuning, every layer once (A/B of two builds: TP_LIB=path)
+        tot_ms = tot_fl = 0.0
+        for (H, W, Cin, Cout, taps) in LAYERS:
+            N = (images_for_f16 if F16 else images_for)(H, W, Cin)
+            ms, _ = run(H, W, Cin, Cout, taps, N, iters=7)
+            fl = 3.0 * _lib.load().tp_conv_tf32x3_flops(N, H, W, Cin, Cout, taps)
+            tot_ms += ms
+            tot_fl += fl
+            print(f"{H:2d} {W:2d} {Cin:4d} {Cout:4d} {taps:4d} {N:6d} {ms:7.3f} {fl / ms / 1e9:10.1f}")
+        print(f"# {os.environ.get('TP_LIB', 'default build')}: weighted {tot_fl / tot_ms / 1e9:.1f} executed TF/s")
         return
     if "ncu_pair" in sys.argv:   # two shapes, single-CTA tiles then CTA pairs (wrap in ncu)
         for shp in ((4, 4, 256, 512, 9), (4, 4, 512, 512, 9)):

@@ -294,7 +294,9 @@ def reduce_rows_multi(op, tensors, signed=False):
             b = _cuda_f32(b, "tensor")
             if b.shape != a.shape:
                 raise TorchPrunerB200Error("activation and gradient shapes differ")
-        ok = hw % 4 == 0 and 0 < hw <= tile and a.data_ptr() % 16 == 0 and \
+        # (rows longer than 1024 floats leave most warps of a CTA without a row in a 16 KB tile and
+        # are large enough to run at speed on their own: profiles/r02_tune_multi_single.txt)
+        ok = hw % 4 == 0 and 0 < hw <= min(tile, 1024) and a.data_ptr() % 16 == 0 and \
             (b is None or b.data_ptr() % 16 == 0) and B * C > 0
         if not ok:
             outs[i] = taylor_reduce(b, a, signed) if op == "taylor" else \

@@ -111,10 +111,34 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // process: after 2^26 failed polls (seconds) the kernel traps instead, the launch fails with a
 // sticky CUDA error and the next entry point returns TP_ERR_CUDA.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+#ifdef TP_MBAR_UNBOUNDED   // A/B builds only (profiles/): the round-1 wait, which spins forever
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+  return;
+#endif
   if (mbar_try_wait(bar, parity)) return;
   uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++polls == (1u << 26)) __trap();
+  }
+}
+
+// Unbounded form for waiters that hold many live registers (the conv epilogue warps keep a
+// 128-float accumulator row each): the poll counter of the bounded form costs them a spill.  It
+// may only wait for an event that a BOUNDED waiter is also (transitively) waiting for — the
+// epilogue waits for MMAs whose issuer waits, bounded, for TMA data — so a dead pipeline still
+// ends in a trap.
+__device__ __forceinline__ void mbar_wait_unbounded(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
   }
 }
 

@@ -460,7 +460,7 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
     const int n_chunks = (g.num_kb + g.promote - 1) / g.promote;
     for (int chunk = 0; chunk < n_chunks; ++chunk) {
       const int buf = chunk & 1;
-      mbar_wait(&acc_full[buf], (uint32_t)((chunk >> 1) & 1));
+      mbar_wait_unbounded(&acc_full[buf], (uint32_t)((chunk >> 1) & 1));
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
 #pragma unroll
@@ -841,7 +841,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
 #pragma unroll
         for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
         for (int chunk = 0; chunk < chunks_this_tile; ++chunk) {
-          mbar_wait(&acc_full[buf], acc_phase);
+          mbar_wait_unbounded(&acc_full[buf], acc_phase);
           tc_fence_after();
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
 #pragma unroll
