@@ -353,7 +353,7 @@ def test_shapley_schedules_agree():
 
     base, m = run()
     assert m.last_run_info["evaluations"] == 2 * 3 * 64
-    for attrs in ({"max_stack": 1}, {"max_stack": 7}, {"max_stack_bytes": 1}):
+    for attrs in ({"max_stack": 1}, {"max_stack": 7}, {"max_stack_bytes": 1, "max_stack_bytes_engine": 1}):
         other, _ = run(**attrs)
         assert np.abs(other - base).max() <= 2e-6
 

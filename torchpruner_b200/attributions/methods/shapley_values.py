@@ -178,7 +178,14 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
         self.mask_indices = []
         self.process_group = None
         self.shard = os.environ.get("TORCHPRUNER_B200_SHARD", "0") == "1"
+        # Bytes of stacked masked activations per launch.  On the engine 2 GiB (measured 3 % faster
+        # than 512 MiB on the VGG16 job: fewer, larger launches; the kernels index with 64 bits).
+        # Through the model's own forward_partial 512 MiB: tensors of 2^31 bytes and more push
+        # cuDNN onto a 25x slower direct kernel (profiles/r01_launches_bench_core_v1.csv).
         self.max_stack_bytes = int(os.environ.get("TORCHPRUNER_B200_STACK_MB", "512")) << 20
+        self.max_stack_bytes_engine = int(os.environ.get(
+            "TORCHPRUNER_B200_ENGINE_STACK_MB",
+            os.environ.get("TORCHPRUNER_B200_STACK_MB", "2048"))) << 20
         self.max_stack = int(os.environ.get("TORCHPRUNER_B200_MAX_STACK", "512"))
         # "auto": run recognised conv/BN/ReLU/pool/linear tails on the tcgen05 3xTF32 engine after
         # checking it against forward_partial; False: always call forward_partial.
@@ -333,7 +340,8 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
 
                 def engine_buffers():
                     per_copy = (4 if native.use_f16 else 8) * native.stack_elems(B, 1)  # hi + lo
-                    p_max = int(max(1, min(self.max_stack, n, self.max_stack_bytes // per_copy)))
+                    p_max = int(max(1, min(self.max_stack, n,
+                                           self.max_stack_bytes_engine // per_copy)))
                     hi = torch.empty(native.stack_elems(B, max(p_max, min(2, n))),
                                      dtype=native.stack_dtype, device=z.device)
                     return p_max, hi, torch.empty_like(hi)
