@@ -92,6 +92,18 @@ __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* map) {
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// One lane of a fully active warp (always the same one for the same mask).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -547,6 +559,16 @@ struct ConvCfgP {
   static constexpr int kStages = (kStageBytes > 48 * 1024) ? 3 : 4;
   static constexpr int kNumAcc = 4;
   static constexpr int kTmemCols = kNumAcc * BLOCK_N;  // 512 / 256
+  // Epilogue teams: with 128 output columns, two groups of four warps take 64 columns each.  One
+  // team could not keep up: per tile it drains the TMEM partial sums (4 tcgen05.ld per warp and
+  // chunk), adds them up, and at the end scales / activates / splits / stages / stores all 128
+  // columns, ~90 % of the tile's MMA time — the MMA issuer was seen waiting for a free
+  // accumulator 4.7 polls per chunk while it never waited for operands (profiles/
+  // r02_ncu_conv_pair_summary.txt), and a stripped kernel issues the same MMAs at 100 % of the
+  // pipe (profiles/micro/mma_pace.cu).
+  static constexpr int kTeams = BLOCK_N >= 128 ? 2 : 1;
+  static constexpr int kTeamCols = BLOCK_N / kTeams;
+  static constexpr int kThreads = 64 + 128 * kTeams;
   static constexpr int kStoreBytes = kBlockM * 32 * 4;  // one [128 rows][32 cols] staging tile
   static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kStoreBytes + 1024 /*align*/ +
                                     512 /*barriers*/ + 2 * BLOCK_N * 4;
@@ -597,7 +619,14 @@ __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// named barriers of the epilogue: 1 + team for the 128 threads of one team, 3 for all teams
+__device__ __forceinline__ void epi_barrier(int team) {
+  asm volatile("bar.sync %0, 128;" ::"r"(1 + team) : "memory");
+}
+template <int THREADS>
+__device__ __forceinline__ void epi_barrier_all() {
+  asm volatile("bar.sync 3, %0;" ::"n"(THREADS) : "memory");
+}
 
 // Tile -> pixel box origin of CTA `rank` of a pair: the two CTAs take the SAME position (so they
 // walk the same taps) in two adjacent image blocks.  An odd image-block count leaves the last
@@ -614,7 +643,7 @@ __device__ __forceinline__ void tile_origin_pair(const ConvGeom& g, int mp, int 
 }
 
 template <int BLOCK_N, bool F16, bool PAIR>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(ConvCfgP<BLOCK_N, PAIR>::kThreads, 1)
 conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                        const __grid_constant__ CUtensorMap tm_a_lo,
                        const __grid_constant__ CUtensorMap tm_b_hi,
@@ -660,7 +689,8 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     }
     for (int b = 0; b < Cfg::kNumAcc; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], PAIR ? 8 : 4);   // pair: the epilogue warps of both CTAs
+      // one arrival per epilogue warp (pair: of both CTAs)
+      mbar_init(&acc_empty[b], (PAIR ? 8 : 4) * Cfg::kTeams);
     }
     fence_mbar_init();
   } else if (warp == 1) {
@@ -737,7 +767,14 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {  // ===== MMA issuer (the leader CTA of a pair) =====
+    // ===== MMA issuer (the leader CTA of a pair) =====
+    // The whole warp walks the loop and ONE elected lane issues.  With the loop under
+    // `if (lane == 0)` every descriptor and address is a per-thread value that has to be moved
+    // to the uniform registers tcgen05.mma reads, one guarded move at a time: 250 instructions
+    // per k-block, longer than the 12 MMAs they issue take on the pipe (768 clocks) — the pipe
+    // idled 39 % of the time with operands always ready.  Converged, the same arithmetic stays
+    // on the uniform datapath.
+    if (rank == 0) {
       constexpr uint32_t idesc = make_idesc<BLOCK_N, F16, PAIR>();
       int stage = 0;
       uint32_t phase = 0;
@@ -768,34 +805,36 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
             const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
             const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+            const bool chunk_done = (in_chunk + 1 == g.promote) || (kb == nk - 1);
+            if (elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < kBlockK / 8; ++kk) {
-              const uint64_t off = (uint64_t)(kk * 32 >> 4);
+              for (int kk = 0; kk < kBlockK / 8; ++kk) {
+                const uint64_t off = (uint64_t)(kk * 32 >> 4);
+                if (PAIR) {
+                  umma_pair<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+                  umma_pair<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+                  umma_pair<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+                } else {
+                  umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
+                  umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
+                  umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+                }
+              }
               if (PAIR) {
-                umma_pair<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-                umma_pair<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-                umma_pair<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+                umma_commit_pair(&empty[stage]);   // frees the stage in both CTAs
+                if (chunk_done) umma_commit_pair(&acc_full[buf]);   // wakes both CTAs' epilogues
               } else {
-                umma_x<F16>(tmem_d, a_lo + off, b_hi + off, idesc, (in_chunk | kk) != 0);
-                umma_x<F16>(tmem_d, a_hi + off, b_lo + off, idesc, 1u);
-                umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
+                umma_commit(&empty[stage]);
+                if (chunk_done) umma_commit(&acc_full[buf]);
               }
             }
-            if (PAIR) {
-              umma_commit_pair(&empty[stage]);   // frees the stage in both CTAs
-            } else {
-              umma_commit(&empty[stage]);
-            }
+            __syncwarp();
             if (++stage == Cfg::kStages) {
               stage = 0;
               phase ^= 1u;
             }
-            if (++in_chunk == g.promote || kb == nk - 1) {
-              if (PAIR) {
-                umma_commit_pair(&acc_full[buf]);   // wakes the epilogue warps of both CTAs
-              } else {
-                umma_commit(&acc_full[buf]);
-              }
+            ++in_chunk;
+            if (chunk_done) {
               in_chunk = 0;
               if (++buf == num_acc) {
                 buf = 0;
@@ -808,11 +847,16 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
     }
     __syncwarp();
   } else {
-    // ===== epilogue warps =====
-    const int et = threadIdx.x - 64;  // 0..127
-    const int q = warp & 3;
+    // ===== epilogue warps: kTeams groups of four, each owning kTeamCols output columns =====
+    constexpr int kTeams = Cfg::kTeams, kCols = Cfg::kTeamCols;
+    const int et = threadIdx.x - 64;  // 0 .. 128 * kTeams - 1
+    const int team = et >> 7;
+    const int cb = team * kCols;      // first column of this team inside the tile
+    const int q = warp & 3;           // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;    // row of the tile == TMEM lane
-    const bool issuer = (et == 0);
+    const bool issuer = ((et & 127) == 0);
+    // staging tiles: two teams have one each, a single team double-buffers
+    constexpr int kWaitRead = kTeams == 2 ? 0 : 1;
     int buf = 0;
     uint32_t acc_phase = 0;
     uint32_t stores = 0;
@@ -831,21 +875,23 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
         const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
         // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
         if (sub == 0) {
-          for (int j = et; j < BLOCK_N; j += 128) {
+          epi_barrier_all<128 * kTeams>();
+          for (int j = et; j < BLOCK_N; j += 128 * kTeams) {
             const int col = nt * BLOCK_N + j;
             s_scale[j] = col < g.Cout ? scale[col] : 0.f;
             s_shift[j] = col < g.Cout ? shift[col] : 0.f;
           }
         }
-        float acc[BLOCK_N];
+        float acc[kCols];
 #pragma unroll
-        for (int j = 0; j < BLOCK_N; ++j) acc[j] = 0.f;
+        for (int j = 0; j < kCols; ++j) acc[j] = 0.f;
         for (int chunk = 0; chunk < chunks_this_tile; ++chunk) {
           mbar_wait_unbounded(&acc_full[buf], acc_phase);
           tc_fence_after();
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N);
+          const uint32_t taddr =
+              tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLOCK_N + cb);
 #pragma unroll
-          for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+          for (int c0 = 0; c0 < kCols; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(taddr + c0, v);
 #pragma unroll
@@ -865,22 +911,22 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
             acc_phase ^= 1u;
           }
         }
-        epi_barrier();  // scale/shift of this tile visible to all epilogue threads
+        epi_barrier_all<128 * kTeams>();  // scale/shift of this tile visible to all epilogue threads
         if (F16 && g.split) {
           // fp16 split outputs: staging rows are 64 halves (128 bytes), so 64 columns per store
 #pragma unroll
-          for (int c0 = 0; c0 < BLOCK_N; c0 += 64) {
+          for (int c0 = 0; c0 < kCols; c0 += 64) {
             float y[64];
 #pragma unroll
             for (int j = 0; j < 64; ++j) {
-              float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+              float t = fmaf(acc[c0 + j], s_scale[cb + c0 + j], s_shift[cb + c0 + j]);
               y[j] = apply_act(t, g.relu, g.slope) * g.out_scale;
             }
             if (g.pool) {
               // running maximum of the 2x2 window in the TMEM columns behind the accumulators
               // (this thread's lane, so no other thread ever touches it)
-              const uint32_t paddr =
-                  tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(num_acc * BLOCK_N + c0);
+              const uint32_t paddr = tmem_base + ((uint32_t)(q * 32) << 16) +
+                                     (uint32_t)(num_acc * BLOCK_N + cb + c0);
               if (sub > 0) {
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -898,9 +944,9 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
               }
             }
             for (int pass = 0; pass < 2; ++pass) {
-              uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
-              if (issuer) bulk_wait_read<1>();
-              epi_barrier();
+              uint8_t* sbuf = store_buf + (kTeams == 2 ? (uint32_t)team : (stores & 1u)) * Cfg::kStoreBytes;
+              if (issuer) bulk_wait_read<kWaitRead>();
+              epi_barrier(team);
               uint8_t* rowp = sbuf + row * 128;
 #pragma unroll
               for (int c = 0; c < 8; ++c) {
@@ -919,9 +965,9 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                     make_uint4(w[0], w[1], w[2], w[3]);
               }
               fence_proxy_async();
-              epi_barrier();
+              epi_barrier(team);
               if (issuer) {
-                tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0,
+                tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + cb + c0,
                              g.pool ? wb : w0, g.pool ? hb : h0, n0);
                 bulk_commit();
               }
@@ -932,19 +978,19 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
         }
         const int passes = g.split ? 2 : 1;
 #pragma unroll
-        for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        for (int c0 = 0; c0 < kCols; c0 += 32) {
           float y[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            float t = fmaf(acc[c0 + j], s_scale[c0 + j], s_shift[c0 + j]);
+            float t = fmaf(acc[c0 + j], s_scale[cb + c0 + j], s_shift[cb + c0 + j]);
             t = apply_act(t, g.relu, g.slope);
             y[j] = t;
           }
           for (int pass = 0; pass < passes; ++pass) {
-            uint8_t* sbuf = store_buf + (stores & 1u) * Cfg::kStoreBytes;
-            // the TMA store that used this staging tile two stores ago must have read it out
-            if (issuer) bulk_wait_read<1>();
-            epi_barrier();
+            uint8_t* sbuf = store_buf + (kTeams == 2 ? (uint32_t)team : (stores & 1u)) * Cfg::kStoreBytes;
+            // the TMA store that used this staging tile before must have read it out
+            if (issuer) bulk_wait_read<kWaitRead>();
+            epi_barrier(team);
             uint8_t* rowp = sbuf + row * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
@@ -964,9 +1010,9 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
               *reinterpret_cast<float4*>(rowp + ((c ^ (row & 7)) << 4)) = o;  // 128B swizzle
             }
             fence_proxy_async();
-            epi_barrier();
+            epi_barrier(team);
             if (issuer) {
-              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + c0, w0, h0, n0);
+              tma_store_4d(pass == 0 ? &tm_y_hi : &tm_y_lo, sbuf, nt * BLOCK_N + cb + c0, w0, h0, n0);
               bulk_commit();
             }
             ++stores;
@@ -1188,7 +1234,7 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   if (grid > cap) grid = cap;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(kConvThreads);
+  cfg.blockDim = dim3(Cfg::kThreads);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -1297,13 +1343,12 @@ static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H
   if (Cout <= 16)
     return launch_conv<16, F16>(a_hi, a_lo, w_hi, w_lo, g, scale, shift, yf_hi, yf_lo, st);
   if (persistent) {
-    // CTA pairs (256-row tiles, half of B per SM) where they were measured faster than single-CTA
-    // tiles (profiles/r02_conv_pair_ab.txt): long reductions — K >= 4608, the 512-channel 3x3
-    // layers (+5..7 %) — and wide linear layers (+10 %).  With a short K loop the extra
-    // cross-SM hand-shakes per tile cost more than the saved operand traffic (-20 % at K = 576).
-    // conv_pair = 2 forces pairs wherever they are possible (tests).
-    const long long K = (long long)taps * Cin;
-    const bool pair_wins = K >= 4608 || (taps == 1 && K >= 512 && Cout >= 128);
+    // CTA pairs (256-row tiles, half of B per SM) wherever two image blocks exist.  With the MMA
+    // issue loop on the uniform datapath the single-CTA kernel is bound by what the M128xN128
+    // MMA reads from shared memory (1 090-1 170 TFLOP/s executed); pairs read a quarter less and
+    // reach 1 290-1 510 on every 128-wide layer (profiles/r02_conv_pair_ab.txt).  64-wide tiles
+    // gain nothing (719 vs 739) and stay single.  conv_pair: 1 = never, 2 = wherever possible.
+    const bool pair_wins = Cout > 64;
     const bool pair = tuning().conv_pair != 1 && (N + g.bn - 1) / g.bn >= 2 &&
                       (pair_wins || tuning().conv_pair == 2);
     if (Cout <= 64) {
