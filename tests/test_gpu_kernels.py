@@ -67,9 +67,10 @@ def test_several_tensors_in_one_launch_match_the_oracle():
     tay = _lib.reduce_rows_multi("taylor", list(zip(zd, gd)), signed=True)
     launches = {k: v[0] for k, v in prof.records.items()}
     _lib.profile_end()
-    # 10 tensors in ONE launch; 49-float rows, 8192-float rows, [3, 2048] viewed as rows of one
-    # element and the empty tensor go through the single-tensor entry point
-    assert launches == {"reduce_rows_multi[taylor]": 1, "taylor_reduce": 4}, launches
+    # 9 tensors in ONE launch; 49-float rows, 4096- and 8192-float rows (longer than the 1024 the
+    # wrapper batches), [3, 2048] viewed as rows of one element and the empty tensor go through
+    # the single-tensor entry point
+    assert launches == {"reduce_rows_multi[taylor]": 1, "taylor_reduce": 5}, launches
     apoz = _lib.reduce_rows_multi("apoz", zd)
     sens = _lib.reduce_rows_multi("abs_sum", gd)
     unsigned = _lib.reduce_rows_multi("taylor", list(zip(zd, gd)))
