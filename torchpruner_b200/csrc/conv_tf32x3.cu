@@ -419,25 +419,28 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer =====
-      constexpr uint32_t idesc = make_idesc<BLOCK_N, F16>();
-      int stage = 0;
-      uint32_t phase = 0;
-      int chunk = 0, in_chunk = 0;
-      for (int kb = 0; kb < g.num_kb; ++kb) {
-        const int buf = chunk & 1;
-        if (in_chunk == 0) {  // this TMEM buffer must have been drained (2 chunks ago)
-          mbar_wait(&acc_empty[buf], (uint32_t)(((chunk >> 1) & 1) ^ 1));
-          tc_fence_after();
-        }
-        mbar_wait(&full[stage], phase);
+    // ===== MMA issuer: the warp walks the loop, one elected lane issues (see the persistent
+    // kernel: under `if (lane == 0)` the loop was 250 instructions per k-block) =====
+    constexpr uint32_t idesc = make_idesc<BLOCK_N, F16>();
+    int stage = 0;
+    uint32_t phase = 0;
+    int chunk = 0, in_chunk = 0;
+    for (int kb = 0; kb < g.num_kb; ++kb) {
+      const int buf = chunk & 1;
+      if (in_chunk == 0) {  // this TMEM buffer must have been drained (2 chunks ago)
+        mbar_wait(&acc_empty[buf], (uint32_t)(((chunk >> 1) & 1) ^ 1));
         tc_fence_after();
-        uint8_t* st = smem + stage * Cfg::kStageBytes;
-        const uint64_t a_hi = umma_desc_sw128(st);
-        const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
-        const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
-        const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
-        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+      }
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      uint8_t* st = smem + stage * Cfg::kStageBytes;
+      const uint64_t a_hi = umma_desc_sw128(st);
+      const uint64_t a_lo = umma_desc_sw128(st + Cfg::kABytes);
+      const uint64_t b_hi = umma_desc_sw128(st + 2 * Cfg::kABytes);
+      const uint64_t b_lo = umma_desc_sw128(st + 2 * Cfg::kABytes + Cfg::kBBytes);
+      const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BLOCK_N);
+      const bool chunk_done = (in_chunk + 1 == g.promote) || (kb == g.num_kb - 1);
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < kBlockK / 8; ++kk) {
           const uint64_t off = (uint64_t)(kk * 32 >> 4);  // 8 tf32 = 32 bytes inside the swizzle row
@@ -447,18 +450,19 @@ conv_tf32x3_kernel(const __grid_constant__ CUtensorMap tm_a_hi,
           umma_x<F16>(tmem_d, a_hi + off, b_hi + off, idesc, 1u);
         }
         umma_commit(&empty[stage]);  // stage reusable once these MMAs have read it
-        if (++stage == Cfg::kStages) {
-          stage = 0;
-          phase ^= 1u;
-        }
-        if (++in_chunk == g.promote || kb == g.num_kb - 1) {
-          umma_commit(&acc_full[buf]);  // partial sum of this chunk complete
-          in_chunk = 0;
-          ++chunk;
-        }
+        if (chunk_done) umma_commit(&acc_full[buf]);  // partial sum of this chunk complete
+      }
+      __syncwarp();
+      if (++stage == Cfg::kStages) {
+        stage = 0;
+        phase ^= 1u;
+      }
+      ++in_chunk;
+      if (chunk_done) {
+        in_chunk = 0;
+        ++chunk;
       }
     }
-    __syncwarp();
   } else {
     // ===== epilogue: fold partial sums (TMEM -> registers), then affine / ReLU / split =====
     const int q = warp & 3;  // TMEM lane quarter this warp may access
