@@ -106,13 +106,18 @@ class _FakePlan:
     def __init__(self, use_f16=True, incremental=True, head_out=None):
         self.use_f16, self.incremental, self.head_out = use_f16, incremental, head_out
         self.released = 0
+        self.exact = [{"pool_before": False, "cout": 1}, {"pool_before": False, "cout": 1}]
 
     def release(self):
         self.released += 1
         self.incremental = False
 
-    def activation(self, x):
-        return x[:, :1] * 2.0 + x[:, 1:2]
+    def run_steps(self, z, start, stop=2):   # step 0: 2 * ch0 + ch1; step 1: + 1
+        outs = []
+        for i in range(start, stop):
+            z = z[:, :1] * 2.0 + z[:, 1:2] if i == 0 else z + 1.0
+            outs.append(z)
+        return outs
 
 
 def _plan_worker(rank, world, port, out_dir):
@@ -121,7 +126,7 @@ def _plan_worker(rank, world, port, out_dir):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from torchpruner_b200.attributions.methods.shapley_values import (agree_on_plan,
-                                                                          sharded_activation)
+                                                                          sharded_steps)
 
         lines = []
         # rank 1 lost its plan (verification a hair over the tolerance): both take the library path
@@ -138,8 +143,12 @@ def _plan_worker(rank, world, port, out_dir):
         lines.append(repr(got is mine))
         # the batch's activation: each rank computes ceil(5 / 2) rows, one all-gather
         x = torch.arange(5 * 2 * 3 * 3, dtype=torch.float32).view(5, 2, 3, 3)
-        z = sharded_activation(_FakePlan(head_out=(1, 3, 3)), x, rank, world)
-        lines.append(repr(bool(torch.equal(z, x[:, :1] * 2.0 + x[:, 1:2])) and tuple(z.shape)))
+        outs = sharded_steps(_FakePlan(head_out=(1, 3, 3)), x, 0, rank, world)
+        want = x[:, :1] * 2.0 + x[:, 1:2]
+        ok = len(outs) == 2 and torch.equal(outs[0], want) and torch.equal(outs[1], want + 1.0)
+        later = sharded_steps(_FakePlan(head_out=(1, 3, 3)), outs[0], 1, rank, world)
+        ok = ok and len(later) == 1 and torch.equal(later[0], want + 1.0)
+        lines.append(repr(bool(ok) and tuple(outs[1].shape)))
         with open(os.path.join(out_dir, f"plan{rank}.txt"), "w") as f:
             f.write("\n".join(lines))
     finally:

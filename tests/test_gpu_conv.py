@@ -930,3 +930,55 @@ def test_conv_cta_pairs_give_the_same_bits_as_single_cta_tiles(N, H, W, Cin, Cou
     if pool:
         want = F.max_pool2d(want.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
     assert float((y.double() - want).abs().max()) <= 2e-6 * max(1.0, float(want.abs().max()))
+
+
+def test_activation_cache_gives_the_same_bits():
+    """Scoring layer after layer on the same batch continues the head from the cached activation
+    of the previous layer (one block instead of the whole prefix).  The tables must be the bits a
+    cold cache gives; another batch, another model state or a write through .data must not be
+    served from it."""
+    from torchpruner_b200 import workloads
+    from torchpruner_b200.attributions import ShapleyAttributionMetric, native_tail
+
+    saved = torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        model, shape = workloads.build("vgg16_cifar")
+        model.to(DEV)
+        loaders = [workloads.synthetic_batches(shape, n=16, batch_size=16, seed=s) for s in (5, 6)]
+        layers = [model.features[i] for i in (20, 24, 27, 30)]
+
+        def run(layer, loader):
+            np.random.seed(3)
+            m = ShapleyAttributionMetric(model, loader, workloads.cross_entropy, DEV, sv_samples=1,
+                                         reduction="none")
+            with contextlib.redirect_stdout(io.StringIO()):
+                sv = m.run(layer, find_best_evaluation_module=True)
+            assert m.last_run_info["native_head"]
+            return sv
+
+        warm = {}
+        for layer in layers:          # plans get built; activations accumulate in the cache
+            for li, loader in enumerate(loaders):
+                warm[(id(layer), li)] = run(layer, loader)
+        entries = native_tail._ACTS[model]
+        assert len(entries) == 2 and all(len(e[2]) == 10 for e in entries.values())   # 10 blocks
+        launches = []
+        for layer in layers[1:]:      # a cached prefix: at most one block is computed per run
+            prof = _lib.profile_begin(timed=False)
+            again = run(layer, loaders[1])
+            launches.append(prof.records.get("contrib_sum_direct", [0])[0])
+            _lib.profile_end()
+            assert np.array_equal(again, warm[(id(layer), 1)])
+        assert launches == [0, 0, 0], launches
+        for layer in layers:          # cold cache: the same bits
+            native_tail._ACTS.pop(model, None)
+            assert np.array_equal(run(layer, loaders[0]), warm[(id(layer), 0)])
+        # a write through .data: the plan's checksum notices, plans AND activations are dropped
+        model.features[17].weight.data.mul_(1.5)
+        changed = run(layers[1], loaders[0])
+        assert np.abs(changed - warm[(id(layers[1]), 0)]).max() > 1e-3
+        native_tail._ACTS.pop(model, None)
+        assert np.array_equal(run(layers[1], loaders[0]), changed)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved

@@ -15,7 +15,8 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
-from .attributions.native_tail import NativeTail, cached_plan, head_plan, remember_plan
+from .attributions.native_tail import (NativeTail, cached_activation, cached_plan, head_plan,
+                                       model_signature, remember_plan)
 from .utils import find_best_module_for_attributions
 
 
@@ -37,8 +38,8 @@ def ablation_curve(model, x, y, module, ranking, criterion=None, find_best_evalu
             m, (torch.nn.modules.batchnorm._BatchNorm, torch.nn.modules.dropout._DropoutNd))
             for m in model.modules())
         head = head_plan(model, module_nl, x)[0] if (native_tail and stack_safe) else None
-        if head is not None:   # the activation itself on the fp32-accurate engine (head_plan)
-            z = head.activation(x)
+        if head is not None:   # the activation itself, exactly (head_plan), cached per batch
+            z = cached_activation(model, model_signature(model), head, x, head.run_steps)
         else:
             z = model.forward_partial(x, to_module=module_nl).detach().float().contiguous()
         B, C = z.shape[0], z.shape[1]

@@ -8,8 +8,8 @@ from torch.nn.modules.batchnorm import _BatchNorm
 from torch.nn.modules.dropout import _DropoutNd
 
 from .. import attributions as _base
-from ..native_tail import (NativeTail, cached_plan, head_plan, model_signature, note_agreement,
-                           remember_plan)
+from ..native_tail import (NativeTail, cached_activation, cached_plan, head_plan, model_signature,
+                           note_agreement, remember_plan)
 from ... import _lib
 
 _ZERO_BITS = 0x00000000
@@ -104,27 +104,37 @@ def agree_on_plan(native, has_work, device, group=None):
     return apply_vote(native, plan_vote(native, has_work, device, group))
 
 
-def sharded_activation(head, x, rank, world, group=None):
-    """The cached activation of the batch ``x``, each rank computing the rows of
-    ``ceil(B / world)`` examples and one all-gather putting the batch together.  Per-example
-    arithmetic does not depend on which rank (or which slice) an example is in, so every rank ends
-    up with the bits a single GPU computes.  Without this the once-per-batch forward to the
-    evaluation module is replicated on every rank and does not shrink as GPUs are added (the
-    serial fraction of the strong-scaling job)."""
+def sharded_steps(head, z, start, rank, world, group=None):
+    """Outputs of the head's steps ``start`` .. last for the whole batch, each rank computing the
+    rows of ``ceil(B / world)`` examples and one all-gather per step putting the batch together.
+    Per-example arithmetic does not depend on which rank (or which slice) an example is in, so
+    every rank ends up with the bits a single GPU computes.  Without this the once-per-batch
+    forward to the evaluation module is replicated on every rank and does not shrink as GPUs are
+    added (the serial fraction of the strong-scaling job)."""
     import torch.distributed as dist
 
-    B = x.shape[0]
+    B = z.shape[0]
     if world <= 1 or B < 2 or not (dist.is_available() and dist.is_initialized()):
-        return head.activation(x)
+        return head.run_steps(z, start)
     chunk = -(-B // world)
     lo, hi = min(rank * chunk, B), min((rank + 1) * chunk, B)
-    C, H, W = head.head_out
-    gathered = torch.zeros((world * chunk, C, H, W), dtype=torch.float32, device=x.device)
-    if hi > lo:
-        gathered[rank * chunk: rank * chunk + (hi - lo)] = head.activation(x[lo:hi].contiguous())
-    dist.all_gather_into_tensor(gathered, gathered[rank * chunk:(rank + 1) * chunk].clone(),
-                                group=group)
-    return gathered[:B]
+    outs = []
+    for i in range(start, len(head.exact)):
+        mine = head.run_steps(z[lo:hi].contiguous(), i, i + 1) if hi > lo else []
+        if mine:
+            shape = tuple(mine[0].shape[1:])
+        else:   # a rank without rows: the shape comes from the step itself
+            e = head.exact[i]
+            H, W = (z.shape[2] // 2, z.shape[3] // 2) if e["pool_before"] else (z.shape[2], z.shape[3])
+            shape = (e["cout"], H, W)
+        part = torch.zeros((chunk,) + shape, dtype=torch.float32, device=z.device)
+        if mine:
+            part[:hi - lo] = mine[0]
+        gathered = torch.empty((world * chunk,) + shape, dtype=torch.float32, device=z.device)
+        dist.all_gather_into_tensor(gathered, part, group=group)
+        z = gathered[:B]
+        outs.append(z)
+    return outs
 
 
 _WARNED_GENERIC = weakref.WeakSet()
@@ -311,7 +321,9 @@ class ShapleyAttributionMetric(_base._AttributionMetric):
                 if world > 1:
                     head, _ = self._agreed("head", head, head_info, True, world, x, module, group)
                 if head is not None:
-                    original_z = sharded_activation(head, x, rank, world, group)
+                    original_z = cached_activation(
+                        self.model, sig, head, x,
+                        lambda zz, start: sharded_steps(head, zz, start, rank, world, group))
                 else:
                     original_z, _ = self.run_forward_partial(x, to_module=module)
                 z = original_z.detach().float().contiguous()

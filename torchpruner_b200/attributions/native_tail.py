@@ -139,6 +139,44 @@ def cached_plan(model, module, z, kind="tail", sig=None):
     return False, None, None
 
 
+# Activations the head plans have computed, per model and input batch: scoring the layers of a
+# model one after the other on the same data (the reference's workflow: one `run` per layer, the
+# same loader) asks for the same prefix of the network again and again — the head of layer l + 1
+# is the head of layer l plus one block.  model -> {batch checksum: (signature, step keys,
+# activations after each step)}, least recently used batches dropped beyond ACT_CACHE_BYTES.
+_ACTS = weakref.WeakKeyDictionary()
+ACT_CACHE_BYTES = int(os.environ.get("TORCHPRUNER_B200_ACT_CACHE_MB", "2048")) << 20
+
+
+def cached_activation(model, sig, head, x, compute):
+    """The head's output for the batch ``x``, continuing from the longest prefix of its steps
+    whose outputs for this very batch (same bits: the batch is identified by a checksum of its
+    contents) are cached.  ``compute(z, start)`` returns the outputs of steps ``start`` .. last
+    given the output ``z`` of step ``start - 1``.  Entries are only valid under the model
+    signature they were made with, and ``forget_plans`` (which every detected change of a weight
+    goes through) drops them."""
+    if ACT_CACHE_BYTES <= 0:
+        return compute(x, 0)[-1]
+    chain = tuple(e["key"] for e in head.exact)
+    batch = (tuple(x.shape), int(_digest([x])[0]))
+    entries = _ACTS.setdefault(model, {})
+    entry = entries.pop(batch, None)
+    acts, start = [], 0
+    if entry is not None and entry[0] == sig:
+        while start < min(len(chain), len(entry[1])) and chain[start] == entry[1][start]:
+            start += 1
+        acts = list(entry[2][:start])
+    if start < len(chain):
+        acts += compute(acts[-1] if acts else x, start)
+    entries[batch] = (sig, chain, acts)   # most recently used last
+    total = 0
+    for key in reversed(list(entries)):
+        total += sum(a.numel() * a.element_size() for a in entries[key][2])
+        if total > ACT_CACHE_BYTES:
+            del entries[key]
+    return acts[len(chain) - 1]
+
+
 def note_agreement(model, module, z, kind, key, outcome):
     """Remember, with the cached plan, what the ranks of a sharded job agreed on for it (see
     shapley_values.agree_on_plan): the next run of the same job applies it without a collective.
@@ -160,9 +198,11 @@ def forget_plans(model=None):
     if model is None:
         _PLANS.clear()
         _LAYERS.clear()
+        _ACTS.clear()
     else:
         _PLANS.pop(model, None)
         _LAYERS.pop(model, None)
+        _ACTS.pop(model, None)
 
 
 def remember_plan(model, module, z, plan, info, kind="tail", sig=None):
@@ -433,6 +473,12 @@ class NativeTail:
                 exact.append({"wt": w4[:, :c_in].permute(1, 2, 3, 0).reshape(c_in, 9, cout_p).contiguous(),
                               "C1": cout_p, "cout": cout, "scale64": scale64, "shift64": shift64,
                               "relu": relu, "pool_before": pool_pending,
+                              # what this step computes, for the activation cache: the tensors
+                              # it was built from, its activation and whether it pools its input
+                              "key": (_tensor_key(m.weight, m.bias),
+                                      _tensor_key(bn_used.weight, bn_used.bias, bn_used.running_mean,
+                                                  bn_used.running_var) if bn_used is not None else None,
+                                      relu, pool_pending),
                               "unit": torch.ones(cout_p, device=dev),
                               "zero": torch.zeros(cout_p, device=dev)})
                 pool_pending = pool
@@ -642,13 +688,19 @@ class NativeTail:
         0.6-1.3e-4 of the largest score from a float64 evaluation; with the tensor-core engine's
         22-bit operands 3-7e-5; with this, 0.3-3e-5, the reference's own CPU fp32 distance
         (profiles/r02_parity_sources.txt)."""
-        cur = x
-        for e in self.exact:
+        return self.run_steps(x, 0)[-1]
+
+    def run_steps(self, cur, start, stop=None):
+        """Outputs of the head's steps ``start`` .. ``stop - 1`` (default: the last; each a
+        contiguous NCHW fp32 tensor), given the output of step ``start - 1`` (the input batch for
+        ``start == 0``)."""
+        outs = []
+        for e in self.exact[start:stop]:
             zc = _lib.channel_major(cur, e["pool_before"])
             B, C = cur.shape[0], cur.shape[1]
             H, W = (cur.shape[2] // 2, cur.shape[3] // 2) if e["pool_before"] else \
                 (cur.shape[2], cur.shape[3])
-            acc = torch.zeros(B * H * W * e["C1"], dtype=torch.float64, device=x.device)
+            acc = torch.zeros(B * H * W * e["C1"], dtype=torch.float64, device=cur.device)
             _lib.prefix_contrib_direct(zc, e["wt"], None, 0, C, acc, e["unit"], e["zero"], B, C, H, W,
                                        0, False, False, sign=1.0)
             y = acc.view(B, H, W, e["C1"])[..., :e["cout"]] * e["scale64"] + e["shift64"]
@@ -657,7 +709,8 @@ class NativeTail:
             elif e["relu"]:
                 y = torch.where(y < 0, y * e["relu"][1], y)
             cur = y.permute(0, 3, 1, 2).float().contiguous()
-        return cur
+            outs.append(cur)
+        return outs
 
     def verify_head(self, model, module, x):
         """(ok, error): the head's activation against ``forward_partial(x, to_module=module)``,
