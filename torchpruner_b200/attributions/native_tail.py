@@ -165,9 +165,11 @@ def cached_activation(model, sig, head, x, compute):
     if entry is not None and entry[0] == sig:
         while start < min(len(chain), len(entry[1])) and chain[start] == entry[1][start]:
             start += 1
+        if start == len(chain):   # everything asked for is there (the entry may go further)
+            entries[batch] = entry
+            return entry[2][start - 1]
         acts = list(entry[2][:start])
-    if start < len(chain):
-        acts += compute(acts[-1] if acts else x, start)
+    acts += compute(acts[-1] if acts else x, start)
     entries[batch] = (sig, chain, acts)   # most recently used last
     total = 0
     for key in reversed(list(entries)):
