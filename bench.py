@@ -348,8 +348,14 @@ def run_product(args, rank, world, local_rank):
 
     rank_evals = [0]
 
+    from torchpruner_b200.attributions import native_tail
+
     def device_step(step):
         np.random.seed(1000 + step)  # identical permutations on every rank
+        # Every step is the whole job from its input batch: activations cached by the previous
+        # step are dropped, so the forward to each evaluation module is computed inside the step
+        # (layer l + 1 continues from layer l's activation, as it would in any one job).
+        native_tail._ACTS.pop(model, None)
         m = make_metric(OneBatch(dx, dy))
         rank_evals[0] = 0
         for conv in convs:
@@ -359,6 +365,7 @@ def run_product(args, rank, world, local_rank):
 
     def e2e_step(step):
         np.random.seed(1000 + step)
+        native_tail._ACTS.pop(model, None)
         m = make_metric(OneBatch(hx, hy))
         h2d = d2h = 0
         for conv in convs:
@@ -421,7 +428,6 @@ def run_product(args, rank, world, local_rank):
             # the same call as a user's FIRST one on this model: no cached plan, so every layer
             # pays the trace of forward_partial, the weight preparation (fold, permute, split),
             # the fp16 range calibration and the verification against forward_partial
-            from torchpruner_b200.attributions import native_tail
             native_tail.forget_plans(model)
             barrier()
             t0 = time.perf_counter()
