@@ -974,6 +974,15 @@ def test_activation_cache_gives_the_same_bits():
         for layer in layers:          # cold cache: the same bits
             native_tail._ACTS.pop(model, None)
             assert np.array_equal(run(layer, loaders[0]), warm[(id(layer), 0)])
+        # the same examples in another order are another batch
+        from torch.utils.data import DataLoader, TensorDataset
+        x0, y0 = next(iter(loaders[0]))
+        flipped = DataLoader(TensorDataset(x0.flip(0), y0.flip(0)), batch_size=16, shuffle=False)
+        run(layers[2], loaders[0])
+        got = run(layers[2], flipped)
+        native_tail._ACTS.pop(model, None)
+        assert np.array_equal(got, run(layers[2], flipped))
+        assert np.array_equal(got, warm[(id(layers[2]), 0)][::-1])
         # a write through .data: the plan's checksum notices, plans AND activations are dropped
         model.features[17].weight.data.mul_(1.5)
         changed = run(layers[1], loaders[0])

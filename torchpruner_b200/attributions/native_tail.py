@@ -148,6 +148,16 @@ _ACTS = weakref.WeakKeyDictionary()
 ACT_CACHE_BYTES = int(os.environ.get("TORCHPRUNER_B200_ACT_CACHE_MB", "2048")) << 20
 
 
+def _batch_checksum(x):
+    """Position-dependent checksum of a batch's bits (two 64-bit sums, one weighted by the odd
+    numbers 1, 3, 5, ...): the same examples in another order — a shuffling loader over a small
+    dataset — must not look like the same batch.  One device->host copy of 16 bytes."""
+    bits = x.detach().reshape(-1).view(torch.int32).to(torch.int64)
+    weights = torch.arange(1, 2 * bits.numel(), 2, dtype=torch.int64, device=x.device)
+    both = torch.stack([bits.sum(), (bits * weights).sum()])   # integer overflow wraps: fine
+    return tuple(both.tolist())
+
+
 def cached_activation(model, sig, head, x, compute):
     """The head's output for the batch ``x``, continuing from the longest prefix of its steps
     whose outputs for this very batch (same bits: the batch is identified by a checksum of its
@@ -158,7 +168,7 @@ def cached_activation(model, sig, head, x, compute):
     if ACT_CACHE_BYTES <= 0:
         return compute(x, 0)[-1]
     chain = tuple(e["key"] for e in head.exact)
-    batch = (tuple(x.shape), int(_digest([x])[0]))
+    batch = (tuple(x.shape), _batch_checksum(x))
     entries = _ACTS.setdefault(model, {})
     entry = entries.pop(batch, None)
     acts, start = [], 0
