@@ -8,6 +8,9 @@ import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from torchpruner_b200 import _lib
 
+if os.environ.get("TP_LIB"):   # an alternative build of the library (A/B experiments)
+    _lib.LIB_PATH = os.path.abspath(os.environ["TP_LIB"])
+
 DEV = torch.device("cuda:0")
 B = 256
 # (C, Hp, Wp, C1, pool_after): first tail layer when scoring conv1, conv2(pool first), conv5, conv8, conv10
