@@ -23,3 +23,13 @@ def install_as_torchpruner():
     sys.modules["torchpruner.pruner"] = pruner
     sys.modules["torchpruner.utils"] = utils
     return this
+
+
+def forget_plans(model=None):
+    """Drop every cached execution plan, prepared weight copy, float64 twin and activation the
+    library keeps for ``model`` (for all models when None).  Plans are re-validated on every use
+    (tensor identities, version counters, a checksum of the weight bits), so this is only needed
+    to release memory early."""
+    from .attributions import native_tail
+
+    native_tail.forget_plans(model)
