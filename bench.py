@@ -309,6 +309,25 @@ def time_reductions(device, hbm_peak):
                 out[op]["c4_largest_gbs"] = nb / ms / 1e6
                 out[op]["c4_largest_frac"] = nb / ms / 1e6 / hbm_peak
         del z, g
+    # the same 53 tensors as `run_many` would reduce them on a model whose activations survive the
+    # pass (the hook-friendly ResNet-50): all resident at once, rows of up to 1024 floats (14x14,
+    # 28x28) batched into multi-tensor launches, the rest one launch each
+    try:
+        zs53, gs53 = [], []
+        for (C, H, W), count in shapes.items():
+            for _ in range(count):
+                zs53.append(torch.relu(torch.randn((256, C, H, W), device=device)))
+                gs53.append(torch.randn((256, C, H, W), device=device))
+        many = {"taylor": lambda: _lib.reduce_rows_multi("taylor", list(zip(zs53, gs53))),
+                "apoz": lambda: _lib.reduce_rows_multi("apoz", zs53),
+                "sensitivity": lambda: _lib.reduce_rows_multi("abs_sum", gs53)}
+        for op in ops:
+            ms = timed(many[op], iters=3)
+            out[op]["c4_sweep_run_many_gbs"] = totals[op][0] / ms / 1e6
+            out[op]["c4_sweep_run_many_frac"] = totals[op][0] / ms / 1e6 / hbm_peak
+        del zs53, gs53
+    except Exception as e:  # noqa: BLE001
+        log(f"bench.py: batched config-4 sweep skipped: {e}")
     for op in ops:
         nbytes, ms = totals[op]
         out[op]["c4_sweep_gbs"] = nbytes / ms / 1e6
