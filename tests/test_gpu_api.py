@@ -681,6 +681,34 @@ def test_resnet50_all_convs_taylor_apoz_sensitivity():
     assert checked >= 15
 
 
+def test_run_many_scores_all_53_resnet_layers_in_one_pass():
+    """Hook-friendly ResNet-50: every evaluation module's output survives the pass, so run_many
+    scores all 53 convolutions from one forward(/backward) per batch — 7x7 = 49-float rows go
+    through the single-tensor kernels, everything else through multi-tensor launches — and agrees
+    with `run` layer by layer."""
+    from torchpruner_b200 import _lib
+    torch.manual_seed(0)
+    model, _ = workloads.build("resnet50")
+    model.to(DEV)
+    loader = workloads.synthetic_batches((3, 96, 96), n=8, batch_size=4, seed=3)
+    convs = model.conv_layers()
+    for cls in (APoZAttributionMetric, TaylorAttributionMetric):
+        m = cls(model, loader, workloads.cross_entropy, DEV, reduction="none")
+        prof = _lib.profile_begin(timed=False)
+        many = m.run_many(convs, find_best_evaluation_module=True)
+        launches = sum(v[0] for v in prof.records.values())
+        _lib.profile_end()
+        model.zero_grad()
+        assert len(many) == 53 and launches < 2 * 53     # 2 batches; 53 launches each one by one
+        for i in list(range(0, 53, 6)) + [51, 52]:
+            want = m.run(convs[i], find_best_evaluation_module=True)
+            model.zero_grad()
+            if cls is APoZAttributionMetric:
+                np.testing.assert_array_equal(many[i], want)
+            else:
+                assert norm_err(many[i], want) <= 1e-5
+
+
 def test_stock_resnet50_matches_the_reference_where_it_is_defined():
     """Config 4 on torchvision's ResNet-50 as it ships, find_best_evaluation_module=True, against
     the unmodified reference (tests/golden/resnet50.{npz,txt}, make_golden.py gen_resnet).
