@@ -45,7 +45,10 @@ int tp_device_check(int device);
  *   reduce_tile_floats (multiple of 256), reduce_ctas_per_sm, reduce_tma_min_elems,
  *   reduce_ldg_waves; conv_variant (0 persistent, 1 one tile per CTA), conv_promote (k-blocks per
  *   TMEM partial sum), conv_pos_major (0 auto, 1 never), conv_pos_major_max_hw, conv_pair (256-row
- *   tiles on CTA pairs: 0 where measured faster, 1 never, 2 wherever possible).
+ *   tiles on CTA pairs: 0 where measured faster, 1 never, 2 wherever possible); prefix_variant
+ *   (tp_prefix_contrib_stack: 0 by size, 1 register-load kernel, 2 cp.async ring kernel),
+ *   prefix_ring_cfg (0 by size, 1..3 a fixed ring depth / CTAs per SM), prefix_threads (0 even
+ *   waves, else a forced CTA size).  Every setting of these gives the same bits.
  * Returns TP_ERR_INVALID for an unknown key or an out-of-range value. */
 int tp_set_tuning(const char* key, int64_t value);
 

@@ -761,6 +761,60 @@ def test_direct_prefix_ladder_matches_stored_contributions(B, C, H, W, C1, pool_
     assert float(outs[1][0].float().abs().max()) > 0
 
 
+@pytest.mark.parametrize("half", [False, True])
+@pytest.mark.parametrize("B,Hp,Wp,C,C1,pool_after", [
+    (3, 8, 8, 9, 32, False),
+    (2, 8, 8, 7, 16, True),
+    (5, 2, 2, 6, 128, True),
+    (7, 1, 1, 12, 32, False),
+    (64, 8, 8, 5, 256, True),     # more items than one wave of any configuration
+    (64, 8, 8, 5, 256, False),
+    (1, 4, 6, 4, 8, True),        # fewer items than a warp
+])
+def test_prefix_ring_kernel_matches_register_kernel(B, Hp, Wp, C, C1, pool_after, half):
+    """The stored-form sweep has two kernels (register loads; cp.async ring in several depth /
+    occupancy configurations, picked by size): same arithmetic in the same order, so outputs and
+    running sums must be identical bit for bit, with fewer masks than ring stages too."""
+    gen = torch.Generator().manual_seed(B * 31 + C)
+    pixels = B * Hp * Wp
+    M1 = pixels * C1
+    m_out = (pixels // 4 if pool_after else pixels) * C1
+    T = torch.randn(C * M1, generator=gen).to(DEV)
+    s_all = T.view(C, M1).sum(0, dtype=torch.float64)
+    scale = (torch.rand(C1, generator=gen) - 0.3).to(DEV)
+    shift = (torch.randn(C1, generator=gen) * 0.1).to(DEV)
+    perm = torch.from_numpy(np.random.RandomState(C).permutation(C).astype(np.int64)).to(DEV)
+    dt = torch.float16 if half else torch.float32
+
+    def sweep(P):
+        base = s_all.clone()
+        hi = torch.zeros(max(P, 1) * m_out, device=DEV, dtype=dt)
+        lo = torch.zeros_like(hi)
+        _lib.prefix_contrib_stack(T, perm, 0, 1, base, scale, shift, pixels, C1, Hp, Wp, pool_after,
+                                  ("leaky", 0.1))
+        _lib.prefix_contrib_stack(T, perm, 1, P, base, scale, shift, pixels, C1, Hp, Wp, pool_after,
+                                  ("leaky", 0.1), hi, lo, out_scale=4.0 if half else 1.0)
+        return hi, lo, base
+
+    try:
+        for P in (C - 1, 1, 2):
+            _lib.set_tuning("prefix_variant", 1)
+            want = sweep(P)
+            assert float(want[0].float().abs().max()) > 0
+            for cfg in (1, 2, 3):
+                for threads in (0, 32, 96):
+                    _lib.set_tuning("prefix_variant", 2)
+                    _lib.set_tuning("prefix_ring_cfg", cfg)
+                    _lib.set_tuning("prefix_threads", threads)
+                    got = sweep(P)
+                    for a, b in zip(got, want):
+                        assert torch.equal(a, b), (P, cfg, threads)
+    finally:
+        _lib.set_tuning("prefix_variant", 0)
+        _lib.set_tuning("prefix_ring_cfg", 0)
+        _lib.set_tuning("prefix_threads", 0)
+
+
 def test_native_tail_runs_the_reference_mlp():
     """The 784-2024-2024-10 LeakyReLU perceptron of the reference's untrained-network notebook:
     Linear layers whose K is not a multiple of 32, LeakyReLU epilogue, dense incremental first

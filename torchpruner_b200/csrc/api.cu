@@ -92,6 +92,16 @@ int tp_set_tuning(const char* key, int64_t value) {
   } else if (!strcmp(key, "conv_pair")) {
     TP_REQUIRE(value >= 0 && value <= 2, TP_ERR_INVALID, "conv_pair must be 0, 1 or 2");
     t.conv_pair = (int)value;
+  } else if (!strcmp(key, "prefix_variant")) {
+    TP_REQUIRE(value >= 0 && value <= 2, TP_ERR_INVALID, "prefix_variant must be 0, 1 or 2");
+    t.prefix_variant = (int)value;
+  } else if (!strcmp(key, "prefix_threads")) {
+    TP_REQUIRE(value >= 0 && value <= 256 && value % 32 == 0, TP_ERR_INVALID,
+               "prefix_threads must be 0 or a multiple of 32 up to 256");
+    t.prefix_threads = (int)value;
+  } else if (!strcmp(key, "prefix_ring_cfg")) {
+    TP_REQUIRE(value >= 0 && value <= 3, TP_ERR_INVALID, "prefix_ring_cfg must be in [0,3]");
+    t.prefix_ring_cfg = (int)value;
   } else if (!strcmp(key, "conv_promote")) {
     TP_REQUIRE(value >= 1 && value <= 4096, TP_ERR_INVALID, "conv_promote must be in [1,4096]");
     t.conv_promote = (int)value;

@@ -408,6 +408,122 @@ __device__ __forceinline__ void emit_split4(float4 y, float out_scale, void* out
   }
 }
 
+// ---- stored form, contributions staged through a shared-memory ring -------------------------
+// Same items, same arithmetic in the same order as prefix_contrib_stack_kernel (bit-identical
+// results), but a thread's contribution loads are cp.async copies into its own slots of a D-deep
+// ring instead of register loads: D-1 masks x NSRC 16-byte copies stay in flight per thread at all
+// times (the register version drains to zero at the end of every U-mask trip), and without the
+// U x NSRC float4 staging registers three (pooled) or four CTAs fit an SM instead of two.
+// A thread reads back only what it copied itself, so cp.async.wait_group is the only
+// synchronisation; slot (p+D-1)%D is refilled one iteration after the same thread read it.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <bool POOL, bool HALF, int D, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
+prefix_contrib_ring_kernel(const float* __restrict__ T, const int64_t* __restrict__ perm,
+                           long long k0, int P, double* __restrict__ base,
+                           const float* __restrict__ scale, const float* __restrict__ shift,
+                           PrefixGeom g, void* __restrict__ out_hi_v, void* __restrict__ out_lo_v) {
+  constexpr int NSRC = POOL ? 4 : 1;
+  extern __shared__ __align__(16) unsigned char ring_raw[];
+  float4* ring = reinterpret_cast<float4*>(ring_raw);          // [D][NSRC][blockDim.x]
+  const unsigned nthr = blockDim.x;
+  const uint32_t ring_u32 = smem_u32(ring) + threadIdx.x * 16u;
+  const int opp = g.C1 >> 2;
+  const long long out_pos = POOL ? (g.M1 / g.C1) / 4 : (g.M1 / g.C1);
+  const long long items = out_pos * opp;
+  const long long m_out = out_pos * g.C1;
+  // element offsets of the 2x2 window's other three pixels from the first
+  const int d1 = g.C1, d2 = g.Wp * g.C1, d3 = d2 + g.C1;
+  for (long long it = blockIdx.x * (long long)nthr + threadIdx.x; it < items;
+       it += gridDim.x * (long long)nthr) {
+    const long long pos = it / opp;
+    const int o4 = (int)(it - pos * opp);
+    long long off0;
+    if (POOL) {
+      const int Wo = g.Wp / 2, Ho = g.Hp / 2;
+      const int wo = (int)(pos % Wo);
+      const long long t = pos / Wo;
+      const int ho = (int)(t % Ho);
+      const long long bi = t / Ho;
+      off0 = ((bi * g.Hp + 2 * ho) * g.Wp + 2 * wo) * g.C1 + o4 * 4;
+    } else {
+      off0 = pos * g.C1 + o4 * 4;
+    }
+    auto off = [&](int s) -> long long {
+      return off0 + (s == 0 ? 0 : s == 1 ? d1 : s == 2 ? d2 : d3);
+    };
+    double run[NSRC][4];
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      const double* bp = base + off(s);
+      run[s][0] = bp[0];
+      run[s][1] = bp[1];
+      run[s][2] = bp[2];
+      run[s][3] = bp[3];
+    }
+    const uint32_t stage_bytes = NSRC * nthr * 16u;
+    auto issue = [&](int p, int stage) {
+      const float* Tc = T + perm[k0 + p] * g.M1;
+      const uint32_t slot = ring_u32 + (uint32_t)stage * stage_bytes;
+#pragma unroll
+      for (int s = 0; s < NSRC; ++s) cp_async16(slot + s * nthr * 16u, Tc + off(s));
+    };
+#pragma unroll
+    for (int d = 0; d < D - 1; ++d) {
+      if (d < P) issue(d, d);
+      cp_async_commit();
+    }
+    int fill = D - 1, drain = 0;     // ring stages of mask p+D-1 and of mask p
+    for (int p = 0; p < P; ++p) {
+      if (p + D - 1 < P) issue(p + D - 1, fill);
+      cp_async_commit();
+      cp_async_wait<D - 1>();
+      const float4* slot = ring + (size_t)drain * NSRC * nthr + threadIdx.x;
+      fill = fill + 1 == D ? 0 : fill + 1;
+      drain = drain + 1 == D ? 0 : drain + 1;
+      float4 y = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+      for (int s = 0; s < NSRC; ++s) {
+        const float4 t = slot[s * nthr];
+        run[s][0] -= (double)t.x;
+        run[s][1] -= (double)t.y;
+        run[s][2] -= (double)t.z;
+        run[s][3] -= (double)t.w;
+        if (g.emit) {
+          const float4 a = reinterpret_cast<const float4*>(scale)[o4];
+          const float4 b = reinterpret_cast<const float4*>(shift)[o4];
+          y.x = nan_max(y.x, affine_act(run[s][0], a.x, b.x, g.relu, g.slope));
+          y.y = nan_max(y.y, affine_act(run[s][1], a.y, b.y, g.relu, g.slope));
+          y.z = nan_max(y.z, affine_act(run[s][2], a.z, b.z, g.relu, g.slope));
+          y.w = nan_max(y.w, affine_act(run[s][3], a.w, b.w, g.relu, g.slope));
+        }
+      }
+      if (g.emit)
+        emit_split4<HALF>(y, g.out_scale, out_hi_v, out_lo_v,
+                          (long long)p * m_out + pos * g.C1 + o4 * 4);
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int s = 0; s < NSRC; ++s) {
+      double* bp = base + off(s);
+      bp[0] = run[s][0];
+      bp[1] = run[s][1];
+      bp[2] = run[s][2];
+      bp[3] = run[s][3];
+    }
+  }
+}
+
 template <int BLK, bool HALF>
 __global__ void __launch_bounds__(256, 2)
 prefix_direct_conv_kernel(const float* __restrict__ zc, const float* __restrict__ wt,
@@ -579,6 +695,50 @@ static inline unsigned inc_grid(long long items, int waves = 16) {
   return (unsigned)blocks;
 }
 
+// items are walked one per thread for all P masks, so a launch is as long as its number of waves:
+// the CTA size is the smallest that keeps that number, which evens the waves out
+template <bool POOL, bool HALF, int D, int MAXT, int MINB>
+static int launch_prefix_ring(const float* T, const int64_t* perm, long long k0, int P, double* base,
+                              const float* scale, const float* shift, const PrefixGeom& g,
+                              void* out_hi, void* out_lo, long long items, cudaStream_t st) {
+  const long long slots = (long long)sm_count() * MINB;
+  const long long waves = (items + slots * MAXT - 1) / (slots * MAXT);
+  long long threads = (items + slots * waves - 1) / (slots * waves);
+  threads = (threads + 31) / 32 * 32;
+  if (threads > MAXT) threads = MAXT;
+  if (tuning().prefix_threads) threads = std::min<long long>(tuning().prefix_threads, MAXT);
+  const size_t smem = (size_t)D * (POOL ? 4 : 1) * threads * 16;
+  long long blocks = (items + threads - 1) / threads;
+  const long long cap = slots * 16;
+  if (blocks > cap) blocks = cap;
+  auto kern = prefix_contrib_ring_kernel<POOL, HALF, D, MAXT, MINB>;
+  TP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)blocks, (unsigned)threads, smem, st>>>(T, perm, k0, P, base, scale, shift, g,
+                                                         out_hi, out_lo);
+  TP_LAUNCH_CHECK("prefix_contrib_ring_kernel");
+  return TP_OK;
+}
+
+// ring configurations: 1..3 pooled (depth 4 x 3 CTAs of 256, depth 3 x 4 CTAs of 224, depth 8 x one
+// CTA), 1..2 unpooled (depth 8 x 4 CTAs of 256, depth 16 x 2 CTAs)
+template <bool HALF>
+static int launch_prefix_ring_cfg(int cfg, bool pool, const float* T, const int64_t* perm,
+                                  long long k0, int P, double* base, const float* scale,
+                                  const float* shift, const PrefixGeom& g, void* out_hi,
+                                  void* out_lo, long long items, cudaStream_t st) {
+#define TP_RING(POOL_, D_, MAXT_, MINB_)                                                       \
+  return launch_prefix_ring<POOL_, HALF, D_, MAXT_, MINB_>(T, perm, k0, P, base, scale, shift, g, \
+                                                           out_hi, out_lo, items, st)
+  if (pool) {
+    if (cfg == 2) TP_RING(true, 3, 224, 4);
+    if (cfg == 3) TP_RING(true, 8, 256, 1);
+    TP_RING(true, 4, 256, 3);
+  }
+  if (cfg == 2) TP_RING(false, 16, 256, 2);
+  TP_RING(false, 8, 256, 4);
+#undef TP_RING
+}
+
 }  // namespace tp
 
 extern "C" {
@@ -668,6 +828,22 @@ static int prefix_contrib_stack_impl(const float* T, const int64_t* perm, int64_
   g.out_scale = out_scale;
   const long long items = (pool ? pixels / 4 : pixels) * (C1 / 4);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Which kernel (profiles/r02_prefix_ring_ab.txt): below ~512 items per SM a launch is one thin
+  // wave either way and the register-load kernel is as fast or faster; above, the ring, and for the
+  // pooled sweep the 4 x 224-thread configuration where it saves a wave (10 % better filled).
+  const long long ipsm = (items + sm_count() - 1) / sm_count();
+  const int variant = tuning().prefix_variant;
+  if (variant == 2 || (variant == 0 && ipsm >= 512)) {
+    int cfg = tuning().prefix_ring_cfg;
+    if (cfg == 0) {
+      auto fill = [&](long long cap) { return (double)ipsm / (double)((ipsm + cap - 1) / cap * cap); };
+      cfg = (pool && fill(4 * 224) > fill(3 * 256) + 0.1) ? 2 : 1;
+    }
+    return half ? launch_prefix_ring_cfg<true>(cfg, pool != 0, T, perm, k0, (int)P, base, scale,
+                                               shift, g, out_hi, out_lo, items, st)
+                : launch_prefix_ring_cfg<false>(cfg, pool != 0, T, perm, k0, (int)P, base, scale,
+                                                shift, g, out_hi, out_lo, items, st);
+  }
   const unsigned grid = inc_grid(items);
   if (pool && half) {
     prefix_contrib_stack_kernel<true, true><<<grid, 256, 0, st>>>(T, perm, k0, (int)P, base, scale,
