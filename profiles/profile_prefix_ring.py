@@ -53,7 +53,7 @@ def timed(s, gm, iters=5):
         a.record(); launch(s, gm, hi, lo, base); b.record(); b.synchronize()
         if i:
             ms.append(a.elapsed_time(b))
-    return statistics.median(ms), hi, lo, base
+    return (statistics.median(ms) if ms else 0.0), hi, lo, base
 
 
 if "ncu" in sys.argv:
