@@ -242,6 +242,17 @@ int tp_conv_f16x3_pool2(const void* x_hi, const void* x_lo, int64_t N, int64_t H
                         const float* scale, const float* shift, int act, float leaky_slope,
                         float out_scale, void* y_hi, void* y_lo, tp_stream_t stream);
 int tp_conv_pool2_fusable(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout);
+/* The last VGG block's conv-BN-ReLU-MaxPool on a 2x2 image (cifar10.py:62-77) in its dense form: a
+ * linear layer x [N, Cin] -> four groups of Cout features (one per output pixel; w_* are
+ * [4*Cout, Cin], group-major), scale/shift [Cout] shared by the groups, and the maximum over the
+ * four groups stored: y_* [N, Cout] fp16 pairs of max_g act(scale*(x.W_g) + shift) * out_scale.
+ * The four groups of a tile are computed back to back by the same CTA with their running maximum
+ * in TMEM, like tp_conv_f16x3_pool2; same bits as tp_conv_f16x3 on [4*Cout, Cin] followed by
+ * tp_maxpool2_split_nhwc_f16 on the [N, 2, 2, Cout] view.  Cout % 64 == 0, Cin % 8 == 0. */
+int tp_linear_f16x3_pool4(const void* x_hi, const void* x_lo, int64_t N, int64_t Cin,
+                          const void* w_hi, const void* w_lo, int64_t Cout, const float* scale,
+                          const float* shift, int act, float leaky_slope, float out_scale,
+                          void* y_hi, void* y_lo, tp_stream_t stream);
 int tp_f16_split(const float* x, int64_t n, float scale, void* hi, void* lo, tp_stream_t stream);
 int tp_mask_stack_nhwc_f16(const float* z, const int32_t* inv_perm, int64_t k0, int64_t P,
                            int64_t B, int64_t C, int64_t H, int64_t W, int pool, float scale,

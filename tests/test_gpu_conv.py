@@ -926,6 +926,46 @@ def test_conv_f16x3_fused_pool_is_bit_identical(N, H, W, Cin, Cout, relu):
     assert float((y - ref).abs().max()) <= 1e-6 * float(ref.abs().max())
 
 
+@pytest.mark.parametrize("N,Cin,Cout,relu", [
+    (256, 2048, 512, True),                  # VGG16's conv13 at bs 256: CTA pairs, 4 N tiles
+    (130, 256, 64, ("leaky", 0.2)),          # BLOCK_N = 64, ragged second image block
+    (100, 64, 128, False),                   # one image block (no pair), negative outputs
+    (1500, 512, 192, True),                  # more tiles than SMs, Cout not a multiple of 128
+])
+def test_linear_pool4_is_bit_identical(N, Cin, Cout, relu):
+    """tp_linear_f16x3_pool4 (four output groups back to back, maximum kept in TMEM) against
+    tp_conv_f16x3 on the [4*Cout, Cin] weight followed by tp_maxpool2_split_nhwc_f16 on the
+    [N, 2, 2, Cout] view: the same partial sums and rounding, so the same bits."""
+    gen = torch.Generator(device=DEV).manual_seed(N + 7 * Cin)
+    x = torch.randn((N, 1, 1, Cin), device=DEV, generator=gen) * 2.0
+    w = torch.randn((4 * Cout, Cin), device=DEV, generator=gen) / Cin ** 0.5
+    scale = torch.rand(Cout, device=DEV, generator=gen) + 0.5
+    scale[::3] *= -1.0
+    shift = torch.randn(Cout, device=DEV, generator=gen) * 0.3
+    s_x = 2.0 ** round(np.log2(64.0 / float(x.abs().max())))
+    s_w = 2.0 ** round(np.log2(64.0 / float(w.abs().max())))
+    x_hi, x_lo = _lib.f16_split(x, s_x)
+    w_hi, w_lo = _lib.f16_split(w, s_w)
+    sc = (scale / (s_x * s_w)).contiguous()
+    out_scale = 4.0
+    raw, _ = _lib.conv_tf32x3(x_hi, x_lo, w_hi, w_lo, 1, sc.repeat(4), shift.repeat(4), relu,
+                              split=False)
+    want_hi, want_lo = _lib.maxpool2_split_nhwc(raw.view(N, 2, 2, Cout), half=True, scale=out_scale)
+    got_hi, got_lo = _lib.linear_pool4(x_hi, x_lo, w_hi, w_lo, sc, shift, relu, out_scale=out_scale)
+    assert got_hi.shape == (N, 1, 1, Cout) and got_hi.dtype == torch.float16
+    assert torch.equal(got_hi, want_hi) and torch.equal(got_lo, want_lo)
+    ref = _ref64(x, w, 1, scale.repeat(4), shift.repeat(4), relu).view(N, 4, Cout).amax(dim=1)
+    y = (got_hi.double() + got_lo.double()).view(N, Cout) / out_scale
+    assert float((y - ref).abs().max()) <= 1e-6 * float(ref.abs().max())
+    for pair in (1, 2):      # single-CTA tiles and CTA pairs
+        _lib.set_tuning("conv_pair", pair)
+        try:
+            again = _lib.linear_pool4(x_hi, x_lo, w_hi, w_lo, sc, shift, relu, out_scale=out_scale)
+        finally:
+            _lib.set_tuning("conv_pair", 0)
+        assert torch.equal(again[0], want_hi) and torch.equal(again[1], want_lo)
+
+
 def test_conv_pool2_fusable_limits():
     assert not _lib.conv_pool2_fusable(64, 4, 4, 64, 64)      # fewer than 128 images
     assert not _lib.conv_pool2_fusable(256, 16, 16, 64, 64)   # row-major tiles

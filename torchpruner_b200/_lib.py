@@ -81,6 +81,9 @@ _SIGNATURES = {
                                            _vp, _vp, ctypes.c_int, ctypes.c_float, ctypes.c_float,
                                            _vp, _vp, _vp]),
     "tp_conv_pool2_fusable": (ctypes.c_int, [_i64, _i64, _i64, _i64, _i64]),
+    "tp_linear_f16x3_pool4": (ctypes.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp,
+                                             ctypes.c_int, ctypes.c_float, ctypes.c_float, _vp, _vp,
+                                             _vp]),
     "tp_f16_split": (ctypes.c_int, [_vp, _i64, ctypes.c_float, _vp, _vp, _vp]),
     "tp_mask_stack_nhwc_f16": (ctypes.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64,
                                               ctypes.c_int, ctypes.c_float, _i64, _vp, _vp, _vp]),
@@ -515,6 +518,35 @@ def conv_tf32x3(x_hi, x_lo, w_hi, w_lo, taps, scale, shift, relu, split=True, ou
                 int(taps), Cout, scale.data_ptr(), shift.data_ptr(), *_act_code(relu),
                 y_hi.data_ptr(), y_lo.data_ptr() if y_lo is not None else 0, _stream(x_hi)),
                 "tp_conv_tf32x3")
+    return y_hi, y_lo
+
+
+def linear_pool4(x_hi, x_lo, w_hi, w_lo, scale, shift, relu, out_scale=1.0):
+    """Dense form of conv3x3 + affine + activation + MaxPool2d(2) on a 2x2 image, fp16 flavour:
+    x_* [N, Cin] (any shape with N leading), w_* [4*Cout, Cin] group-major (one group per output
+    pixel), scale/shift [Cout].  Returns the fp16 pair [N, 1, 1, Cout] of the maximum over the four
+    groups, times out_scale."""
+    x_hi, x_lo = _cuda_half(x_hi, "x_hi"), _cuda_half(x_lo, "x_lo")
+    if w_hi.dtype != torch.float16 or w_lo.dtype != torch.float16:
+        raise TorchPrunerB200Error("linear_pool4: fp16 activations need fp16 weights")
+    N = x_hi.shape[0]
+    Cin = x_hi.numel() // max(N, 1)
+    Cout = w_hi.shape[0] // 4
+    if w_hi.shape[0] != 4 * Cout or w_hi.shape[1] != Cin or w_lo.shape != w_hi.shape or \
+            x_lo.shape != x_hi.shape or scale.numel() != Cout or shift.numel() != Cout:
+        raise TorchPrunerB200Error("linear_pool4: operand shapes do not match")
+    y_hi = torch.empty((N, 1, 1, Cout), dtype=torch.float16, device=x_hi.device)
+    y_lo = torch.empty_like(y_hi)
+    flops = load().tp_conv_tf32x3_flops(N, 1, 1, Cin, 4 * Cout, 1) if _profile is not None else 0
+    nbytes = 2 * (2 * x_hi.numel() + 2 * w_hi.numel()) + 2 * 2 * y_hi.numel()
+    name = "conv_f16x3"
+    if _profile is not None and getattr(_profile, "by_shape", False):
+        name = f"{name}[1x1 {Cin}->{4 * Cout} t1 pool4]"
+    with torch.cuda.device(x_hi.device), _launch(name, nbytes, x_hi, 1, flops):
+        _check(load().tp_linear_f16x3_pool4(
+            x_hi.data_ptr(), x_lo.data_ptr(), N, Cin, w_hi.data_ptr(), w_lo.data_ptr(), Cout,
+            scale.data_ptr(), shift.data_ptr(), *_act_code(relu), float(out_scale),
+            y_hi.data_ptr(), y_lo.data_ptr(), _stream(x_hi)), "tp_linear_f16x3_pool4")
     return y_hi, y_lo
 
 

@@ -669,6 +669,15 @@ class NativeTail:
                                               s["shift"], s["relu"], split=True,
                                               out_scale=next_scale, pool=True)
                 continue
+            if f16 and s["pool"] and s["out_view"] is not None and idx < last and FUSE_POOL \
+                    and s["out_view"][2] % 64 == 0:
+                # dense 2x2 layer + MaxPool2d(2): the four output pixels are four groups of output
+                # features, maximum kept in TMEM (scale/shift are the per-channel vectors x 4)
+                cp = s["out_view"][2]
+                x_hi, x_lo = _lib.linear_pool4(x_hi, x_lo, s["w16_hi"], s["w16_lo"],
+                                               s["scale16"][:cp], s["shift"][:cp], s["relu"],
+                                               out_scale=next_scale)
+                continue
             if f16:
                 y_hi, y_lo = _lib.conv_tf32x3(x_hi, x_lo, s["w16_hi"], s["w16_lo"], s["taps"],
                                               s["scale16"], s["shift"], s["relu"], split=split,

@@ -54,7 +54,11 @@ struct ConvGeom {
   int promote;   // k-blocks accumulated in TMEM before the partial sum is folded into registers
   int pool;      // persistent kernel, position-major fp16 split outputs: MaxPool2d(2) fused into
                  // the epilogue (tiles_h x tiles_w is then the POOLED grid; every tile index
-                 // stands for the four output pixels of one window, computed back to back)
+                 // stands for the four output pixels of one window, computed back to back).
+                 // 2: a linear layer whose 4*Cout output features are four groups of Cout (the
+                 // dense form of a 3x3 convolution on a 2x2 image: one group per output pixel);
+                 // the four groups of a tile are computed back to back from the same rows of
+                 // the input and B rows sub*Cout.., and their maximum is stored
   long long m_total;
 };
 
@@ -725,8 +729,9 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           tile_origin(g, mt, n0, hb, wb);
         }
         for (int sub = 0; sub < subs; ++sub) {
-          const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
-          const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+          const int h0 = g.pool == 1 ? 2 * hb + (sub >> 1) : hb;
+          const int w0 = g.pool == 1 ? 2 * wb + (sub & 1) : wb;
+          const int bsub = g.pool == 2 ? sub * g.Cout : 0;   // B rows of this output group
           for (int tap = 0; tap < g.taps; ++tap) {
             const int r = (g.taps == 9) ? tap / 3 : 1;
             const int s = (g.taps == 9) ? tap - r * 3 : 1;
@@ -743,7 +748,7 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                 } else {
                   mbar_arrive_cluster(bar);
                 }
-                const int brow = nt * BLOCK_N + rank * Cfg::kBRows;
+                const int brow = bsub + nt * BLOCK_N + rank * Cfg::kBRows;
                 tma_load_4d_pair(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, bar);
                 tma_load_4d_pair(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
                                  bar);
@@ -755,10 +760,10 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
                 tma_load_4d(st, &tm_a_hi, cb * kKE, w0 + s - 1, h0 + r - 1, n0, &full[stage]);
                 tma_load_4d(st + Cfg::kABytes, &tm_a_lo, cb * kKE, w0 + s - 1, h0 + r - 1, n0,
                             &full[stage]);
-                tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, nt * BLOCK_N,
+                tma_load_2d(st + 2 * Cfg::kABytes, &tm_b_hi, kb * kKE, bsub + nt * BLOCK_N,
                             &full[stage]);
                 tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kBBytes, &tm_b_lo, kb * kKE,
-                            nt * BLOCK_N, &full[stage]);
+                            bsub + nt * BLOCK_N, &full[stage]);
               }
               if (++stage == Cfg::kStages) {
                 stage = 0;
@@ -792,8 +797,8 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
           tile_origin(g, tile / n_tiles, n0, hb, wb);
         }
         for (int sub = 0; sub < subs; ++sub) {
-          const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
-          const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+          const int h0 = g.pool == 1 ? 2 * hb + (sub >> 1) : hb;
+          const int w0 = g.pool == 1 ? 2 * wb + (sub & 1) : wb;
           const int nk = count_kblocks(g, h0, w0);
           int in_chunk = 0;
           for (int kb = 0; kb < nk; ++kb) {
@@ -873,8 +878,8 @@ conv_tf32x3_persistent(const __grid_constant__ CUtensorMap tm_a_hi,
         tile_origin(g, mt, n0, hb, wb);
       }
       for (int sub = 0; sub < subs; ++sub) {
-        const int h0 = g.pool ? 2 * hb + (sub >> 1) : hb;
-        const int w0 = g.pool ? 2 * wb + (sub & 1) : wb;
+        const int h0 = g.pool == 1 ? 2 * hb + (sub >> 1) : hb;
+        const int w0 = g.pool == 1 ? 2 * wb + (sub & 1) : wb;
         const int nk = count_kblocks(g, h0, w0);
         const int chunks_this_tile = (nk + g.promote - 1) / g.promote;
         // per-tile scale/shift (everyone finished reading the previous tile's at its last barrier)
@@ -1210,7 +1215,8 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
                                   cudaStream_t st) {
   using Cfg = ConvCfgP<BLOCK_N, PAIR>;
   CUtensorMap b_hi, b_lo, o_hi, o_lo;
-  const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin, (cuuint64_t)g.Cout};
+  const cuuint64_t bdims[2] = {(cuuint64_t)g.taps * g.Cin,
+                               (cuuint64_t)g.Cout * (g.pool == 2 ? 4 : 1)};
   const cuuint32_t bbox[2] = {(cuuint32_t)KBlock<F16>::kElems, (cuuint32_t)Cfg::kBRows};
   int rc = make_map(&b_hi, w_hi, 2, bdims, bbox, F16);
   if (rc != TP_OK) return rc;
@@ -1218,8 +1224,8 @@ static int launch_conv_persistent(const CUtensorMap& a_hi, const CUtensorMap& a_
   if (rc != TP_OK) return rc;
   // fp16 split outputs are stored 64 halves (128 bytes) per staging row; everything else is fp32
   const bool half_out = F16 && g.split;
-  const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)(g.pool ? g.W / 2 : g.W),
-                               (cuuint64_t)(g.pool ? g.H / 2 : g.H), (cuuint64_t)g.N};
+  const cuuint64_t ydims[4] = {(cuuint64_t)g.Cout, (cuuint64_t)(g.pool == 1 ? g.W / 2 : g.W),
+                               (cuuint64_t)(g.pool == 1 ? g.H / 2 : g.H), (cuuint64_t)g.N};
   const cuuint32_t ybox[4] = {half_out ? 64u : 32u, (cuuint32_t)g.bw, (cuuint32_t)g.bh,
                               (cuuint32_t)g.bn};
   rc = make_map(&o_hi, y_hi, 4, ydims, ybox, half_out);
@@ -1316,7 +1322,11 @@ static int conv_x3_impl(const void* x_hi, const void* x_lo, int64_t N, int64_t H
     g.tiles_w = (int)W;
   }
   g.pool = 0;
-  if (pool) {
+  if (pool == 2) {
+    TP_REQUIRE(F16 && persistent && taps == 1 && H == 1 && W == 1 && y_lo != nullptr, TP_ERR_LIMIT,
+               "tp_linear_f16x3_pool4: needs Cout %% 64 == 0, Cout > 16 and split outputs");
+    g.pool = 2;
+  } else if (pool) {
     TP_REQUIRE(F16 && pos_major && y_lo != nullptr && H % 2 == 0 && W % 2 == 0, TP_ERR_LIMIT,
                "tp_conv_f16x3_pool2: needs position-major tiles (3x3, H*W <= %d, N >= 128), even "
                "H and W and split outputs; ask tp_conv_pool2_fusable first",
@@ -1408,6 +1418,16 @@ int tp_conv_f16x3_pool2(const void* x_hi, const void* x_lo, int64_t N, int64_t H
                         float out_scale, void* y_hi, void* y_lo, tp_stream_t stream) {
   return tp::conv_x3_impl<true>(x_hi, x_lo, N, H, W, Cin, w_hi, w_lo, 9, Cout, scale, shift, act,
                                 leaky_slope, out_scale, y_hi, y_lo, stream, 1);
+}
+
+int tp_linear_f16x3_pool4(const void* x_hi, const void* x_lo, int64_t N, int64_t Cin,
+                          const void* w_hi, const void* w_lo, int64_t Cout, const float* scale,
+                          const float* shift, int act, float leaky_slope, float out_scale,
+                          void* y_hi, void* y_lo, tp_stream_t stream) {
+  TP_REQUIRE(tp::tuning().conv_variant != 1, TP_ERR_LIMIT,
+             "tp_linear_f16x3_pool4: needs the persistent kernel (conv_variant 0)");
+  return tp::conv_x3_impl<true>(x_hi, x_lo, N, 1, 1, Cin, w_hi, w_lo, 1, Cout, scale, shift, act,
+                                leaky_slope, out_scale, y_hi, y_lo, stream, 2);
 }
 
 int tp_conv_pool2_fusable(int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout) {
