@@ -234,7 +234,7 @@ int tp_conv_f16x3(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int6
  * conv-BN-ReLU-MaxPool) fused into the epilogue: y_* are [N, H/2, W/2, Cout] fp16 pairs.  Tiles
  * are position-major (one output pixel x 128 images); the four pixels of a window are computed
  * back to back by the same CTA and their running maximum stays in TMEM, so the full-resolution
- * output never reaches HBM.  Only where tp_conv_pool2_fusable() says 1 (3x3, H*W <= 64, even H
+ * output never reaches HBM.  Only where tp_conv_pool2_fusable() says 1 (3x3, H*W <= 256, even H
  * and W, N >= 128, Cin % 64 == 0, Cout % 64 == 0); TP_ERR_LIMIT otherwise — the caller then runs
  * tp_conv_f16x3 + tp_maxpool2_split_nhwc_f16. */
 int tp_conv_f16x3_pool2(const void* x_hi, const void* x_lo, int64_t N, int64_t H, int64_t W,

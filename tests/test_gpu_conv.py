@@ -968,10 +968,10 @@ def test_linear_pool4_is_bit_identical(N, Cin, Cout, relu):
 
 def test_conv_pool2_fusable_limits():
     assert not _lib.conv_pool2_fusable(64, 4, 4, 64, 64)      # fewer than 128 images
-    assert not _lib.conv_pool2_fusable(256, 16, 16, 64, 64)   # row-major tiles
+    assert not _lib.conv_pool2_fusable(256, 32, 32, 64, 64)   # row-major tiles
     assert not _lib.conv_pool2_fusable(256, 4, 4, 32, 64)     # Cin % 64
     assert not _lib.conv_pool2_fusable(256, 4, 4, 64, 96)     # Cout % 64
-    x = torch.zeros((256, 16, 16, 64), device=DEV, dtype=torch.float16)
+    x = torch.zeros((256, 32, 32, 64), device=DEV, dtype=torch.float16)
     w = torch.zeros((64, 576), device=DEV, dtype=torch.float16)
     one = torch.ones(64, device=DEV)
     with pytest.raises(_lib.TorchPrunerB200Error, match="position-major"):

@@ -54,7 +54,7 @@ struct Tuning {
   int conv_promote = 2;          // k-blocks (of 32 inputs) per TMEM partial sum
   int conv_variant = 0;          // 0 auto (persistent + TMA stores), 1 one tile per CTA
   int conv_pos_major = 0;        // 0 auto (position-major tiles for small images), 1 never
-  int conv_pos_major_max_hw = 64;  // largest H*W that gets position-major tiles
+  int conv_pos_major_max_hw = 256;  // largest H*W that gets position-major tiles
   int conv_pair = 0;             // CTA pairs (cta_group::2): 0 where measured faster, 1 never, 2 always
   int prefix_variant = 0;        // stored-form prefix sweep: 0 auto (cp.async ring), 1 register loads, 2 ring
   int prefix_threads = 0;        // threads per CTA of the ring variant: 0 auto (even waves), else forced
