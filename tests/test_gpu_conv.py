@@ -815,6 +815,31 @@ def test_prefix_ring_kernel_matches_register_kernel(B, Hp, Wp, C, C1, pool_after
         _lib.set_tuning("prefix_threads", 0)
 
 
+def test_prefix_sweep_rejects_misaligned_operands():
+    """The sweep reads contributions and per-channel vectors with 16-byte accesses: an offset view
+    is refused instead of faulting."""
+    B, Hp, Wp, C, C1 = 2, 2, 2, 3, 8
+    pixels, M1 = B * Hp * Wp, B * Hp * Wp * C1
+    T = torch.zeros(C * M1 + 4, device=DEV)
+    base = torch.zeros(M1, dtype=torch.float64, device=DEV)
+    vec = torch.ones(C1 + 4, device=DEV)
+    perm = torch.arange(C, device=DEV)
+    hi = torch.zeros(C * M1, device=DEV)
+    lo = torch.zeros_like(hi)
+    ok = lambda t, sc: _lib.prefix_contrib_stack(t, perm, 0, C, base, sc, vec[:C1], pixels, C1, Hp,
+                                                 Wp, False, True, hi, lo)
+    assert ok(T[:C * M1], vec[:C1]) == M1
+    for variant in (1, 2):
+        _lib.set_tuning("prefix_variant", variant)
+        try:
+            with pytest.raises(_lib.TorchPrunerB200Error, match="aligned"):
+                ok(T[1:C * M1 + 1], vec[:C1])
+            with pytest.raises(_lib.TorchPrunerB200Error, match="aligned"):
+                ok(T[:C * M1], vec[1:C1 + 1])
+        finally:
+            _lib.set_tuning("prefix_variant", 0)
+
+
 def test_native_tail_runs_the_reference_mlp():
     """The 784-2024-2024-10 LeakyReLU perceptron of the reference's untrained-network notebook:
     Linear layers whose K is not a multiple of 32, LeakyReLU epilogue, dense incremental first

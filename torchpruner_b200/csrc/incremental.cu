@@ -816,6 +816,12 @@ static int prefix_contrib_stack_impl(const float* T, const int64_t* perm, int64_
   if (P == 0 || pixels == 0) return TP_OK;
   TP_REQUIRE(T && perm && base && scale && shift, TP_ERR_INVALID,
              "tp_prefix_contrib_stack: NULL pointer");
+  // 16-byte vector loads / cp.async of the contributions and the per-channel vectors, vector stores
+  TP_REQUIRE((uintptr_t)T % 16 == 0 && (uintptr_t)scale % 16 == 0 && (uintptr_t)shift % 16 == 0 &&
+                 (uintptr_t)base % 8 == 0 && (uintptr_t)out_hi % (half ? 8 : 16) == 0 &&
+                 (uintptr_t)out_lo % (half ? 8 : 16) == 0,
+             TP_ERR_INVALID, "tp_prefix_contrib_stack: T, scale, shift and the outputs must be "
+                             "16-byte aligned (fp16 outputs: 8)");
   PrefixGeom g;
   g.M1 = pixels * C1;
   g.C1 = (int)C1;
