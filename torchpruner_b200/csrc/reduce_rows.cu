@@ -51,7 +51,13 @@ template <>
 struct RowOpTraits<OP_APOZ> {
   using acc_t = int;
   static constexpr int kStreams = 1;
-  __device__ __forceinline__ static void add(acc_t& acc, float a, float) { acc += (a > 0.0f); }
+  // one compare and one predicated add per element (false for NaN and -0.0, as the reference's
+  // `output > 0`).  Written as `acc += (a > 0.0f)` the compiler emits three: compare, add into a
+  // copy, predicated move back — and the consumer warps of the small-row shapes are issue-bound.
+  __device__ __forceinline__ static void add(acc_t& acc, float a, float) {
+    asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %1, 0f00000000;\n\t@p add.s32 %0, %0, 1;\n\t}"
+        : "+r"(acc) : "f"(a));
+  }
   __device__ __forceinline__ static float finalize(acc_t acc, int) { return (float)acc; }
 };
 
