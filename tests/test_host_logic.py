@@ -211,3 +211,38 @@ def test_install_as_torchpruner():
                 sys.modules.pop(k, None)
             else:
                 sys.modules[k] = v
+
+
+def test_plan_signature_sees_what_pytorch_can_see():
+    """The plan caches are keyed by a signature of the model's tensors and modes (native_tail):
+    stable while nothing changes, different after an in-place write, a replaced ``.data`` (what
+    pruning does), a resized tensor, a BatchNorm/Dropout mode switch or a swapped module; a tensor
+    shared by two modules is no obstacle."""
+    from torchpruner_b200.attributions.native_tail import model_signature
+
+    torch.manual_seed(0)
+    shared = nn.Linear(6, 6)
+    model = nn.Sequential(nn.Conv2d(3, 4, 3), nn.BatchNorm2d(4), nn.ReLU(), nn.Flatten(),
+                          nn.Dropout(0.5), shared, shared).eval()
+    sig = model_signature(model)
+    assert sig == model_signature(model)
+    with torch.no_grad():
+        model[0].weight.mul_(2.0)                      # in-place write: version counter
+    sig2 = model_signature(model)
+    assert sig2 != sig
+    model[0].bias.data = model[0].bias.data.clone()    # same values, new storage
+    sig3 = model_signature(model)
+    assert sig3 != sig2
+    model[0].weight.data = model[0].weight.data[:3].clone()   # pruned
+    sig4 = model_signature(model)
+    assert sig4 != sig3
+    model[1].train()
+    sig5 = model_signature(model)
+    assert sig5 != sig4
+    model[1].eval()
+    assert model_signature(model) == sig4
+    model[1].running_mean.add_(1.0)                    # buffers count too
+    sig6 = model_signature(model)
+    assert sig6 != sig4
+    model[5] = nn.Linear(6, 6)
+    assert model_signature(model) != sig6
